@@ -1,0 +1,165 @@
+/* kgs.h - C ABI of libkgs, the B200 (sm_100a) hot path of kube_gpu_stats.
+ *
+ * The reference (two Python-2 scripts) exposes no plugin / operator / FFI interface
+ * (SURVEY.md section 8b): its boundary is a handful of Python functions.  This header is
+ * the boundary a native replacement of those loops binds to.  Each entry point cites the
+ * reference lines whose work it takes over ("GUS" = gpu_util_stats/gpu_util_stats.py,
+ * "WUG" = who_use_gpu/who_use_gpu.py under /root/reference); entry points for work that
+ * BASELINE.json's north_star names but the reference does not contain say so.
+ *
+ * Conventions
+ *   - every call returns an int: KGS_OK or a KGS_ERR_* code; nothing throws across the ABI;
+ *     kgs_last_error(h) returns the text of the most recent failure on that handle;
+ *   - the caller owns every host buffer it passes; the library owns all device memory it
+ *     allocates until kgs_destroy;
+ *   - a handle owns two CUDA streams (copy, compute) on one device; a handle is NOT
+ *     thread-safe, distinct handles are independent;
+ *   - there is no CPU fallback: without a CUDA device kgs_create fails.
+ */
+#ifndef KGS_H
+#define KGS_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct kgs_ctx* kgs_handle;
+
+enum {
+    KGS_OK = 0,
+    KGS_ERR_ARG = 1,       /* bad argument (null pointer, zero step, width not a multiple of step ...) */
+    KGS_ERR_CUDA = 2,      /* a CUDA runtime call failed; see kgs_last_error */
+    KGS_ERR_STATE = 3,     /* call out of order (e.g. accumulate before begin, probe before build_join) */
+    KGS_ERR_CAPACITY = 4,  /* a fixed-capacity scratch area overflowed (run log, static scratch) */
+    KGS_ERR_NOMEM = 5
+};
+
+/* key kinds of the windowed statistics (north_star: per-pod / per-GPU / per-node) */
+enum { KGS_KEY_POD = 0, KGS_KEY_GPU = 1, KGS_KEY_NODE = 2, KGS_N_KEY_KINDS = 3 };
+/* which field of the packed util word is aggregated */
+enum { KGS_METRIC_SM = 0, KGS_METRIC_MEM = 1, KGS_METRIC_FB = 2 };
+
+#define KGS_POD_NONE 0xFFFFFFFFu   /* probe result for a (node,pid) with no table entry */
+#define KGS_MAX_Q 8
+
+/* One windowed-statistics job.  Windows: pane p = (ts - t0) / step, window j covers panes
+ * j .. j + width/step - 1 (width == step: tumbling; width a larger multiple: sliding).
+ * Rules R1-R6 in oracle/window_stats.py are the specification. */
+typedef struct kgs_window_spec {
+    uint32_t key_mask;       /* bit k set: produce the table for key kind k */
+    uint32_t metric;         /* KGS_METRIC_* */
+    uint32_t gpus_per_node;  /* node = gpu_gid / gpus_per_node */
+    uint32_t t0;             /* start of window 0, seconds */
+    uint32_t step;           /* seconds between window starts (> 0) */
+    uint32_t width;          /* window width in seconds, a positive multiple of step */
+    uint32_t n_windows;      /* windows per key */
+    uint32_t n_gpus;         /* key domain of KGS_KEY_GPU  (gpu_gid  < n_gpus)  */
+    uint32_t n_nodes;        /* key domain of KGS_KEY_NODE (node     < n_nodes) */
+    uint32_t n_q;            /* number of percentiles, 0..KGS_MAX_Q */
+    double   q[KGS_MAX_Q];   /* each in [0,1] */
+    uint64_t total_samples_hint; /* upper bound of samples this job will accumulate (sizes the
+                                    value log and run log); 0 = size for the resident batch */
+} kgs_window_spec;
+
+/* ---- lifetime ------------------------------------------------------------------------ */
+/* No reference counterpart (the reference has no device).  device = CUDA ordinal. */
+int kgs_create(int device, kgs_handle* out);
+int kgs_destroy(kgs_handle h);
+/* Text of the last error on h; with h == NULL the last kgs_create failure of this thread. */
+const char* kgs_last_error(kgs_handle h);
+/* Wait for everything queued on the handle's streams. */
+int kgs_sync(kgs_handle h);
+const char* kgs_version(void);
+
+/* ---- ingestion (north_star subsystem 1) ---------------------------------------------- */
+/* Replaces the per-sample float() decode + list append of GUS:47-48 / GUS:73-74 as the way
+ * samples reach the statistics: the caller parses once into four u32 columns (16 B/sample)
+ * in pinned memory and the library copies them with cudaMemcpyAsync on its copy stream. */
+int kgs_alloc_pinned(kgs_handle h, size_t nbytes, void** out);
+int kgs_free_pinned(kgs_handle h, void* p);
+/* Copy one batch of n samples into the next of the handle's two device batch slots and make
+ * it the resident batch.  Asynchronous: the host columns must stay valid until kgs_sync or
+ * until a later blocking call on the handle returns.  Batches alternate between two slots,
+ * so the copy of batch i+1 overlaps the kernels still reading batch i. */
+int kgs_ingest(kgs_handle h, const uint32_t* ts, const uint32_t* gpu_gid, const uint32_t* pid,
+               const uint32_t* util, uint64_t n);
+/* Same, for columns that already live in this device's memory (no copy is made; the caller
+ * keeps them alive and unchanged until the work that reads them has been synchronised). */
+int kgs_adopt_device_batch(kgs_handle h, const uint32_t* d_ts, const uint32_t* d_gpu_gid,
+                           const uint32_t* d_pid, const uint32_t* d_util, uint64_t n);
+
+/* ---- (node,pid) -> pod join (north_star subsystem 2) ---------------------------------- */
+/* Build side.  Takes over the dictionaries the reference fills before joining: the
+ * server -> pod -> cards table of GUS:139-148 and the pod identity rows of WUG:27-49,
+ * re-keyed as (node << 32 | pid) -> pod_id.  Open addressing, linear probing, load <= 0.5.
+ * A repeated key keeps the LAST pair, as the reference's dict assignment does (GUS:78, GUS:148).
+ * keys/pod_ids are host arrays of m entries; n_pods = key domain of KGS_KEY_POD. */
+int kgs_build_join(kgs_handle h, const uint64_t* keys, const uint32_t* pod_ids, uint64_t m,
+                   uint32_t n_pods);
+/* Probe side for the resident batch: out_pod_id[i] = pod of sample i or KGS_POD_NONE.  Takes
+ * over the dict probes of GUS:86-91 (server_pods.get(server, {}).get(pod)).  out_pod_id is a
+ * host array of n entries; blocking. */
+int kgs_probe(kgs_handle h, uint32_t gpus_per_node, uint32_t* out_pod_id);
+
+/* ---- windowed statistics (north_star subsystem 3) ------------------------------------- */
+/* The mean of GUS:77-80 (sum/len, 0.0 when empty) generalised to windows and to three key
+ * kinds; max and percentiles have no reference counterpart.
+ * begin: size and clear the accumulators.  accumulate: fold the resident batch in (may be
+ * called once per ingested batch).  finalize: per-cell mean / max / percentiles into the
+ * device result tables.  kgs_window_stats = begin + accumulate + finalize. */
+int kgs_stats_begin(kgs_handle h, const kgs_window_spec* spec);
+int kgs_stats_accumulate(kgs_handle h);
+int kgs_stats_finalize(kgs_handle h);
+int kgs_window_stats(kgs_handle h, const kgs_window_spec* spec);
+/* Capacity, in entries of 16 B, of the run log the next percentile job allocates (0 = automatic:
+ * total_samples_hint / 8 + 65536 per key kind, ample for collector-ordered input).  A job whose
+ * input is far from collector order needs up to one entry per sample and key kind. */
+int kgs_set_run_log_capacity(kgs_handle h, uint64_t entries);
+/* Copy one key kind's result table to host arrays of n_keys * n_windows entries, cell index
+ * key * n_windows + window (pct: n_q rows of that length).  Any pointer may be NULL. Blocking. */
+int kgs_fetch_stats(kgs_handle h, int key_kind, uint64_t* count, uint64_t* sum, uint32_t* max,
+                    double* mean, double* pct);
+/* Device addresses of the same tables, for a caller that exchanges them GPU-to-GPU (the
+ * allgather of per-shard partial tables in north_star).  which: 0 count(u64) 1 sum(u64)
+ * 2 max(u32) 3 mean(f64) 4 pct(f64, n_q rows). */
+int kgs_result_device_ptr(kgs_handle h, int key_kind, int which, void** d_ptr, size_t* nbytes);
+/* All result tables of the finalized job are one contiguous device region (every table starts
+ * 256-byte aligned inside it): its address and size, so one collective can move them all.
+ * kgs_result_device_ptr addresses lie inside this region. */
+int kgs_result_region(kgs_handle h, void** d_ptr, size_t* nbytes);
+
+/* ---- the reference's own statistic, exactly ------------------------------------------- */
+/* GUS:77-80 and GUS:51 on a CSR layout: series s owns values[offsets[s] .. offsets[s+1]).
+ * out[s] = sum(values)/len (0.0 when empty) when div == 0 (GUS:77-80), otherwise
+ * (sum(values) * mul) / div - GUS:51 with mul = step_sec, div = time_range_sec, evaluated in the
+ * reference's order.  Series of up to 64 values are summed left to right by one thread, which
+ * reproduces the reference's naive fp64 sum bit for bit; longer series use a warp tree (within
+ * 1e-12 relative).  values/offsets/out are host arrays; blocking. */
+int kgs_segmented_mean_f64(kgs_handle h, const double* values, const uint64_t* offsets,
+                           uint64_t n_series, double mul, double div, double* out);
+
+/* ---- measurement ---------------------------------------------------------------------- */
+/* Kernel launches issued by this handle since creation (bench.py's gpu_launches). */
+int kgs_launch_count(kgs_handle h, uint64_t* out);
+/* With profiling on, every kernel launch is bracketed by CUDA events on the stream it runs
+ * on; kgs_kernel_time returns the accumulated device time and launch count of one kernel
+ * (ids: KGS_K_*), kgs_reset_kernel_times clears them. */
+enum { KGS_K_BUILD = 0, KGS_K_BUILD_FIN = 1, KGS_K_PROBE = 2, KGS_K_ACCUM = 3, KGS_K_FINALIZE = 4,
+       KGS_K_FINALIZE_BIG = 5, KGS_K_SEGMEAN = 6, KGS_K_CLEAR = 7, KGS_N_KERNELS = 8 };
+int kgs_set_profiling(kgs_handle h, int on);
+int kgs_kernel_time(kgs_handle h, int kernel_id, double* total_ms, uint64_t* launches);
+int kgs_reset_kernel_times(kgs_handle h);
+/* The handle's CUDA streams as cudaStream_t values (which: 0 copy, 1 compute), for a caller that
+ * wants to order its own device work (a collective, an event) after the library's kernels. */
+int kgs_stream(kgs_handle h, int which, void** out_stream);
+/* Device time between two marks on the compute stream (bench.py's timed region). */
+int kgs_mark(kgs_handle h, int which /* 0 or 1 */);
+int kgs_elapsed_ms(kgs_handle h, double* ms);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* KGS_H */

@@ -1,0 +1,731 @@
+// kgs.cu - host side of libkgs: the C ABI declared in include/kgs.h over the sm_100a kernels in
+// join.cuh / accum.cuh / finalize.cuh / segmean.cuh.  CUDA runtime only; no torch, no CPU path.
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/kgs.h"
+
+namespace kgs { constexpr int KGS_MAX_Q_ = KGS_MAX_Q; }
+
+#include "accum.cuh"
+#include "common.cuh"
+#include "finalize.cuh"
+#include "join.cuh"
+#include "segmean.cuh"
+
+using namespace kgs;
+
+namespace {
+
+thread_local std::string g_create_error;
+
+struct DevBuf {   // grow-only device buffer
+    void* p = nullptr;
+    size_t cap = 0;
+};
+
+struct Batch {
+    DevBuf col[4];
+    const uint32_t* ptr[4] = {nullptr, nullptr, nullptr, nullptr};
+    uint64_t n = 0;
+    cudaEvent_t ready = nullptr, consumed = nullptr;
+};
+
+struct KindState {
+    uint32_t n_keys = 0;
+    uint32_t* cnt = nullptr;
+    unsigned long long* sum = nullptr;
+    uint32_t* mx = nullptr;
+    uint32_t* head = nullptr;
+    unsigned long long* o_count = nullptr;
+    unsigned long long* o_sum = nullptr;
+    uint32_t* o_max = nullptr;
+    double* o_mean = nullptr;
+    double* o_pct = nullptr;
+};
+
+struct TimedLaunch {
+    int kid;
+    cudaEvent_t e0, e1;
+};
+
+}  // namespace
+
+struct kgs_ctx {
+    int device = 0;
+    cudaStream_t copy = nullptr, compute = nullptr;
+    std::string err;
+    Batch batch[2];
+    int cur = -1;
+    // join table
+    DevBuf slots, build_keys, build_pods;
+    uint32_t n_slots = 0, n_pods = 0;
+    bool has_table = false;
+    // statistics job
+    bool job_open = false, job_final = false;
+    kgs_window_spec spec{};
+    uint32_t W = 1, n_panes = 0;
+    KindState kind[3];
+    DevBuf arena, vals, desc, tmp, tmp2, tmp3, tmp4;
+    size_t clear_bytes = 0;
+    uint32_t* ctl = nullptr;       // [0] run cursor [1] run-log overflow [2] big-list length [3] spare
+    uint32_t* big_list = nullptr;
+    uint32_t big_cap = 0;
+    size_t result_off = 0, result_bytes = 0;
+    uint64_t vals_cap = 0, vals_used = 0, accumulated = 0;
+    uint32_t desc_cap = 0;
+    uint64_t run_cap_override = 0;
+    // measurement
+    uint64_t launches = 0;
+    bool prof = false;
+    std::vector<TimedLaunch> timed;
+    std::vector<cudaEvent_t> event_pool;
+    double k_ms[KGS_N_KERNELS] = {0};
+    uint64_t k_n[KGS_N_KERNELS] = {0};
+    cudaEvent_t mark[2] = {nullptr, nullptr};
+};
+
+namespace {
+
+int fail(kgs_handle h, int code, const std::string& msg) {
+    if (h) h->err = msg;
+    return code;
+}
+
+#define KGS_CUDA(h, call)                                                                        \
+    do {                                                                                         \
+        cudaError_t e_ = (call);                                                                 \
+        if (e_ != cudaSuccess)                                                                   \
+            return fail(h, KGS_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_));    \
+    } while (0)
+
+int reserve(kgs_handle h, DevBuf& b, size_t bytes) {
+    if (bytes <= b.cap) return KGS_OK;
+    if (b.p) KGS_CUDA(h, cudaFree(b.p));
+    b.p = nullptr;
+    b.cap = 0;
+    size_t want = bytes + bytes / 8 + 256;
+    cudaError_t e = cudaMalloc(&b.p, want);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(h, KGS_ERR_NOMEM, "cudaMalloc of " + std::to_string(want) + " bytes failed: " + cudaGetErrorString(e));
+    }
+    b.cap = want;
+    return KGS_OK;
+}
+
+cudaEvent_t pooled_event(kgs_handle h) {
+    if (!h->event_pool.empty()) {
+        cudaEvent_t e = h->event_pool.back();
+        h->event_pool.pop_back();
+        return e;
+    }
+    cudaEvent_t e = nullptr;
+    cudaEventCreate(&e);
+    return e;
+}
+
+// Every kernel launch goes through here: counts it and, with profiling on, brackets it with
+// events on the launching stream.
+template <class F>
+void launch(kgs_handle h, int kid, cudaStream_t st, F&& f) {
+    if (h->prof) {
+        TimedLaunch t{kid, pooled_event(h), pooled_event(h)};
+        cudaEventRecord(t.e0, st);
+        f();
+        cudaEventRecord(t.e1, st);
+        h->timed.push_back(t);
+    } else {
+        f();
+    }
+    h->launches++;
+}
+
+int drain_timed(kgs_handle h) {
+    for (auto& t : h->timed) {
+        KGS_CUDA(h, cudaEventSynchronize(t.e1));
+        float ms = 0.f;
+        KGS_CUDA(h, cudaEventElapsedTime(&ms, t.e0, t.e1));
+        h->k_ms[t.kid] += ms;
+        h->k_n[t.kid] += 1;
+        h->event_pool.push_back(t.e0);
+        h->event_pool.push_back(t.e1);
+    }
+    h->timed.clear();
+    return KGS_OK;
+}
+
+inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+int grid_for(uint64_t work_items, int per_block, int max_blocks) {
+    uint64_t b = (work_items + per_block - 1) / per_block;
+    if (b < 1) b = 1;
+    if (b > (uint64_t)max_blocks) b = max_blocks;
+    return (int)b;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* kgs_version(void) { return "libkgs 0.1 (sm_100a)"; }
+
+const char* kgs_last_error(kgs_handle h) { return h ? h->err.c_str() : g_create_error.c_str(); }
+
+int kgs_create(int device, kgs_handle* out) {
+    if (!out) return KGS_ERR_ARG;
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0) {
+        g_create_error = std::string("no CUDA device (libkgs has no CPU path): ") +
+                         (e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+        cudaGetLastError();
+        return KGS_ERR_CUDA;
+    }
+    if (device < 0 || device >= count) {
+        g_create_error = "device ordinal out of range";
+        return KGS_ERR_ARG;
+    }
+    kgs_ctx* h = new kgs_ctx();
+    h->device = device;
+    auto bail = [&](cudaError_t ce, const char* what) {
+        g_create_error = std::string(what) + ": " + cudaGetErrorString(ce);
+        delete h;
+        return KGS_ERR_CUDA;
+    };
+    if ((e = cudaSetDevice(device)) != cudaSuccess) return bail(e, "cudaSetDevice");
+    if ((e = cudaStreamCreateWithFlags(&h->copy, cudaStreamNonBlocking)) != cudaSuccess) return bail(e, "cudaStreamCreate");
+    if ((e = cudaStreamCreateWithFlags(&h->compute, cudaStreamNonBlocking)) != cudaSuccess) return bail(e, "cudaStreamCreate");
+    for (int b = 0; b < 2; ++b) {
+        if ((e = cudaEventCreateWithFlags(&h->batch[b].ready, cudaEventDisableTiming)) != cudaSuccess) return bail(e, "cudaEventCreate");
+        if ((e = cudaEventCreateWithFlags(&h->batch[b].consumed, cudaEventDisableTiming)) != cudaSuccess) return bail(e, "cudaEventCreate");
+        if ((e = cudaEventCreate(&h->mark[b])) != cudaSuccess) return bail(e, "cudaEventCreate");
+    }
+    *out = h;
+    return KGS_OK;
+}
+
+int kgs_destroy(kgs_handle h) {
+    if (!h) return KGS_OK;
+    cudaSetDevice(h->device);
+    cudaStreamSynchronize(h->copy);
+    cudaStreamSynchronize(h->compute);
+    for (auto& t : h->timed) {
+        cudaEventDestroy(t.e0);
+        cudaEventDestroy(t.e1);
+    }
+    for (auto e : h->event_pool) cudaEventDestroy(e);
+    for (int b = 0; b < 2; ++b) {
+        for (int c = 0; c < 4; ++c)
+            if (h->batch[b].col[c].p) cudaFree(h->batch[b].col[c].p);
+        cudaEventDestroy(h->batch[b].ready);
+        cudaEventDestroy(h->batch[b].consumed);
+        cudaEventDestroy(h->mark[b]);
+    }
+    DevBuf* bufs[] = {&h->slots, &h->build_keys, &h->build_pods, &h->arena, &h->vals, &h->desc,
+                      &h->tmp, &h->tmp2, &h->tmp3, &h->tmp4};
+    for (DevBuf* b : bufs)
+        if (b->p) cudaFree(b->p);
+    cudaStreamDestroy(h->copy);
+    cudaStreamDestroy(h->compute);
+    delete h;
+    return KGS_OK;
+}
+
+int kgs_sync(kgs_handle h) {
+    if (!h) return KGS_ERR_ARG;
+    KGS_CUDA(h, cudaSetDevice(h->device));
+    KGS_CUDA(h, cudaStreamSynchronize(h->copy));
+    KGS_CUDA(h, cudaStreamSynchronize(h->compute));
+    return KGS_OK;
+}
+
+int kgs_alloc_pinned(kgs_handle h, size_t nbytes, void** out) {
+    if (!h || !out) return KGS_ERR_ARG;
+    KGS_CUDA(h, cudaSetDevice(h->device));
+    cudaError_t e = cudaHostAlloc(out, nbytes ? nbytes : 1, cudaHostAllocDefault);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(h, KGS_ERR_NOMEM, std::string("cudaHostAlloc: ") + cudaGetErrorString(e));
+    }
+    return KGS_OK;
+}
+
+int kgs_free_pinned(kgs_handle h, void* p) {
+    if (!h) return KGS_ERR_ARG;
+    if (p) KGS_CUDA(h, cudaFreeHost(p));
+    return KGS_OK;
+}
+
+int kgs_ingest(kgs_handle h, const uint32_t* ts, const uint32_t* gpu_gid, const uint32_t* pid,
+               const uint32_t* util, uint64_t n) {
+    if (!h || (n && (!ts || !gpu_gid || !pid || !util))) return fail(h, KGS_ERR_ARG, "kgs_ingest: null column");
+    if (n >= (1ull << 32)) return fail(h, KGS_ERR_ARG, "kgs_ingest: a batch holds fewer than 2^32 samples");
+    KGS_CUDA(h, cudaSetDevice(h->device));
+    const int b = (h->cur + 1) & 1;
+    Batch& B = h->batch[b];
+    const uint32_t* src[4] = {ts, gpu_gid, pid, util};
+    // the slot may still be read by kernels queued on the compute stream
+    KGS_CUDA(h, cudaStreamWaitEvent(h->copy, B.consumed, 0));
+    for (int c = 0; c < 4; ++c) {
+        if (n * 4 + 16 > B.col[c].cap) {
+            // growing a slot frees device memory: make sure nothing is still using it
+            KGS_CUDA(h, cudaStreamSynchronize(h->compute));
+            KGS_CUDA(h, cudaStreamSynchronize(h->copy));
+        }
+        int rc = reserve(h, B.col[c], n * 4 + 16);
+        if (rc) return rc;
+        B.ptr[c] = static_cast<const uint32_t*>(B.col[c].p);
+        if (n) KGS_CUDA(h, cudaMemcpyAsync(B.col[c].p, src[c], n * 4, cudaMemcpyHostToDevice, h->copy));
+    }
+    B.n = n;
+    KGS_CUDA(h, cudaEventRecord(B.ready, h->copy));
+    h->cur = b;
+    return KGS_OK;
+}
+
+int kgs_adopt_device_batch(kgs_handle h, const uint32_t* d_ts, const uint32_t* d_gpu_gid,
+                           const uint32_t* d_pid, const uint32_t* d_util, uint64_t n) {
+    if (!h || (n && (!d_ts || !d_gpu_gid || !d_pid || !d_util))) return fail(h, KGS_ERR_ARG, "kgs_adopt_device_batch: null column");
+    if (n >= (1ull << 32)) return fail(h, KGS_ERR_ARG, "a batch holds fewer than 2^32 samples");
+    const uintptr_t all = (uintptr_t)d_ts | (uintptr_t)d_gpu_gid | (uintptr_t)d_pid | (uintptr_t)d_util;
+    if (all & 15) return fail(h, KGS_ERR_ARG, "device columns must be 16-byte aligned");
+    KGS_CUDA(h, cudaSetDevice(h->device));
+    const int b = (h->cur + 1) & 1;
+    Batch& B = h->batch[b];
+    B.ptr[0] = d_ts; B.ptr[1] = d_gpu_gid; B.ptr[2] = d_pid; B.ptr[3] = d_util;
+    B.n = n;
+    KGS_CUDA(h, cudaEventRecord(B.ready, h->copy));
+    h->cur = b;
+    return KGS_OK;
+}
+
+int kgs_build_join(kgs_handle h, const uint64_t* keys, const uint32_t* pod_ids, uint64_t m, uint32_t n_pods) {
+    if (!h || (m && (!keys || !pod_ids))) return fail(h, KGS_ERR_ARG, "kgs_build_join: null array");
+    if (m >= (1ull << 30)) return fail(h, KGS_ERR_ARG, "kgs_build_join: at most 2^30 - 1 pairs");
+    KGS_CUDA(h, cudaSetDevice(h->device));
+    for (uint64_t i = 0; i < m; ++i)
+        if (keys[i] == kEmptyKey) return fail(h, KGS_ERR_ARG, "kgs_build_join: key 0xFFFFFFFFFFFFFFFF is reserved");
+    uint32_t n_slots = 1024;
+    while (n_slots < 2 * m) n_slots <<= 1;
+    // the old table may still be read by queued kernels
+    KGS_CUDA(h, cudaStreamSynchronize(h->compute));
+    int rc;
+    if ((rc = reserve(h, h->slots, (size_t)n_slots * sizeof(JoinSlot)))) return rc;
+    if ((rc = reserve(h, h->build_keys, m * 8 + 8))) return rc;
+    if ((rc = reserve(h, h->build_pods, m * 4 + 4))) return rc;
+    cudaStream_t st = h->compute;
+    if (m) {
+        KGS_CUDA(h, cudaMemcpyAsync(h->build_keys.p, keys, m * 8, cudaMemcpyHostToDevice, st));
+        KGS_CUDA(h, cudaMemcpyAsync(h->build_pods.p, pod_ids, m * 4, cudaMemcpyHostToDevice, st));
+    }
+    JoinSlot* slots = static_cast<JoinSlot*>(h->slots.p);
+    launch(h, KGS_K_CLEAR, st, [&] { k_join_clear<<<grid_for(n_slots, 256, 148 * 8), 256, 0, st>>>(slots, n_slots); });
+    if (m) {
+        launch(h, KGS_K_BUILD, st, [&] {
+            k_join_build<<<grid_for(m, 256, 148 * 8), 256, 0, st>>>(
+                slots, n_slots - 1, static_cast<const unsigned long long*>(h->build_keys.p), (uint32_t)m);
+        });
+        launch(h, KGS_K_BUILD_FIN, st, [&] {
+            k_join_resolve<<<grid_for(n_slots, 256, 148 * 8), 256, 0, st>>>(
+                slots, n_slots, static_cast<const uint32_t*>(h->build_pods.p));
+        });
+    }
+    KGS_CUDA(h, cudaGetLastError());
+    // host arrays are pageable in general: do not return before they have been consumed
+    KGS_CUDA(h, cudaStreamSynchronize(st));
+    h->n_slots = n_slots;
+    h->n_pods = n_pods;
+    h->has_table = true;
+    return KGS_OK;
+}
+
+int kgs_probe(kgs_handle h, uint32_t gpus_per_node, uint32_t* out_pod_id) {
+    if (!h) return KGS_ERR_ARG;
+    if (!h->has_table) return fail(h, KGS_ERR_STATE, "kgs_probe: no join table (call kgs_build_join)");
+    if (h->cur < 0) return fail(h, KGS_ERR_STATE, "kgs_probe: no resident batch (call kgs_ingest)");
+    if (gpus_per_node == 0) return fail(h, KGS_ERR_ARG, "kgs_probe: gpus_per_node is 0");
+    KGS_CUDA(h, cudaSetDevice(h->device));
+    Batch& B = h->batch[h->cur];
+    if (B.n == 0) return KGS_OK;
+    if (!out_pod_id) return fail(h, KGS_ERR_ARG, "kgs_probe: null output");
+    int rc;
+    if ((rc = reserve(h, h->tmp, B.n * 4 + 16))) return rc;
+    cudaStream_t st = h->compute;
+    KGS_CUDA(h, cudaStreamWaitEvent(st, B.ready, 0));
+    launch(h, KGS_K_PROBE, st, [&] {
+        k_join_probe<<<grid_for(B.n / 4 + 1, 256, 148 * 8), 256, 0, st>>>(
+            static_cast<const JoinSlot*>(h->slots.p), h->n_slots - 1, B.ptr[1], B.ptr[2], B.n,
+            make_fastdiv(gpus_per_node), static_cast<uint32_t*>(h->tmp.p));
+    });
+    KGS_CUDA(h, cudaGetLastError());
+    KGS_CUDA(h, cudaEventRecord(B.consumed, st));
+    KGS_CUDA(h, cudaMemcpyAsync(out_pod_id, h->tmp.p, B.n * 4, cudaMemcpyDeviceToHost, st));
+    KGS_CUDA(h, cudaStreamSynchronize(st));
+    return KGS_OK;
+}
+
+int kgs_set_run_log_capacity(kgs_handle h, uint64_t entries) {
+    if (!h) return KGS_ERR_ARG;
+    h->run_cap_override = entries;
+    return KGS_OK;
+}
+
+int kgs_stats_begin(kgs_handle h, const kgs_window_spec* sp) {
+    if (!h || !sp) return KGS_ERR_ARG;
+    if (sp->key_mask == 0 || sp->key_mask > 7) return fail(h, KGS_ERR_ARG, "key_mask must select 1..3 key kinds");
+    if (sp->metric > KGS_METRIC_FB) return fail(h, KGS_ERR_ARG, "unknown metric");
+    if (sp->step == 0 || sp->width == 0 || sp->width % sp->step) return fail(h, KGS_ERR_ARG, "width must be a positive multiple of step");
+    if (sp->n_windows == 0) return fail(h, KGS_ERR_ARG, "n_windows is 0");
+    if (sp->gpus_per_node == 0) return fail(h, KGS_ERR_ARG, "gpus_per_node is 0");
+    if (sp->n_q > KGS_MAX_Q) return fail(h, KGS_ERR_ARG, "too many percentiles");
+    for (uint32_t i = 0; i < sp->n_q; ++i)
+        if (!(sp->q[i] >= 0.0 && sp->q[i] <= 1.0)) return fail(h, KGS_ERR_ARG, "percentile outside [0,1]");
+    if (sp->n_q && sp->metric == KGS_METRIC_FB)
+        return fail(h, KGS_ERR_ARG, "percentiles of fb_mib (16-bit domain) are not available yet; use mean/max");
+    if ((sp->key_mask & 1) && !h->has_table) return fail(h, KGS_ERR_STATE, "per-pod statistics need kgs_build_join first");
+    KGS_CUDA(h, cudaSetDevice(h->device));
+    const uint32_t W = sp->width / sp->step;
+    const uint64_t n_panes = (uint64_t)sp->n_windows + W - 1;
+    const uint32_t nk_in[3] = {h->n_pods, sp->n_gpus, sp->n_nodes};
+    uint64_t total_hint = sp->total_samples_hint;
+    if (!total_hint && h->cur >= 0) total_hint = h->batch[h->cur].n;
+    const bool pct = sp->n_q > 0;
+    // arena layout: [ctl | accumulators ...] cleared at begin, then results, then the big list
+    size_t off = 256, n_kinds = 0;
+    struct Lay { size_t cnt, sum, mx, head, oc, os, om, omean, opct; } lay[3];
+    for (int k = 0; k < 3; ++k) {
+        if (!(sp->key_mask & (1u << k))) continue;
+        ++n_kinds;
+        const uint64_t pc = (uint64_t)nk_in[k] * n_panes;
+        if (pc >= (1ull << 31)) return fail(h, KGS_ERR_ARG, "n_keys * n_panes must stay below 2^31 per key kind");
+        lay[k].sum = off; off = align_up(off + pc * 8, 256);
+        lay[k].cnt = off; off = align_up(off + pc * 4, 256);
+        lay[k].mx = off; off = align_up(off + pc * 4, 256);
+        lay[k].head = off; if (pct) off = align_up(off + pc * 4, 256);
+    }
+    const size_t clear_bytes = off;
+    for (int k = 0; k < 3; ++k) {
+        if (!(sp->key_mask & (1u << k))) continue;
+        const uint64_t wc = (uint64_t)nk_in[k] * sp->n_windows;
+        lay[k].oc = off; off = align_up(off + wc * 8, 256);
+        lay[k].os = off; off = align_up(off + wc * 8, 256);
+        lay[k].omean = off; off = align_up(off + wc * 8, 256);
+        lay[k].opct = off; off = align_up(off + wc * 8 * sp->n_q, 256);
+        lay[k].om = off; off = align_up(off + wc * 4, 256);
+    }
+    const uint32_t big_cap = (uint32_t)(total_hint / kSmallMax * (W) + 16) * (uint32_t)n_kinds;
+    const size_t big_off = off;
+    off = align_up(off + (size_t)big_cap * 8, 256);
+    // queued kernels may still use the previous job's arena
+    if (off > h->arena.cap) KGS_CUDA(h, cudaStreamSynchronize(h->compute));
+    int rc;
+    if ((rc = reserve(h, h->arena, off))) return rc;
+    char* base = static_cast<char*>(h->arena.p);
+    h->ctl = reinterpret_cast<uint32_t*>(base);
+    for (int k = 0; k < 3; ++k) {
+        KindState& K = h->kind[k];
+        K = KindState();
+        if (!(sp->key_mask & (1u << k))) continue;
+        K.n_keys = nk_in[k];
+        K.sum = reinterpret_cast<unsigned long long*>(base + lay[k].sum);
+        K.cnt = reinterpret_cast<uint32_t*>(base + lay[k].cnt);
+        K.mx = reinterpret_cast<uint32_t*>(base + lay[k].mx);
+        K.head = pct ? reinterpret_cast<uint32_t*>(base + lay[k].head) : nullptr;
+        K.o_count = reinterpret_cast<unsigned long long*>(base + lay[k].oc);
+        K.o_sum = reinterpret_cast<unsigned long long*>(base + lay[k].os);
+        K.o_mean = reinterpret_cast<double*>(base + lay[k].omean);
+        K.o_pct = reinterpret_cast<double*>(base + lay[k].opct);
+        K.o_max = reinterpret_cast<uint32_t*>(base + lay[k].om);
+    }
+    h->result_off = clear_bytes;
+    h->result_bytes = big_off - clear_bytes;
+    h->big_list = reinterpret_cast<uint32_t*>(base + big_off);
+    h->big_cap = big_cap;
+    h->clear_bytes = clear_bytes;
+    if (pct) {
+        const uint64_t vals_cap = total_hint + 16 * 4096 + 64;
+        if (vals_cap >= (1ull << 32)) return fail(h, KGS_ERR_ARG, "percentile jobs hold fewer than 2^32 samples per handle; shard the trace");
+        uint64_t dcap = h->run_cap_override ? h->run_cap_override : (total_hint / 8 + 65536) * n_kinds;
+        if (dcap > 0xFFFFFFF0ull) dcap = 0xFFFFFFF0ull;
+        if (vals_cap > h->vals.cap || dcap * 16 > h->desc.cap) KGS_CUDA(h, cudaStreamSynchronize(h->compute));
+        if ((rc = reserve(h, h->vals, vals_cap))) return rc;
+        if ((rc = reserve(h, h->desc, dcap * 16))) return rc;
+        h->vals_cap = vals_cap;
+        h->desc_cap = (uint32_t)dcap;
+    } else {
+        h->vals_cap = 0;
+        h->desc_cap = 0;
+    }
+    KGS_CUDA(h, cudaMemsetAsync(h->arena.p, 0, clear_bytes, h->compute));
+    h->spec = *sp;
+    h->W = W;
+    h->n_panes = (uint32_t)n_panes;
+    h->vals_used = 0;
+    h->accumulated = 0;
+    h->job_open = true;
+    h->job_final = false;
+    return KGS_OK;
+}
+
+int kgs_stats_accumulate(kgs_handle h) {
+    if (!h) return KGS_ERR_ARG;
+    if (!h->job_open) return fail(h, KGS_ERR_STATE, "kgs_stats_accumulate: no open job (call kgs_stats_begin)");
+    if (h->cur < 0) return fail(h, KGS_ERR_STATE, "kgs_stats_accumulate: no resident batch (call kgs_ingest)");
+    KGS_CUDA(h, cudaSetDevice(h->device));
+    Batch& B = h->batch[h->cur];
+    if (B.n == 0) return KGS_OK;
+    const kgs_window_spec& sp = h->spec;
+    const bool pct = sp.n_q > 0;
+    if (pct && h->vals_used + B.n + 16 > h->vals_cap)
+        return fail(h, KGS_ERR_CAPACITY, "value log full: total_samples_hint was smaller than the samples accumulated");
+    AccumParams P{};
+    P.ts = B.ptr[0]; P.gid = B.ptr[1]; P.pid = B.ptr[2]; P.util = B.ptr[3];
+    P.n = B.n;
+    P.vals_base = h->vals_used;
+    P.slots = static_cast<const JoinSlot*>(h->slots.p);
+    P.tmask = h->n_slots ? h->n_slots - 1 : 0;
+    P.t0 = sp.t0;
+    P.dstep = make_fastdiv(sp.step);
+    P.n_panes = h->n_panes;
+    P.dgpn = make_fastdiv(sp.gpus_per_node);
+    P.mshift = sp.metric == KGS_METRIC_SM ? 0 : sp.metric == KGS_METRIC_MEM ? 8 : 16;
+    P.mmask = sp.metric == KGS_METRIC_FB ? 0xFFFFu : 0xFFu;
+    P.key_mask = sp.key_mask;
+    for (int k = 0; k < 3; ++k) {
+        P.n_keys[k] = h->kind[k].n_keys;
+        P.cnt[k] = h->kind[k].cnt;
+        P.sum[k] = h->kind[k].sum;
+        P.mx[k] = h->kind[k].mx;
+        P.head[k] = h->kind[k].head;
+    }
+    P.vals = static_cast<uint8_t*>(h->vals.p);
+    P.desc = static_cast<uint4*>(h->desc.p);
+    P.desc_cap = h->desc_cap;
+    P.ctl = h->ctl;
+    cudaStream_t st = h->compute;
+    KGS_CUDA(h, cudaStreamWaitEvent(st, B.ready, 0));
+    const int grid = grid_for((B.n + 127) / 128, 8, 148 * 8);
+    launch(h, KGS_K_ACCUM, st, [&] {
+        if (pct) k_accum<true><<<grid, 256, 0, st>>>(P);
+        else k_accum<false><<<grid, 256, 0, st>>>(P);
+    });
+    KGS_CUDA(h, cudaGetLastError());
+    KGS_CUDA(h, cudaEventRecord(B.consumed, st));
+    if (pct) h->vals_used = align_up(h->vals_used + B.n, 16);
+    h->accumulated += B.n;
+    return KGS_OK;
+}
+
+int kgs_stats_finalize(kgs_handle h) {
+    if (!h) return KGS_ERR_ARG;
+    if (!h->job_open) return fail(h, KGS_ERR_STATE, "kgs_stats_finalize: no open job");
+    KGS_CUDA(h, cudaSetDevice(h->device));
+    const kgs_window_spec& sp = h->spec;
+    FinParams P{};
+    uint32_t slot = 0, cells = 0;
+    for (int k = 0; k < 3; ++k) {
+        if (!(sp.key_mask & (1u << k))) continue;
+        const KindState& K = h->kind[k];
+        FinKind& F = P.kind[slot++];
+        F.n_keys = K.n_keys;
+        F.cell_begin = cells;
+        F.cnt = K.cnt; F.sum = K.sum; F.mx = K.mx; F.head = K.head;
+        F.o_count = K.o_count; F.o_sum = K.o_sum; F.o_max = K.o_max; F.o_mean = K.o_mean; F.o_pct = K.o_pct;
+        const uint64_t wc = (uint64_t)K.n_keys * sp.n_windows;
+        if (cells + wc >= (1ull << 32)) return fail(h, KGS_ERR_ARG, "too many window cells");
+        cells += (uint32_t)wc;
+    }
+    for (uint32_t s = slot; s < 3; ++s) P.kind[s].cell_begin = 0xFFFFFFFFu;
+    P.n_kinds = slot;
+    P.total_cells = cells;
+    P.n_windows = sp.n_windows;
+    P.n_panes = h->n_panes;
+    P.W = h->W;
+    P.n_q = sp.n_q;
+    for (uint32_t i = 0; i < sp.n_q; ++i) P.q[i] = sp.q[i];
+    P.vals = static_cast<const uint8_t*>(h->vals.p);
+    P.desc = static_cast<const uint4*>(h->desc.p);
+    P.big_list = h->big_list;
+    P.ctl = h->ctl;
+    P.big_cap = h->big_cap;
+    cudaStream_t st = h->compute;
+    if (cells) {
+        launch(h, KGS_K_FINALIZE, st, [&] {
+            k_finalize<<<(cells + kFinThreads - 1) / kFinThreads, kFinThreads, 0, st>>>(P);
+        });
+        if (sp.n_q && h->accumulated > kSmallMax) {
+            launch(h, KGS_K_FINALIZE_BIG, st, [&] { k_finalize_big<<<148, 128, 0, st>>>(P); });
+        }
+    }
+    KGS_CUDA(h, cudaGetLastError());
+    h->job_final = true;
+    return KGS_OK;
+}
+
+int kgs_window_stats(kgs_handle h, const kgs_window_spec* spec) {
+    int rc;
+    if ((rc = kgs_stats_begin(h, spec))) return rc;
+    if ((rc = kgs_stats_accumulate(h))) return rc;
+    return kgs_stats_finalize(h);
+}
+
+static int check_job_flags(kgs_handle h) {
+    uint32_t ctl[4] = {0, 0, 0, 0};
+    KGS_CUDA(h, cudaMemcpyAsync(ctl, h->ctl, sizeof(ctl), cudaMemcpyDeviceToHost, h->compute));
+    KGS_CUDA(h, cudaStreamSynchronize(h->compute));
+    if (ctl[1])
+        return fail(h, KGS_ERR_CAPACITY,
+                    "run log overflow: " + std::to_string(ctl[0]) + " run descriptors needed, capacity " +
+                        std::to_string(h->desc_cap) + " (input far from collector order; raise it with kgs_set_run_log_capacity)");
+    return KGS_OK;
+}
+
+int kgs_fetch_stats(kgs_handle h, int key_kind, uint64_t* count, uint64_t* sum, uint32_t* max, double* mean, double* pct) {
+    if (!h) return KGS_ERR_ARG;
+    if (!h->job_final) return fail(h, KGS_ERR_STATE, "kgs_fetch_stats: no finalized job");
+    if (key_kind < 0 || key_kind > 2 || !(h->spec.key_mask & (1u << key_kind))) return fail(h, KGS_ERR_ARG, "key kind not part of this job");
+    KGS_CUDA(h, cudaSetDevice(h->device));
+    int rc;
+    if (h->spec.n_q && (rc = check_job_flags(h))) return rc;
+    const KindState& K = h->kind[key_kind];
+    const size_t wc = (size_t)K.n_keys * h->spec.n_windows;
+    cudaStream_t st = h->compute;
+    if (wc) {
+        if (count) KGS_CUDA(h, cudaMemcpyAsync(count, K.o_count, wc * 8, cudaMemcpyDeviceToHost, st));
+        if (sum) KGS_CUDA(h, cudaMemcpyAsync(sum, K.o_sum, wc * 8, cudaMemcpyDeviceToHost, st));
+        if (max) KGS_CUDA(h, cudaMemcpyAsync(max, K.o_max, wc * 4, cudaMemcpyDeviceToHost, st));
+        if (mean) KGS_CUDA(h, cudaMemcpyAsync(mean, K.o_mean, wc * 8, cudaMemcpyDeviceToHost, st));
+        if (pct && h->spec.n_q) KGS_CUDA(h, cudaMemcpyAsync(pct, K.o_pct, wc * 8 * h->spec.n_q, cudaMemcpyDeviceToHost, st));
+    }
+    KGS_CUDA(h, cudaStreamSynchronize(st));
+    return KGS_OK;
+}
+
+int kgs_result_device_ptr(kgs_handle h, int key_kind, int which, void** d_ptr, size_t* nbytes) {
+    if (!h || !d_ptr || !nbytes) return KGS_ERR_ARG;
+    if (!h->job_final) return fail(h, KGS_ERR_STATE, "kgs_result_device_ptr: no finalized job");
+    if (key_kind < 0 || key_kind > 2 || !(h->spec.key_mask & (1u << key_kind))) return fail(h, KGS_ERR_ARG, "key kind not part of this job");
+    const KindState& K = h->kind[key_kind];
+    const size_t wc = (size_t)K.n_keys * h->spec.n_windows;
+    switch (which) {
+        case 0: *d_ptr = K.o_count; *nbytes = wc * 8; break;
+        case 1: *d_ptr = K.o_sum; *nbytes = wc * 8; break;
+        case 2: *d_ptr = K.o_max; *nbytes = wc * 4; break;
+        case 3: *d_ptr = K.o_mean; *nbytes = wc * 8; break;
+        case 4: *d_ptr = K.o_pct; *nbytes = wc * 8 * h->spec.n_q; break;
+        default: return fail(h, KGS_ERR_ARG, "which must be 0..4");
+    }
+    return KGS_OK;
+}
+
+int kgs_result_region(kgs_handle h, void** d_ptr, size_t* nbytes) {
+    if (!h || !d_ptr || !nbytes) return KGS_ERR_ARG;
+    if (!h->job_final) return fail(h, KGS_ERR_STATE, "kgs_result_region: no finalized job");
+    *d_ptr = static_cast<char*>(h->arena.p) + h->result_off;
+    *nbytes = h->result_bytes;
+    return KGS_OK;
+}
+
+int kgs_segmented_mean_f64(kgs_handle h, const double* values, const uint64_t* offsets, uint64_t n_series,
+                           double mul, double div, double* out) {
+    if (!h) return KGS_ERR_ARG;
+    if (n_series == 0) return KGS_OK;
+    if (!offsets || !out) return fail(h, KGS_ERR_ARG, "kgs_segmented_mean_f64: null array");
+    if (n_series >= (1ull << 31)) return fail(h, KGS_ERR_ARG, "too many series");
+    const uint64_t nv = offsets[n_series];
+    if (nv && !values) return fail(h, KGS_ERR_ARG, "kgs_segmented_mean_f64: null values");
+    std::vector<uint32_t> long_ids;
+    for (uint64_t s = 0; s < n_series; ++s) {
+        if (offsets[s + 1] < offsets[s]) return fail(h, KGS_ERR_ARG, "offsets must be non-decreasing");
+        if (offsets[s + 1] - offsets[s] > kSeqMax) long_ids.push_back((uint32_t)s);
+    }
+    KGS_CUDA(h, cudaSetDevice(h->device));
+    cudaStream_t st = h->compute;
+    KGS_CUDA(h, cudaStreamSynchronize(st));   // tmp buffers may be reallocated
+    int rc;
+    if ((rc = reserve(h, h->tmp, nv * 8 + 8))) return rc;
+    if ((rc = reserve(h, h->tmp2, (n_series + 1) * 8))) return rc;
+    if ((rc = reserve(h, h->tmp3, n_series * 8))) return rc;
+    if ((rc = reserve(h, h->tmp4, long_ids.size() * 4 + 4))) return rc;
+    if (nv) KGS_CUDA(h, cudaMemcpyAsync(h->tmp.p, values, nv * 8, cudaMemcpyHostToDevice, st));
+    KGS_CUDA(h, cudaMemcpyAsync(h->tmp2.p, offsets, (n_series + 1) * 8, cudaMemcpyHostToDevice, st));
+    if (!long_ids.empty())
+        KGS_CUDA(h, cudaMemcpyAsync(h->tmp4.p, long_ids.data(), long_ids.size() * 4, cudaMemcpyHostToDevice, st));
+    const double* dv = static_cast<const double*>(h->tmp.p);
+    const unsigned long long* doff = static_cast<const unsigned long long*>(h->tmp2.p);
+    double* dout = static_cast<double*>(h->tmp3.p);
+    launch(h, KGS_K_SEGMEAN, st, [&] {
+        k_segmean_short<<<(unsigned)((n_series + 127) / 128), 128, 0, st>>>(dv, doff, (uint32_t)n_series, mul, div, dout);
+    });
+    if (!long_ids.empty()) {
+        const uint32_t nl = (uint32_t)long_ids.size();
+        launch(h, KGS_K_SEGMEAN, st, [&] {
+            k_segmean_long<<<(nl * 32 + 127) / 128, 128, 0, st>>>(dv, doff, static_cast<const uint32_t*>(h->tmp4.p), nl, mul, div, dout);
+        });
+    }
+    KGS_CUDA(h, cudaGetLastError());
+    KGS_CUDA(h, cudaMemcpyAsync(out, dout, n_series * 8, cudaMemcpyDeviceToHost, st));
+    KGS_CUDA(h, cudaStreamSynchronize(st));
+    return KGS_OK;
+}
+
+int kgs_launch_count(kgs_handle h, uint64_t* out) {
+    if (!h || !out) return KGS_ERR_ARG;
+    *out = h->launches;
+    return KGS_OK;
+}
+
+int kgs_set_profiling(kgs_handle h, int on) {
+    if (!h) return KGS_ERR_ARG;
+    int rc = drain_timed(h);
+    h->prof = on != 0;
+    return rc;
+}
+
+int kgs_kernel_time(kgs_handle h, int kernel_id, double* total_ms, uint64_t* launches) {
+    if (!h || kernel_id < 0 || kernel_id >= KGS_N_KERNELS) return KGS_ERR_ARG;
+    int rc = drain_timed(h);
+    if (rc) return rc;
+    if (total_ms) *total_ms = h->k_ms[kernel_id];
+    if (launches) *launches = h->k_n[kernel_id];
+    return KGS_OK;
+}
+
+int kgs_reset_kernel_times(kgs_handle h) {
+    if (!h) return KGS_ERR_ARG;
+    int rc = drain_timed(h);
+    for (int i = 0; i < KGS_N_KERNELS; ++i) {
+        h->k_ms[i] = 0;
+        h->k_n[i] = 0;
+    }
+    return rc;
+}
+
+int kgs_stream(kgs_handle h, int which, void** out_stream) {
+    if (!h || !out_stream || which < 0 || which > 1) return KGS_ERR_ARG;
+    *out_stream = which ? (void*)h->compute : (void*)h->copy;
+    return KGS_OK;
+}
+
+int kgs_mark(kgs_handle h, int which) {
+    if (!h || which < 0 || which > 1) return KGS_ERR_ARG;
+    KGS_CUDA(h, cudaSetDevice(h->device));
+    KGS_CUDA(h, cudaEventRecord(h->mark[which], h->compute));
+    return KGS_OK;
+}
+
+int kgs_elapsed_ms(kgs_handle h, double* ms) {
+    if (!h || !ms) return KGS_ERR_ARG;
+    KGS_CUDA(h, cudaEventSynchronize(h->mark[1]));
+    float f = 0.f;
+    KGS_CUDA(h, cudaEventElapsedTime(&f, h->mark[0], h->mark[1]));
+    *ms = f;
+    return KGS_OK;
+}
+
+}  // extern "C"

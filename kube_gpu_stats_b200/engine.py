@@ -1,0 +1,243 @@
+"""Engine: a thin object over one libkgs handle (one GPU, two CUDA streams).
+
+This is host plumbing only - every computation happens in libkgs.so.  The drop-in
+modules (``gpu_util_stats.py``, ``who_use_gpu.py``), ``bench.py`` and the tests
+all go through this class, i.e. through the C ABI of include/kgs.h.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _ffi
+
+KIND_ID = {'pod': _ffi.KEY_POD, 'gpu': _ffi.KEY_GPU, 'node': _ffi.KEY_NODE}
+METRIC_ID = {'sm': _ffi.METRIC_SM, 'mem': _ffi.METRIC_MEM, 'fb': _ffi.METRIC_FB}
+
+
+class KgsError(RuntimeError):
+    def __init__(self, code, text):
+        super().__init__('libkgs error %d: %s' % (code, text))
+        self.code = code
+
+
+def _u32(a):
+    return np.ascontiguousarray(a, dtype=np.uint32)
+
+
+class Engine:
+    def __init__(self, device=0):
+        self._lib = _ffi.lib()
+        h = C.c_void_p()
+        rc = self._lib.kgs_create(int(device), C.byref(h))
+        if rc:
+            raise KgsError(rc, self._lib.kgs_last_error(None).decode())
+        self._h = h
+        self.device = device
+        self._keep = []          # host arrays an asynchronous copy may still be reading
+        self._pinned = []
+        self._spec = None
+        self._n_keys = {}
+        self.n_resident = 0
+
+    # -- plumbing ---------------------------------------------------------------------
+    def _ck(self, rc):
+        if rc:
+            raise KgsError(rc, self._lib.kgs_last_error(self._h).decode())
+
+    def close(self):
+        if self._h:
+            for p in self._pinned:
+                self._lib.kgs_free_pinned(self._h, p)
+            self._pinned = []
+            self._lib.kgs_destroy(self._h)
+            self._h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def sync(self):
+        self._ck(self._lib.kgs_sync(self._h))
+        self._keep = []
+
+    def pinned(self, n, dtype=np.uint32):
+        """A numpy array over n elements of page-locked host memory (freed on close)."""
+        nbytes = int(n) * np.dtype(dtype).itemsize
+        p = C.c_void_p()
+        self._ck(self._lib.kgs_alloc_pinned(self._h, nbytes, C.byref(p)))
+        self._pinned.append(p)
+        buf = (C.c_char * max(nbytes, 1)).from_address(p.value)
+        return np.frombuffer(buf, dtype=dtype, count=int(n))
+
+    # -- ingestion --------------------------------------------------------------------
+    def ingest(self, ts, gpu_gid, pid, util):
+        """Queue the copy of one batch (four u32 columns) to the device; asynchronous."""
+        cols = [_u32(ts), _u32(gpu_gid), _u32(pid), _u32(util)]
+        n = len(cols[0])
+        if any(len(c) != n for c in cols):
+            raise ValueError('columns differ in length')
+        self._keep.append(cols)
+        self._ck(self._lib.kgs_ingest(self._h, *[c.ctypes.data for c in cols], n))
+        self.n_resident = n
+
+    def adopt_device_batch(self, d_ts, d_gid, d_pid, d_util, n):
+        self._ck(self._lib.kgs_adopt_device_batch(self._h, int(d_ts), int(d_gid), int(d_pid), int(d_util), int(n)))
+        self.n_resident = int(n)
+
+    # -- join -------------------------------------------------------------------------
+    def build_join(self, keys, pod_ids, n_pods):
+        keys = np.ascontiguousarray(keys, dtype=np.uint64)
+        pod_ids = _u32(pod_ids)
+        if len(keys) != len(pod_ids):
+            raise ValueError('keys and pod_ids differ in length')
+        self._ck(self._lib.kgs_build_join(self._h, keys.ctypes.data, pod_ids.ctypes.data, len(keys), int(n_pods)))
+        self._n_keys['pod'] = int(n_pods)
+
+    def probe(self, gpus_per_node=8):
+        out = np.empty(self.n_resident, dtype=np.uint32)
+        self._ck(self._lib.kgs_probe(self._h, int(gpus_per_node), out.ctypes.data))
+        self._keep = []
+        return out
+
+    # -- windowed statistics ------------------------------------------------------------
+    def make_spec(self, kinds=('pod',), metric='sm', gpus_per_node=8, t0=0, step=60, width=None,
+                  n_windows=1, n_gpus=0, n_nodes=0, qs=(), total_samples_hint=0):
+        sp = _ffi.WindowSpec()
+        sp.key_mask = 0
+        for k in kinds:
+            sp.key_mask |= 1 << KIND_ID[k]
+        sp.metric = METRIC_ID[metric] if isinstance(metric, str) else int(metric)
+        sp.gpus_per_node = gpus_per_node
+        sp.t0, sp.step, sp.width = int(t0), int(step), int(step if width is None else width)
+        sp.n_windows, sp.n_gpus, sp.n_nodes = int(n_windows), int(n_gpus), int(n_nodes)
+        if len(qs) > _ffi.MAX_Q:
+            raise ValueError('at most %d percentiles' % _ffi.MAX_Q)
+        sp.n_q = len(qs)
+        for i, q in enumerate(qs):
+            sp.q[i] = float(q)
+        sp.total_samples_hint = int(total_samples_hint)
+        return sp
+
+    def set_run_log_capacity(self, entries):
+        self._ck(self._lib.kgs_set_run_log_capacity(self._h, int(entries)))
+
+    def stats_begin(self, spec):
+        self._spec = spec
+        self._n_keys['gpu'] = spec.n_gpus
+        self._n_keys['node'] = spec.n_nodes
+        self._ck(self._lib.kgs_stats_begin(self._h, C.byref(spec)))
+
+    def stats_accumulate(self):
+        self._ck(self._lib.kgs_stats_accumulate(self._h))
+
+    def stats_finalize(self):
+        self._ck(self._lib.kgs_stats_finalize(self._h))
+
+    def window_stats_device(self, spec):
+        """begin + accumulate + finalize on the resident batch; results stay on the device."""
+        self._spec = spec
+        self._n_keys['gpu'] = spec.n_gpus
+        self._n_keys['node'] = spec.n_nodes
+        self._ck(self._lib.kgs_window_stats(self._h, C.byref(spec)))
+
+    def fetch(self, kind, want=('count', 'sum', 'max', 'mean', 'pct')):
+        sp = self._spec
+        ncell = self._n_keys[kind] * sp.n_windows
+        out = {}
+        if 'count' in want:
+            out['count'] = np.empty(ncell, dtype=np.uint64)
+        if 'sum' in want:
+            out['sum'] = np.empty(ncell, dtype=np.uint64)
+        if 'max' in want:
+            out['max'] = np.empty(ncell, dtype=np.uint32)
+        if 'mean' in want:
+            out['mean'] = np.empty(ncell, dtype=np.float64)
+        if 'pct' in want:
+            out['pct'] = np.empty((sp.n_q, ncell), dtype=np.float64)
+
+        def ptr(name):
+            return out[name].ctypes.data if name in out and out[name].size else None
+
+        self._ck(self._lib.kgs_fetch_stats(self._h, KIND_ID[kind], ptr('count'), ptr('sum'), ptr('max'),
+                                           ptr('mean'), ptr('pct')))
+        self._keep = []
+        return out
+
+    def window_stats(self, kinds=('pod',), **kw):
+        """One-shot job on the resident batch.  Returns {kind: {count,sum,max,mean,pct}}.
+        If the run log overflows (input far from collector order) the job is repeated once
+        with a run log sized for the worst case."""
+        spec = self.make_spec(kinds=kinds, **kw)
+        for attempt in (0, 1):
+            self.window_stats_device(spec)
+            try:
+                return {k: self.fetch(k) for k in kinds}
+            except KgsError as e:
+                if e.code != _ffi.KGS_ERR_CAPACITY or attempt:
+                    raise
+                self.set_run_log_capacity((self.n_resident + 64) * len(kinds))
+        raise AssertionError('unreachable')
+
+    def result_device_ptr(self, kind, which):
+        p, n = C.c_void_p(), C.c_size_t()
+        self._ck(self._lib.kgs_result_device_ptr(self._h, KIND_ID[kind], int(which), C.byref(p), C.byref(n)))
+        return p.value, n.value
+
+    def result_region(self):
+        p, n = C.c_void_p(), C.c_size_t()
+        self._ck(self._lib.kgs_result_region(self._h, C.byref(p), C.byref(n)))
+        return p.value, n.value
+
+    # -- the reference's statistic ------------------------------------------------------
+    def segmented_mean(self, values, offsets, mul=0.0, div=0.0):
+        values = np.ascontiguousarray(values, dtype=np.float64)
+        offsets = np.ascontiguousarray(offsets, dtype=np.uint64)
+        ns = len(offsets) - 1
+        out = np.empty(max(ns, 0), dtype=np.float64)
+        if ns > 0:
+            self._ck(self._lib.kgs_segmented_mean_f64(self._h, values.ctypes.data, offsets.ctypes.data, ns,
+                                                      float(mul), float(div), out.ctypes.data))
+        return out
+
+    # -- measurement --------------------------------------------------------------------
+    def launch_count(self):
+        n = C.c_uint64()
+        self._ck(self._lib.kgs_launch_count(self._h, C.byref(n)))
+        return n.value
+
+    def set_profiling(self, on):
+        self._ck(self._lib.kgs_set_profiling(self._h, 1 if on else 0))
+
+    def reset_kernel_times(self):
+        self._ck(self._lib.kgs_reset_kernel_times(self._h))
+
+    def kernel_times(self):
+        """{kernel name: (total ms, launches)} accumulated while profiling was on."""
+        out = {}
+        for kid, name in enumerate(_ffi.KERNEL_NAMES):
+            ms, n = C.c_double(), C.c_uint64()
+            self._ck(self._lib.kgs_kernel_time(self._h, kid, C.byref(ms), C.byref(n)))
+            out[name] = (ms.value, n.value)
+        return out
+
+    def stream(self, which='compute'):
+        """cudaStream_t of the handle's copy / compute stream as an integer."""
+        p = C.c_void_p()
+        self._ck(self._lib.kgs_stream(self._h, 1 if which == 'compute' else 0, C.byref(p)))
+        return p.value or 0
+
+    def mark(self, which):
+        self._ck(self._lib.kgs_mark(self._h, which))
+
+    def elapsed_ms(self):
+        ms = C.c_double()
+        self._ck(self._lib.kgs_elapsed_ms(self._h, C.byref(ms)))
+        return ms.value

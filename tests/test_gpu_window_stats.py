@@ -1,0 +1,154 @@
+"""Windowed statistics through the C ABI vs the oracle (rules R1-R6).  Integer results and
+percentiles are bit-exact; mean is an exact integer sum with one correctly rounded divide, so
+it is compared bit for bit as well (tolerance 0, tighter than north_star's 1e-12)."""
+import numpy as np
+import pytest
+
+from conftest import assert_stats_equal
+from kube_gpu_stats_b200 import synth
+from oracle import window_stats as ws
+
+pytestmark = pytest.mark.gpu
+
+KINDS = {'pod': ws.KEY_POD, 'gpu': ws.KEY_GPU, 'node': ws.KEY_NODE}
+METRICS = {'sm': 0, 'mem': 1, 'fb': 2}
+QS = (0.5, 0.95, 0.99)
+
+
+def n_keys_of(tr, kind):
+    return {'pod': tr.n_pods, 'gpu': tr.n_gpus, 'node': tr.n_nodes}[kind]
+
+
+def oracle(tr, kind, metric, t0, step, width, n_windows, qs):
+    return ws.window_stats_np(tr.ts, tr.gpu_gid, tr.pid, tr.util, tr.keys, tr.pod_ids,
+                              key_kind=KINDS[kind], metric=METRICS[metric], gpus_per_node=tr.gpus_per_node,
+                              t0=t0, step=step, width=width, n_windows=n_windows,
+                              n_keys=n_keys_of(tr, kind), qs=qs)
+
+
+def run(engine, tr, kinds, metric, t0, step, width, n_windows, qs, ingest=True):
+    if ingest:
+        engine.build_join(tr.keys, tr.pod_ids, tr.n_pods)
+        engine.ingest(tr.ts, tr.gpu_gid, tr.pid, tr.util)
+    return engine.window_stats(kinds=kinds, metric=metric, gpus_per_node=tr.gpus_per_node, t0=t0, step=step,
+                               width=width, n_windows=n_windows, n_gpus=tr.n_gpus, n_nodes=tr.n_nodes, qs=qs)
+
+
+def check(engine, tr, kinds, metric, t0, step, width, n_windows, qs, ingest=True):
+    got = run(engine, tr, kinds, metric, t0, step, width, n_windows, qs, ingest)
+    for k in kinds:
+        assert_stats_equal(got[k], oracle(tr, k, metric, t0, step, width, n_windows, qs), what='%s/%s' % (k, metric))
+
+
+@pytest.fixture(scope='module')
+def cfg1():
+    return synth.config(1)
+
+
+def test_cfg1_tumbling_all_kinds(engine, cfg1):
+    """BASELINE configs[0]: 1 node x 8 GPUs x 8 procs, 32 pods, 1 h at 1 s; 1-min windows."""
+    check(engine, cfg1, ('pod', 'gpu', 'node'), 'sm', cfg1.t0, 60, 60, 60, QS)
+
+
+def test_cfg1_mem_metric_single_kinds(engine, cfg1):
+    for kind in ('pod', 'gpu', 'node'):
+        check(engine, cfg1, (kind,), 'mem', cfg1.t0, 60, 60, 60, (0.95,), ingest=(kind == 'pod'))
+
+
+def test_cfg1_small_python_statement(engine, cfg1):
+    """The loop statement of the rules (window_stats_py) on a slice small enough for it."""
+    n = 20000
+    tr = synth.Trace(cfg1.ts[:n], cfg1.gpu_gid[:n], cfg1.pid[:n], cfg1.util[:n], cfg1.keys, cfg1.pod_ids,
+                     cfg1.n_pods, cfg1.n_nodes, 8, cfg1.t0, 3600)
+    got = run(engine, tr, ('pod',), 'sm', tr.t0, 60, 60, 6, QS)['pod']
+    table = ws.build_table(tr.keys, tr.pod_ids)
+    want = ws.window_stats_py(tr.ts, tr.gpu_gid, tr.pid, tr.util, table, key_kind=ws.KEY_POD, metric=0,
+                              gpus_per_node=8, t0=tr.t0, step=60, width=60, n_windows=6, n_keys=tr.n_pods, qs=QS)
+    assert_stats_equal(got, {k: np.array(v) for k, v in want.items()}, what='py statement')
+
+
+def test_cfg2_slice(engine):
+    """BASELINE configs[1] shape at 1/50 scale: 20 nodes x 8 GPUs x 1 h, 200 pods (tenancy churn)."""
+    tr = synth.config(2, scale=0.02)
+    check(engine, tr, ('pod', 'gpu', 'node'), 'sm', tr.t0, 60, 60, 60, (0.95,))
+
+
+def test_mean_max_only_and_fb_metric(engine, cfg1):
+    check(engine, cfg1, ('pod', 'gpu', 'node'), 'sm', cfg1.t0, 60, 60, 60, ())
+    check(engine, cfg1, ('pod', 'node'), 'fb', cfg1.t0, 300, 300, 12, (), ingest=False)
+
+
+def test_window_edges_and_odd_step(engine, cfg1):
+    """t0 inside the trace, a step that divides nothing, fewer windows than the trace covers:
+    samples before t0 and after the last window are left out (R3)."""
+    check(engine, cfg1, ('pod', 'gpu'), 'sm', cfg1.t0 + 123, 7, 7, 100, QS)
+    check(engine, cfg1, ('gpu',), 'sm', cfg1.t0 + 5000, 60, 60, 4, QS, ingest=False)      # nothing in range
+    check(engine, cfg1, ('node',), 'sm', cfg1.t0 - 100, 1, 1, 200, (0.5,), ingest=False)  # step 1, empty head
+
+
+def test_sliding_windows(engine, cfg1):
+    """configs[4] shape in small: width 5 panes, step 10 s."""
+    check(engine, cfg1, ('pod', 'gpu', 'node'), 'sm', cfg1.t0, 10, 50, 356, (0.5, 0.99))
+
+
+def test_whole_range_big_cells(engine, cfg1):
+    """One window over the hour: the node cell holds 230 400 samples (> 65 535: the u32-bin path)."""
+    check(engine, cfg1, ('pod', 'gpu', 'node'), 'sm', cfg1.t0, 3600, 3600, 1, QS)
+
+
+def test_shuffled_order(engine, cfg1):
+    """Any input order must give the same tables (runs of length ~1: ragged path, run-log retry)."""
+    rng = np.random.default_rng(5)
+    n = 60000
+    idx = rng.permutation(cfg1.n)[:n]
+    tr = synth.Trace(cfg1.ts[idx], cfg1.gpu_gid[idx], cfg1.pid[idx], cfg1.util[idx], cfg1.keys, cfg1.pod_ids,
+                     cfg1.n_pods, cfg1.n_nodes, 8, cfg1.t0, 3600)
+    check(engine, tr, ('pod', 'gpu', 'node'), 'sm', tr.t0, 60, 60, 60, QS)
+
+
+@pytest.mark.parametrize('n', [0, 1, 3, 4, 5, 127, 128, 129, 1000])
+def test_ragged_sizes_full_u8_domain(engine, n):
+    """Tiny and ragged batches, values over the whole 0..255 byte domain, unmatched pids."""
+    rng = np.random.default_rng(n)
+    gid = np.sort(rng.integers(0, 16, size=n)).astype(np.uint32)
+    ts = (1000 + np.arange(n) // 3).astype(np.uint32)
+    pid = rng.integers(1, 4, size=n).astype(np.uint32)
+    util = rng.integers(0, 1 << 32, size=n, dtype=np.uint64).astype(np.uint32)
+    keys = np.array([(0 << 32) | 1, (0 << 32) | 2, (1 << 32) | 1, (1 << 32) | 3], np.uint64)
+    pods = np.array([0, 1, 2, 1], np.uint32)
+    tr = synth.Trace(ts, gid, pid, util, keys, pods, 3, 2, 8, 1000, 400)
+    check(engine, tr, ('pod', 'gpu', 'node'), 'mem', 1000, 5, 10, 20, (0.0, 0.5, 1.0))
+
+
+def test_streamed_batches_equal_one_batch(engine, cfg1):
+    """begin / (ingest, accumulate)* / finalize over 7 uneven batches == the one-shot job."""
+    tr = cfg1
+    engine.build_join(tr.keys, tr.pod_ids, tr.n_pods)
+    spec = engine.make_spec(kinds=('pod', 'gpu', 'node'), metric='sm', gpus_per_node=8, t0=tr.t0, step=60,
+                            n_windows=60, n_gpus=tr.n_gpus, n_nodes=tr.n_nodes, qs=QS, total_samples_hint=tr.n)
+    engine.stats_begin(spec)
+    cuts = [0, 1001, 50000, 50003, 120000, 200001, 230399, tr.n]
+    for a, b in zip(cuts[:-1], cuts[1:]):
+        engine.ingest(tr.ts[a:b], tr.gpu_gid[a:b], tr.pid[a:b], tr.util[a:b])
+        engine.stats_accumulate()
+    engine.stats_finalize()
+    for k in ('pod', 'gpu', 'node'):
+        assert_stats_equal(engine.fetch(k), oracle(tr, k, 'sm', tr.t0, 60, 60, 60, QS), what='streamed ' + k)
+
+
+def test_state_and_argument_errors(engine, cfg1):
+    from kube_gpu_stats_b200 import _ffi
+    from kube_gpu_stats_b200.engine import KgsError
+    with pytest.raises(KgsError) as e:
+        engine.stats_accumulate()
+    assert e.value.code == _ffi.KGS_ERR_STATE
+    engine.ingest(cfg1.ts[:8], cfg1.gpu_gid[:8], cfg1.pid[:8], cfg1.util[:8])
+    with pytest.raises(KgsError) as e:      # per-pod job without a join table
+        engine.window_stats(kinds=('pod',), t0=cfg1.t0, step=60, n_windows=1)
+    assert e.value.code == _ffi.KGS_ERR_STATE
+    with pytest.raises(KgsError) as e:      # width not a multiple of step
+        engine.window_stats(kinds=('gpu',), t0=cfg1.t0, step=60, width=90, n_windows=1, n_gpus=8)
+    assert e.value.code == _ffi.KGS_ERR_ARG
+    with pytest.raises(KgsError) as e:
+        engine.window_stats(kinds=('gpu',), t0=cfg1.t0, step=60, n_windows=1, n_gpus=8, qs=(1.5,))
+    assert e.value.code == _ffi.KGS_ERR_ARG
