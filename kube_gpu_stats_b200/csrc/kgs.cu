@@ -73,7 +73,8 @@ struct kgs_ctx {
     size_t clear_bytes = 0;
     uint32_t* ctl = nullptr;       // [0] run cursor [1] run-log overflow [2] big-list length [3] spare
     uint32_t* big_list = nullptr;
-    uint32_t big_cap = 0;
+    uint32_t* mid_list = nullptr;
+    uint32_t big_cap = 0, mid_cap = 0;
     size_t result_off = 0, result_bytes = 0;
     uint64_t vals_cap = 0, vals_used = 0, accumulated = 0;
     uint32_t desc_cap = 0;
@@ -421,6 +422,12 @@ int kgs_stats_begin(kgs_handle h, const kgs_window_spec* sp) {
     const uint32_t big_cap = (uint32_t)(total_hint / kSmallMax * (W) + 16) * (uint32_t)n_kinds;
     const size_t big_off = off;
     off = align_up(off + (size_t)big_cap * 8, 256);
+    uint64_t mid_cap = 0;
+    if (pct)
+        for (int k = 0; k < 3; ++k)
+            if (sp->key_mask & (1u << k)) mid_cap += (uint64_t)nk_in[k] * sp->n_windows;
+    const size_t mid_off = off;
+    off = align_up(off + (size_t)mid_cap * 8, 256);
     // queued kernels may still use the previous job's arena
     if (off > h->arena.cap) KGS_CUDA(h, cudaStreamSynchronize(h->compute));
     int rc;
@@ -446,6 +453,8 @@ int kgs_stats_begin(kgs_handle h, const kgs_window_spec* sp) {
     h->result_bytes = big_off - clear_bytes;
     h->big_list = reinterpret_cast<uint32_t*>(base + big_off);
     h->big_cap = big_cap;
+    h->mid_list = reinterpret_cast<uint32_t*>(base + mid_off);
+    h->mid_cap = (uint32_t)mid_cap;
     h->clear_bytes = clear_bytes;
     if (pct) {
         const uint64_t vals_cap = total_hint + 16 * 4096 + 64;
@@ -509,7 +518,12 @@ int kgs_stats_accumulate(kgs_handle h) {
     P.ctl = h->ctl;
     cudaStream_t st = h->compute;
     KGS_CUDA(h, cudaStreamWaitEvent(st, B.ready, 0));
-    const int grid = grid_for((B.n + 127) / 128, 8, 148 * 8);
+    // 4 CTAs of 8 warps per SM; every warp owns a contiguous chunk of 128-sample tiles
+    const uint64_t n_tiles = (B.n + 127) / 128;
+    const uint64_t max_warps = 148ull * 4 * kAccumWarps;
+    const uint64_t tpw = (n_tiles + max_warps - 1) / max_warps;
+    P.tiles_per_warp = (uint32_t)(tpw < 4 ? 4 : tpw);
+    const int grid = (int)((n_tiles + (uint64_t)P.tiles_per_warp * kAccumWarps - 1) / ((uint64_t)P.tiles_per_warp * kAccumWarps));
     launch(h, KGS_K_ACCUM, st, [&] {
         if (pct) k_accum<true><<<grid, 256, 0, st>>>(P);
         else k_accum<false><<<grid, 256, 0, st>>>(P);
@@ -551,14 +565,20 @@ int kgs_stats_finalize(kgs_handle h) {
     P.vals = static_cast<const uint8_t*>(h->vals.p);
     P.desc = static_cast<const uint4*>(h->desc.p);
     P.big_list = h->big_list;
+    P.mid_list = h->mid_list;
     P.ctl = h->ctl;
     P.big_cap = h->big_cap;
+    P.mid_cap = h->mid_cap;
     cudaStream_t st = h->compute;
     if (cells) {
         launch(h, KGS_K_FINALIZE, st, [&] {
-            k_finalize<<<(cells + kFinThreads - 1) / kFinThreads, kFinThreads, 0, st>>>(P);
+            k_finalize_tiny<<<(cells + TinyLayout::NT - 1) / TinyLayout::NT, TinyLayout::NT, 0, st>>>(P);
         });
-        if (sp.n_q && h->accumulated > kSmallMax) {
+        if (sp.n_q) {   // cells above 255 samples or with values >= 128
+            const int mid_grid = grid_for(cells, MidLayout::NT, 148 * 6);
+            launch(h, KGS_K_FINALIZE_MID, st, [&] { k_finalize_mid<<<mid_grid, MidLayout::NT, 0, st>>>(P); });
+        }
+        if (sp.n_q && h->accumulated * h->W > kSmallMax) {
             launch(h, KGS_K_FINALIZE_BIG, st, [&] { k_finalize_big<<<148, 128, 0, st>>>(P); });
         }
     }
