@@ -148,7 +148,7 @@ int kgs_launch_count(kgs_handle h, uint64_t* out);
  * on; kgs_kernel_time returns the accumulated device time and launch count of one kernel
  * (ids: KGS_K_*), kgs_reset_kernel_times clears them. */
 enum { KGS_K_BUILD = 0, KGS_K_BUILD_FIN = 1, KGS_K_PROBE = 2, KGS_K_ACCUM = 3, KGS_K_FINALIZE = 4,
-       KGS_K_FINALIZE_BIG = 5, KGS_K_SEGMEAN = 6, KGS_K_CLEAR = 7, KGS_K_FINALIZE_MID = 8, KGS_N_KERNELS = 9 };
+       KGS_K_FINALIZE_BIG = 5, KGS_K_SEGMEAN = 6, KGS_K_CLEAR = 7, KGS_K_FINALIZE_WIDE = 8, KGS_N_KERNELS = 9 };
 int kgs_set_profiling(kgs_handle h, int on);
 int kgs_kernel_time(kgs_handle h, int kernel_id, double* total_ms, uint64_t* launches);
 int kgs_reset_kernel_times(kgs_handle h);

@@ -16,9 +16,9 @@ KEY_POD, KEY_GPU, KEY_NODE = 0, 1, 2
 METRIC_SM, METRIC_MEM, METRIC_FB = 0, 1, 2
 POD_NONE = 0xFFFFFFFF
 MAX_Q = 8
-(K_BUILD, K_BUILD_FIN, K_PROBE, K_ACCUM, K_FINALIZE, K_FINALIZE_BIG, K_SEGMEAN, K_CLEAR, K_FINALIZE_MID) = range(9)
-KERNEL_NAMES = ['join_build', 'join_resolve', 'join_probe', 'accum', 'finalize_tiny', 'finalize_big',
-                'segmean', 'join_clear', 'finalize_mid']
+(K_BUILD, K_BUILD_FIN, K_PROBE, K_ACCUM, K_FINALIZE, K_FINALIZE_BIG, K_SEGMEAN, K_CLEAR, K_FINALIZE_WIDE) = range(9)
+KERNEL_NAMES = ['join_build', 'join_resolve', 'join_probe', 'accum', 'finalize_cells', 'finalize_big',
+                'segmean', 'join_clear', 'finalize_wide']
 
 
 class WindowSpec(C.Structure):

@@ -73,8 +73,8 @@ struct kgs_ctx {
     size_t clear_bytes = 0;
     uint32_t* ctl = nullptr;       // [0] run cursor [1] run-log overflow [2] big-list length [3] spare
     uint32_t* big_list = nullptr;
-    uint32_t* mid_list = nullptr;
-    uint32_t big_cap = 0, mid_cap = 0;
+    uint32_t* wide_list = nullptr;
+    uint32_t big_cap = 0, wide_cap = 0;
     size_t result_off = 0, result_bytes = 0;
     uint64_t vals_cap = 0, vals_used = 0, accumulated = 0;
     uint32_t desc_cap = 0;
@@ -422,12 +422,12 @@ int kgs_stats_begin(kgs_handle h, const kgs_window_spec* sp) {
     const uint32_t big_cap = (uint32_t)(total_hint / kSmallMax * (W) + 16) * (uint32_t)n_kinds;
     const size_t big_off = off;
     off = align_up(off + (size_t)big_cap * 8, 256);
-    uint64_t mid_cap = 0;
+    uint64_t wide_cap = 0;
     if (pct)
         for (int k = 0; k < 3; ++k)
-            if (sp->key_mask & (1u << k)) mid_cap += (uint64_t)nk_in[k] * sp->n_windows;
-    const size_t mid_off = off;
-    off = align_up(off + (size_t)mid_cap * 8, 256);
+            if (sp->key_mask & (1u << k)) wide_cap += (uint64_t)nk_in[k] * sp->n_windows;
+    const size_t wide_off = off;
+    off = align_up(off + (size_t)wide_cap * 8, 256);
     // queued kernels may still use the previous job's arena
     if (off > h->arena.cap) KGS_CUDA(h, cudaStreamSynchronize(h->compute));
     int rc;
@@ -453,8 +453,8 @@ int kgs_stats_begin(kgs_handle h, const kgs_window_spec* sp) {
     h->result_bytes = big_off - clear_bytes;
     h->big_list = reinterpret_cast<uint32_t*>(base + big_off);
     h->big_cap = big_cap;
-    h->mid_list = reinterpret_cast<uint32_t*>(base + mid_off);
-    h->mid_cap = (uint32_t)mid_cap;
+    h->wide_list = reinterpret_cast<uint32_t*>(base + wide_off);
+    h->wide_cap = (uint32_t)wide_cap;
     h->clear_bytes = clear_bytes;
     if (pct) {
         const uint64_t vals_cap = total_hint + 16 * 4096 + 64;
@@ -561,22 +561,33 @@ int kgs_stats_finalize(kgs_handle h) {
     P.n_panes = h->n_panes;
     P.W = h->W;
     P.n_q = sp.n_q;
-    for (uint32_t i = 0; i < sp.n_q; ++i) P.q[i] = sp.q[i];
+    {   // ascending percentiles for the one-pass selection; q_row restores the caller's order
+        uint32_t order[KGS_MAX_Q];
+        for (uint32_t i = 0; i < sp.n_q; ++i) order[i] = i;
+        for (uint32_t i = 1; i < sp.n_q; ++i)
+            for (uint32_t j = i; j > 0 && sp.q[order[j]] < sp.q[order[j - 1]]; --j) {
+                const uint32_t t = order[j]; order[j] = order[j - 1]; order[j - 1] = t;
+            }
+        for (uint32_t i = 0; i < sp.n_q; ++i) {
+            P.q[i] = sp.q[order[i]];
+            P.q_row[i] = order[i];
+        }
+    }
     P.vals = static_cast<const uint8_t*>(h->vals.p);
     P.desc = static_cast<const uint4*>(h->desc.p);
     P.big_list = h->big_list;
-    P.mid_list = h->mid_list;
+    P.wide_list = h->wide_list;
     P.ctl = h->ctl;
     P.big_cap = h->big_cap;
-    P.mid_cap = h->mid_cap;
+    P.wide_cap = h->wide_cap;
     cudaStream_t st = h->compute;
     if (cells) {
         launch(h, KGS_K_FINALIZE, st, [&] {
-            k_finalize_tiny<<<(cells + TinyLayout::NT - 1) / TinyLayout::NT, TinyLayout::NT, 0, st>>>(P);
+            k_finalize_cells<<<(cells + CellLayout::NT - 1) / CellLayout::NT, CellLayout::NT, 0, st>>>(P);
         });
-        if (sp.n_q) {   // cells above 255 samples or with values >= 128
-            const int mid_grid = grid_for(cells, MidLayout::NT, 148 * 6);
-            launch(h, KGS_K_FINALIZE_MID, st, [&] { k_finalize_mid<<<mid_grid, MidLayout::NT, 0, st>>>(P); });
+        if (sp.n_q) {   // cells with values >= 128 (and, through the big list, above 65 535 samples)
+            const int wide_grid = grid_for(cells, WideLayout::NT, 148 * 6);
+            launch(h, KGS_K_FINALIZE_WIDE, st, [&] { k_finalize_wide<<<wide_grid, WideLayout::NT, 0, st>>>(P); });
         }
         if (sp.n_q && h->accumulated * h->W > kSmallMax) {
             launch(h, KGS_K_FINALIZE_BIG, st, [&] { k_finalize_big<<<148, 128, 0, st>>>(P); });
