@@ -41,7 +41,6 @@ struct FinParams {
     double q[8];
     const uint8_t* vals;
     const uint4* desc;
-    uint32_t q_row[8];                   // q[] is ascending; q_row[i] = the caller's index of q[i]
     uint32_t* wide_list;                 // pairs (kind slot, cell) left to k_finalize_wide
     uint32_t* big_list;                  // pairs left to k_finalize_big
     uint32_t* ctl;                       // ctl[2] = big_list length, ctl[3] = wide_list length
@@ -67,100 +66,159 @@ __device__ __forceinline__ double pct_lerp(uint32_t vlo, uint32_t vhi, double w)
 
 // ---- private histogram layouts -----------------------------------------------------------------
 // u16 bins, two per 32-bit word; word index = (bin >> 1) * NT + tid, so every access of thread
-// tid falls on bank tid % 32 whatever the bin.
+// tid falls on bank tid % 32 whatever the bin.  All accesses go through explicit shared-space
+// PTX with 32-bit addresses; `base` = shared address of the thread's word 0.
+__device__ __forceinline__ uint32_t lds_u16(uint32_t a) {
+    unsigned short v;
+    asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(a) : "memory");
+    return v;
+}
+__device__ __forceinline__ void sts_u16(uint32_t a, uint32_t v) {
+    asm volatile("st.shared.u16 [%0], %1;" ::"r"(a), "h"((unsigned short)v) : "memory");
+}
+__device__ __forceinline__ uint32_t lds_u32(uint32_t a) {
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a) : "memory");
+    return v;
+}
+__device__ __forceinline__ void sts_u32(uint32_t a, uint32_t v) {
+    asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory");
+}
+
 template <int NT_, int BINS_>
 struct Layout16 {
     static constexpr int NT = NT_, BINS = BINS_, WORDS = BINS_ / 2;
-    static __device__ __forceinline__ void inc(unsigned char* hb, uint32_t tid4, uint32_t bin) {
-        *reinterpret_cast<unsigned short*>(hb + ((bin >> 1) * (NT * 4)) + tid4 + ((bin & 1u) << 1)) += 1;
+    static constexpr int ROW = NT_ * 4;             // bytes between consecutive words of one thread
+    static __device__ __forceinline__ uint32_t addr(uint32_t base, uint32_t bin) {
+        return base + (bin >> 1) * ROW + ((bin & 1u) << 1);
+    }
+    // Two increments at once.  The loads are issued together so the two read-modify-write chains
+    // overlap; when both bytes hit the same bin the second store carries both increments.
+    static __device__ __forceinline__ void inc2(uint32_t base, uint32_t bin_a, uint32_t bin_b, uint32_t da, uint32_t db) {
+        const uint32_t aa = addr(base, bin_a), ab = addr(base, bin_b);
+        uint32_t va = lds_u16(aa), vb = lds_u16(ab);
+        va += da;
+        vb = (aa == ab) ? va : vb;
+        vb += db;
+        sts_u16(aa, va);
+        sts_u16(ab, vb);
     }
 };
 using CellLayout = Layout16<128, 128>;   // values 0..127: 256 B per thread, 32 KB per CTA of 128 threads
 using WideLayout = Layout16<64, 256>;    // values 0..255: 512 B per thread, 32 KB per CTA of 64 threads
 
-// Count the bytes of x selected by `mask` (bit k = byte k) into the thread's histogram.
+// Count the bytes of x selected by `mask` (bit k = byte k) into the thread's histogram.  Masked
+// bytes are counted with an increment of 0 rather than skipped: no branches, no divergence.
 template <class L, bool MASKED>
-__device__ __forceinline__ void add16(unsigned char* hb, uint32_t tid4, const uint4& x, uint32_t mask) {
+__device__ __forceinline__ void add16(uint32_t base, const uint4& x, uint32_t mask) {
     const uint32_t w[4] = {x.x, x.y, x.z, x.w};
 #pragma unroll
-    for (int k = 0; k < 16; ++k) {
-        if (!MASKED || (mask & (1u << k))) L::inc(hb, tid4, (w[k >> 2] >> (8 * (k & 3))) & 0xFFu);
+    for (int k = 0; k < 16; k += 2) {
+        uint32_t ba = (w[k >> 2] >> (8 * (k & 3))) & 0xFFu;
+        uint32_t bb = (w[k >> 2] >> (8 * ((k + 1) & 3))) & 0xFFu;
+        const uint32_t da = MASKED ? ((mask >> k) & 1u) : 1u, db = MASKED ? ((mask >> (k + 1)) & 1u) : 1u;
+        if (MASKED) {   // bytes outside the run may hold any value: keep their (+0) access inside the table
+            ba *= da;
+            bb *= db;
+        }
+        L::inc2(base, ba, bb, da, db);
     }
 }
 
-// Count the bytes vals[start, start+len) into the thread's histogram, 16 aligned bytes per load.
+// Count the W pane lists of this thread's window cell into its histogram.  WARP-SYNCHRONOUS: all
+// 32 lanes call it together (lanes without a cell pass valid = false) and step through runs and
+// 16-byte blocks in lockstep, so the warp always executes ONE of the two block bodies: the
+// unmasked one when every lane has a whole block, the arithmetic-masked one otherwise.
 template <class L>
-__device__ __forceinline__ void add_run(unsigned char* hb, uint32_t tid4, const uint8_t* __restrict__ vals,
-                                        uint32_t start, uint32_t len) {
-    const uint32_t end = start + len;
-    uint32_t blk = start & ~15u;
-    uint4 x = __ldg(reinterpret_cast<const uint4*>(vals + blk));
-    while (true) {
-        const uint32_t lo = max(start, blk) - blk, hi = min(end, blk + 16) - blk;
-        const bool more = blk + 16 < end;
-        uint4 nx = x;
-        if (more) nx = __ldg(reinterpret_cast<const uint4*>(vals + blk + 16));
-        if (hi - lo == 16) add16<L, false>(hb, tid4, x, 0xFFFFu);
-        else add16<L, true>(hb, tid4, x, ((1u << hi) - 1u) & ~((1u << lo) - 1u));
-        if (!more) break;
-        x = nx;
-        blk += 16;
-    }
-}
-
-// Walk the W pane lists of one window cell.
-template <class L>
-__device__ __forceinline__ void add_cell(unsigned char* hb, uint32_t tid4, const FinParams& P, const FinKind& K,
-                                         uint32_t pc0) {
+__device__ __forceinline__ void add_cell(uint32_t base, const FinParams& P, const FinKind& K, uint32_t pc0,
+                                         bool valid) {
+    constexpr uint32_t kAll = 0xFFFFFFFFu;
     for (uint32_t d = 0; d < P.W; ++d) {
-        uint32_t at = K.head[pc0 + d];
-        while (at) {
-            const uint4 r = __ldg(P.desc + (at - 1));
-            add_run<L>(hb, tid4, P.vals, r.x, r.y);
+        uint32_t at = valid ? K.head[pc0 + d] : 0u;
+        while (__any_sync(kAll, at != 0)) {
+            uint4 r = make_uint4(0, 0, 0, 0);
+            if (at) r = __ldg(P.desc + (at - 1));
+            const uint32_t start = r.x, end = r.x + r.y;
+            uint32_t blk = start & ~15u;
+            while (__any_sync(kAll, blk < end)) {
+                uint4 x = make_uint4(0, 0, 0, 0);
+                uint32_t mask = 0;
+                if (blk < end) {
+                    x = __ldg(reinterpret_cast<const uint4*>(P.vals + blk));
+                    const uint32_t lo = max(start, blk) - blk, hi = min(end, blk + 16) - blk;
+                    mask = ((1u << hi) - 1u) & ~((1u << lo) - 1u);
+                }
+                if (__all_sync(kAll, mask == 0xFFFFu)) add16<L, false>(base, x, 0xFFFFu);
+                else add16<L, true>(base, x, mask);
+                blk += 16;
+            }
             at = r.z;
         }
     }
 }
 
-// Select the percentiles from the thread's histogram and store them.  P.q is ascending (the host
-// sorts it; P.q_row maps back to the caller's order), so one forward pass over the words serves
-// every rank: `cum` counts the values below word w.
+// The value of rank `ilo` and of rank `ihi` (ihi = ilo or ilo + 1) among the `count` values of the
+// thread's histogram, whose highest occupied bin is vmax.  Ranks in the lower half are searched
+// upwards from the first occupied bin, ranks in the upper half downwards from vmax.
 template <class L>
-__device__ __forceinline__ void select_store(const uint32_t* hist, uint32_t tid, const FinParams& P,
-                                             const FinKind& K, uint32_t c, uint32_t count) {
-    const uint32_t ncell = K.n_keys * P.n_windows;
-    uint32_t w = 0, cum = 0;
-    uint32_t word = hist[tid];
-    uint32_t ws = (word & 0xFFFFu) + (word >> 16);
-    for (uint32_t iq = 0; iq < P.n_q; ++iq) {
-        uint32_t ilo, ihi;
-        double wt;
-        pct_ranks(P.q[iq], count, ilo, ihi, wt);
-        while (cum + ws <= ilo && w < (uint32_t)L::WORDS - 1) {   // count > ilo ends this inside the table
+__device__ __forceinline__ void select2(uint32_t base, uint32_t count, uint32_t vmax, uint32_t ilo, uint32_t ihi,
+                                        uint32_t& vlo, uint32_t& vhi) {
+    const uint32_t top = base + (uint32_t)(L::WORDS - 1) * L::ROW;
+    uint32_t a, word, le;   // le = number of values <= vlo
+    if (ilo < (count >> 1)) {
+        a = base;
+        while ((word = lds_u32(a)) == 0 && a < top) a += L::ROW;
+        uint32_t cum = 0, ws = (word & 0xFFFFu) + (word >> 16);
+        while (cum + ws <= ilo && a < top) {
             cum += ws;
-            ++w;
-            word = hist[w * L::NT + tid];
+            a += L::ROW;
+            word = lds_u32(a);
             ws = (word & 0xFFFFu) + (word >> 16);
         }
-        const uint32_t c0 = word & 0xFFFFu;
-        const bool in_lo = ilo - cum < c0;                 // cum <= ilo < cum + c0
-        const uint32_t vlo = 2 * w + (in_lo ? 0u : 1u);
-        const uint32_t bin_end = in_lo ? cum + c0 : cum + ws;   // ranks below bin_end share vlo's value
-        uint32_t vhi = vlo;
-        if (ihi >= bin_end) {                              // the next occupied bin
-            if (in_lo && (word >> 16)) {
-                vhi = vlo + 1;
-            } else {
-                uint32_t w2 = w;
-                uint32_t word2;
-                do {
-                    ++w2;
-                    word2 = hist[w2 * L::NT + tid];
-                } while (!word2 && w2 < (uint32_t)L::WORDS - 1);
-                vhi = 2 * w2 + ((word2 & 0xFFFFu) ? 0u : 1u);
-            }
+        const bool in_lo = ilo - cum < (word & 0xFFFFu);
+        vlo = 2 * ((a - base) / L::ROW) + (in_lo ? 0u : 1u);
+        le = in_lo ? cum + (word & 0xFFFFu) : cum + ws;
+    } else {
+        const uint32_t u = count - 1 - ilo;   // rank counted from the top
+        a = base + (vmax >> 1) * L::ROW;
+        word = lds_u32(a);
+        uint32_t cum = 0, ws = (word & 0xFFFFu) + (word >> 16);
+        while (cum + ws <= u && a > base) {
+            cum += ws;
+            a -= L::ROW;
+            word = lds_u32(a);
+            ws = (word & 0xFFFFu) + (word >> 16);
         }
-        K.o_pct[(size_t)P.q_row[iq] * ncell + c] = pct_lerp(vlo, vhi, wt);
+        const bool in_hi = u - cum < (word >> 16);
+        vlo = 2 * ((a - base) / L::ROW) + (in_hi ? 1u : 0u);
+        le = count - (in_hi ? cum : cum + (word >> 16));
+    }
+    vhi = vlo;
+    if (ihi >= le) {   // the next occupied bin above vlo
+        if (!(vlo & 1u) && (word >> 16)) {
+            vhi = vlo + 1;
+        } else {
+            uint32_t word2;
+            do {
+                a += L::ROW;
+                word2 = lds_u32(a);
+            } while (!word2 && a < top);
+            vhi = 2 * ((a - base) / L::ROW) + ((word2 & 0xFFFFu) ? 0u : 1u);
+        }
+    }
+}
+
+// Rule R5 for every requested percentile of one cell.
+template <class L>
+__device__ __forceinline__ void select_store(uint32_t base, const FinParams& P, const FinKind& K, uint32_t c,
+                                             uint32_t count, uint32_t vmax) {
+    const uint32_t ncell = K.n_keys * P.n_windows;
+    for (uint32_t iq = 0; iq < P.n_q; ++iq) {
+        uint32_t ilo, ihi, vlo, vhi;
+        double wt;
+        pct_ranks(P.q[iq], count, ilo, ihi, wt);
+        select2<L>(base, count, vmax, ilo, ihi, vlo, vhi);
+        K.o_pct[(size_t)iq * ncell + c] = pct_lerp(vlo, vhi, wt);
     }
 }
 
@@ -178,6 +236,13 @@ __global__ void __launch_bounds__(CellLayout::NT) k_finalize_cells(const __grid_
     using L = CellLayout;
     __shared__ uint32_t hist[L::WORDS * L::NT];
     const uint32_t tid = threadIdx.x;
+    if (P.n_q) {   // clear the CTA's histograms together (16 STS.128 per thread)
+        uint4* z = reinterpret_cast<uint4*>(hist);
+#pragma unroll
+        for (int i = 0; i < L::WORDS / 4; ++i) z[i * L::NT + tid] = make_uint4(0, 0, 0, 0);
+        __syncthreads();
+    }
+    const uint32_t base = (uint32_t)__cvta_generic_to_shared(hist) + tid * 4;
     const uint32_t idx = blockIdx.x * L::NT + tid;
     const bool live = idx < P.total_cells;
     const uint32_t gc = live ? P.total_cells - 1 - idx : 0;
@@ -222,11 +287,8 @@ __global__ void __launch_bounds__(CellLayout::NT) k_finalize_cells(const __grid_
         const uint32_t ncell = K.n_keys * P.n_windows;
         for (uint32_t iq = 0; iq < P.n_q; ++iq) K.o_pct[(size_t)iq * ncell + c] = nan_f64();
     }
-    if (!fast) return;
-    const uint32_t nw = (vmax >> 1) + 1;
-    for (uint32_t w = 0; w < nw; ++w) hist[w * L::NT + tid] = 0;
-    add_cell<L>(reinterpret_cast<unsigned char*>(hist), tid * 4, P, K, pc0);
-    select_store<L>(hist, tid, P, K, c, (uint32_t)count);
+    add_cell<L>(base, P, K, pc0, fast);   // warp-synchronous: every lane takes part
+    if (fast) select_store<L>(base, P, K, c, (uint32_t)count, vmax);
 }
 
 // The wide list: values up to 255 (u16 bins, 256 values); cells above 65 535 samples move on to
@@ -237,27 +299,36 @@ __global__ void __launch_bounds__(WideLayout::NT) k_finalize_wide(const __grid_c
     const uint32_t tid = threadIdx.x;
     const uint32_t n_wide = P.ctl[1] ? 0u : min(P.ctl[3], P.wide_cap);
     if (blockIdx.x * L::NT >= n_wide) return;
-    for (uint32_t w = 0; w < L::WORDS; ++w) hist[w * L::NT + tid] = 0;
-    for (uint32_t it = blockIdx.x * L::NT + tid; it < n_wide; it += gridDim.x * L::NT) {
-        const uint32_t ks = P.wide_list[2 * it];
-        const uint32_t c = P.wide_list[2 * it + 1];
-        const FinKind& K = P.kind[ks];
-        const unsigned long long count = K.o_count[c];
-        if (count > kSmallMax) {
-            const uint32_t at = atomicAdd(P.ctl + 2, 1u);
-            if (at < P.big_cap) {
-                P.big_list[2 * at] = ks;
-                P.big_list[2 * at + 1] = c;
+    const uint32_t base = (uint32_t)__cvta_generic_to_shared(hist) + tid * 4;
+    for (uint32_t a = base; a < base + L::WORDS * L::ROW; a += L::ROW) sts_u32(a, 0);
+    for (uint32_t it0 = blockIdx.x * L::NT; it0 < n_wide; it0 += gridDim.x * L::NT) {   // CTA-uniform trips
+        const uint32_t it = it0 + tid;
+        bool valid = it < n_wide;
+        uint32_t ks = 0, c = 0, vmax = 0, pc0 = 0;
+        unsigned long long count = 0;
+        if (valid) {
+            ks = P.wide_list[2 * it];
+            c = P.wide_list[2 * it + 1];
+            count = P.kind[ks].o_count[c];
+            if (count > kSmallMax) {
+                const uint32_t at = atomicAdd(P.ctl + 2, 1u);
+                if (at < P.big_cap) {
+                    P.big_list[2 * at] = ks;
+                    P.big_list[2 * at + 1] = c;
+                }
+                valid = false;
             }
-            continue;
         }
-        const uint32_t vmax = K.o_max[c];
-        const uint32_t key = c / P.n_windows;
-        const uint32_t pc0 = key * P.n_panes + (c - key * P.n_windows);
-        add_cell<L>(reinterpret_cast<unsigned char*>(hist), tid * 4, P, K, pc0);
-        select_store<L>(hist, tid, P, K, c, (uint32_t)count);
-        const uint32_t nw = (vmax >> 1) + 1;   // leave the histogram clean for the next cell
-        for (uint32_t w = 0; w < nw; ++w) hist[w * L::NT + tid] = 0;
+        const FinKind& K = P.kind[ks];
+        if (valid) {
+            vmax = K.o_max[c];
+            const uint32_t key = c / P.n_windows;
+            pc0 = key * P.n_panes + (c - key * P.n_windows);
+        }
+        add_cell<L>(base, P, K, pc0, valid);
+        if (valid) select_store<L>(base, P, K, c, (uint32_t)count, vmax);
+        // leave the histogram clean for the next cell (idle lanes only ever add 0 to bin 0)
+        for (uint32_t a = base; a <= base + (vmax >> 1) * L::ROW; a += L::ROW) sts_u32(a, 0);
     }
 }
 
@@ -300,7 +371,7 @@ __global__ void __launch_bounds__(128) k_finalize_big(const __grid_constant__ Fi
                     if (ihi - cum < cb) vhi = b;
                     cum += cb;
                 }
-                K.o_pct[(size_t)P.q_row[iq] * ncell + c] = pct_lerp(vlo, vhi, w);
+                K.o_pct[(size_t)iq * ncell + c] = pct_lerp(vlo, vhi, w);
             }
         }
         __syncwarp();

@@ -8,8 +8,6 @@
 
 #include "../../include/kgs.h"
 
-namespace kgs { constexpr int KGS_MAX_Q_ = KGS_MAX_Q; }
-
 #include "accum.cuh"
 #include "common.cuh"
 #include "finalize.cuh"
@@ -561,18 +559,7 @@ int kgs_stats_finalize(kgs_handle h) {
     P.n_panes = h->n_panes;
     P.W = h->W;
     P.n_q = sp.n_q;
-    {   // ascending percentiles for the one-pass selection; q_row restores the caller's order
-        uint32_t order[KGS_MAX_Q];
-        for (uint32_t i = 0; i < sp.n_q; ++i) order[i] = i;
-        for (uint32_t i = 1; i < sp.n_q; ++i)
-            for (uint32_t j = i; j > 0 && sp.q[order[j]] < sp.q[order[j - 1]]; --j) {
-                const uint32_t t = order[j]; order[j] = order[j - 1]; order[j - 1] = t;
-            }
-        for (uint32_t i = 0; i < sp.n_q; ++i) {
-            P.q[i] = sp.q[order[i]];
-            P.q_row[i] = order[i];
-        }
-    }
+    for (uint32_t i = 0; i < sp.n_q; ++i) P.q[i] = sp.q[i];
     P.vals = static_cast<const uint8_t*>(h->vals.p);
     P.desc = static_cast<const uint4*>(h->desc.p);
     P.big_list = h->big_list;
