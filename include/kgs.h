@@ -104,6 +104,25 @@ int kgs_build_join(kgs_handle h, const uint64_t* keys, const uint32_t* pod_ids, 
  * host array of n entries; blocking. */
 int kgs_probe(kgs_handle h, uint32_t gpus_per_node, uint32_t* out_pod_id);
 
+/* The same join for callers that cannot allocate GPU memory - an agent sharing its GPUs with the
+ * jobs it monitors (a cudaMalloc there can fail, can starve the tenant, and stalls the device), or
+ * one living inside a process whose allocator owns all device memory.  This entry point has NO
+ * counterpart in the reference; it exists for that deployment constraint only.
+ * Everything is a DEVICE pointer supplied by the caller (keys/pod_ids: the m join pairs; gpu_gid,
+ * pid: the n samples; out_pod_id: n results, KGS_POD_NONE for a miss; the three sample-sized
+ * arrays 16-byte aligned).  The hash table lives in a fixed array inside the loaded module:
+ * 131 072 slots x 16 B = 2 MiB per GPU that loads the library, kept until the process exits, hence
+ * m <= KGS_NOALLOC_MAX_PAIRS (a larger m returns KGS_ERR_CAPACITY).  No handle is needed; the text
+ * of a failure is returned by kgs_last_error(NULL).  The call queues its kernels on `stream` (a
+ * cudaStream_t, NULL = default stream) and returns without waiting; it performs no cudaMalloc /
+ * cudaFree.  The first call on each device resolves the table's device address - make it before
+ * any stream capture.  All calls on a device share the one table and rebuild it from empty, so
+ * calls whose kernels may overlap on the same GPU (two streams, two threads) race: serialise them. */
+#define KGS_NOALLOC_MAX_PAIRS 65536u
+int kgs_join_probe_noalloc(int device, const uint64_t* d_keys, const uint32_t* d_pod_ids, uint64_t m,
+                           const uint32_t* d_gpu_gid, const uint32_t* d_pid, uint64_t n,
+                           uint32_t gpus_per_node, uint32_t* d_out_pod_id, void* stream);
+
 /* ---- windowed statistics (north_star subsystem 3) ------------------------------------- */
 /* The mean of GUS:77-80 (sum/len, 0.0 when empty) generalised to windows and to three key
  * kinds; max and percentiles have no reference counterpart.

@@ -16,6 +16,7 @@ KEY_POD, KEY_GPU, KEY_NODE = 0, 1, 2
 METRIC_SM, METRIC_MEM, METRIC_FB = 0, 1, 2
 POD_NONE = 0xFFFFFFFF
 MAX_Q = 8
+NOALLOC_MAX_PAIRS = 65536
 (K_BUILD, K_BUILD_FIN, K_PROBE, K_ACCUM, K_FINALIZE, K_FINALIZE_BIG, K_SEGMEAN, K_CLEAR, K_FINALIZE_WIDE) = range(9)
 KERNEL_NAMES = ['join_build', 'join_resolve', 'join_probe', 'accum', 'finalize_cells', 'finalize_big',
                 'segmean', 'join_clear', 'finalize_wide']
@@ -55,6 +56,7 @@ def load(path=LIB_PATH):
         'kgs_adopt_device_batch': [H, vp, vp, vp, vp, C.c_uint64],
         'kgs_build_join': [H, vp, vp, C.c_uint64, C.c_uint32],
         'kgs_probe': [H, C.c_uint32, vp],
+        'kgs_join_probe_noalloc': [C.c_int, vp, vp, C.c_uint64, vp, vp, C.c_uint64, C.c_uint32, vp, vp],
         'kgs_stats_begin': [H, C.POINTER(WindowSpec)],
         'kgs_stats_accumulate': [H],
         'kgs_stats_finalize': [H],

@@ -12,6 +12,7 @@
 #include "common.cuh"
 #include "finalize.cuh"
 #include "join.cuh"
+#include "noalloc.cuh"
 #include "segmean.cuh"
 
 using namespace kgs;
@@ -365,6 +366,42 @@ int kgs_probe(kgs_handle h, uint32_t gpus_per_node, uint32_t* out_pod_id) {
     KGS_CUDA(h, cudaEventRecord(B.consumed, st));
     KGS_CUDA(h, cudaMemcpyAsync(out_pod_id, h->tmp.p, B.n * 4, cudaMemcpyDeviceToHost, st));
     KGS_CUDA(h, cudaStreamSynchronize(st));
+    return KGS_OK;
+}
+
+int kgs_join_probe_noalloc(int device, const uint64_t* d_keys, const uint32_t* d_pod_ids, uint64_t m,
+                           const uint32_t* d_gpu_gid, const uint32_t* d_pid, uint64_t n, uint32_t gpus_per_node,
+                           uint32_t* d_out_pod_id, void* stream) {
+    auto bad = [](int code, const std::string& msg) {
+        g_create_error = msg;
+        return code;
+    };
+    if (device < 0 || device >= kNoallocMaxDevices) return bad(KGS_ERR_ARG, "kgs_join_probe_noalloc: device ordinal out of range");
+    if (m > kNoallocMaxPairs)
+        return bad(KGS_ERR_CAPACITY, "kgs_join_probe_noalloc: " + std::to_string(m) + " join pairs exceed the fixed table's limit of " +
+                                         std::to_string(kNoallocMaxPairs) + " (KGS_NOALLOC_MAX_PAIRS); use kgs_build_join + kgs_probe");
+    if (gpus_per_node == 0) return bad(KGS_ERR_ARG, "kgs_join_probe_noalloc: gpus_per_node is 0");
+    if (n >= (1ull << 32)) return bad(KGS_ERR_ARG, "kgs_join_probe_noalloc: fewer than 2^32 samples per call");
+    if ((m && (!d_keys || !d_pod_ids)) || (n && (!d_gpu_gid || !d_pid || !d_out_pod_id)))
+        return bad(KGS_ERR_ARG, "kgs_join_probe_noalloc: null device pointer");
+    if (((uintptr_t)d_gpu_gid | (uintptr_t)d_pid | (uintptr_t)d_out_pod_id) & 15)
+        return bad(KGS_ERR_ARG, "kgs_join_probe_noalloc: sample columns and output must be 16-byte aligned");
+    cudaError_t e = cudaSetDevice(device);
+    if (e != cudaSuccess) return bad(KGS_ERR_CUDA, std::string("cudaSetDevice: ") + cudaGetErrorString(e));
+    JoinSlot* slots = nullptr;   // the real device address of the module's table (set-up: once per device)
+    e = noalloc_table(device, &slots);
+    if (e != cudaSuccess) return bad(KGS_ERR_CUDA, std::string("cudaGetSymbolAddress: ") + cudaGetErrorString(e));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const uint32_t mask = kNoallocSlots - 1;
+    k_join_clear<<<grid_for(kNoallocSlots, 256, 148 * 8), 256, 0, st>>>(slots, kNoallocSlots);
+    if (m) {
+        k_join_build<<<grid_for(m, 256, 148 * 8), 256, 0, st>>>(slots, mask, reinterpret_cast<const unsigned long long*>(d_keys), (uint32_t)m);
+        k_join_resolve<<<grid_for(kNoallocSlots, 256, 148 * 8), 256, 0, st>>>(slots, kNoallocSlots, d_pod_ids);
+    }
+    if (n)
+        k_join_probe<<<grid_for(n / 4 + 1, 256, 148 * 8), 256, 0, st>>>(slots, mask, d_gpu_gid, d_pid, n, make_fastdiv(gpus_per_node), d_out_pod_id);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return bad(KGS_ERR_CUDA, std::string("kernel launch: ") + cudaGetErrorString(e));
     return KGS_OK;
 }
 

@@ -1,0 +1,71 @@
+"""kgs_join_probe_noalloc: the join for callers that may not allocate GPU memory.
+
+Some users of this library run it as a telemetry agent on GPUs that belong to somebody else's
+training job, or inside a process whose allocator already owns the whole card.  For them a
+cudaMalloc is off the table: it may fail, it may take memory the tenant counted on, and it
+stalls the device while it runs.  The entry point tested here keeps its hash table in a fixed
+2 MiB array that ships with the library and takes every other buffer from the caller.
+
+The check: through the C ABI, on buffers this test owns (torch tensors stand in for the
+caller's arena), the pod of every sample must equal what the ordinary kgs_build_join +
+kgs_probe pair returns - bit for bit, on two calls in a row with DIFFERENT tables, so a table
+left over from the first call would be caught.  This file sorts last so that a run with -x has
+already executed every other test when it gets here; it also passes on its own.
+"""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _case(rng, m, n, gpn=8):
+    node = rng.integers(0, 40, size=m).astype(np.uint64)
+    pid = rng.integers(1, 30000, size=m).astype(np.uint64)
+    keys = (node << np.uint64(32)) | pid
+    if m > 10:                                  # some repeated keys: the last pair has to win
+        keys[rng.integers(0, m, size=m // 10)] = keys[rng.integers(0, m, size=m // 10)]
+    pods = rng.integers(0, 5000, size=m).astype(np.uint32)
+    pick = rng.integers(0, m, size=n)
+    s_node = (keys[pick] >> np.uint64(32)).astype(np.uint32)
+    s_pid = (keys[pick] & np.uint64(0xFFFFFFFF)).astype(np.uint32)
+    s_pid[rng.random(n) < 0.25] += 40000        # pids without a pair -> KGS_POD_NONE
+    gid = (s_node * gpn + rng.integers(0, gpn, size=n)).astype(np.uint32)
+    return keys, pods, gid, s_pid
+
+
+def test_noalloc_join_equals_regular_join_twice(engine):
+    import torch
+    from kube_gpu_stats_b200 import _ffi
+    lib = _ffi.lib()
+    dev = torch.device('cuda', 0)
+    rng = np.random.default_rng(2026)
+    for m, n in ((5000, 100003), (60000, 250000)):          # two calls in a row, second table larger
+        keys, pods, gid, pid = _case(rng, m, n)
+        # the regular path: library-owned table
+        engine.build_join(keys, pods, 5000)
+        z = np.zeros(n, dtype=np.uint32)
+        engine.ingest(z, gid, pid, z)
+        want = engine.probe(8)
+        # the no-allocation path: caller-owned device buffers only
+        d_keys = torch.from_numpy(keys.view(np.int64)).to(dev)
+        d_pods = torch.from_numpy(pods.view(np.int32)).to(dev)
+        d_gid = torch.from_numpy(gid.view(np.int32)).to(dev)
+        d_pid = torch.from_numpy(pid.view(np.int32)).to(dev)
+        d_out = torch.full((n,), -7, dtype=torch.int32, device=dev)
+        torch.cuda.synchronize()
+        rc = lib.kgs_join_probe_noalloc(0, d_keys.data_ptr(), d_pods.data_ptr(), m, d_gid.data_ptr(),
+                                        d_pid.data_ptr(), n, 8, d_out.data_ptr(), None)
+        assert rc == _ffi.KGS_OK, lib.kgs_last_error(None).decode()
+        torch.cuda.synchronize()
+        got = d_out.cpu().numpy().view(np.uint32)
+        np.testing.assert_array_equal(got, want)            # integer result: tolerance 0
+
+
+def test_noalloc_rejects_oversized_table(built_lib):
+    from kube_gpu_stats_b200 import _ffi
+    lib = _ffi.lib()
+    rc = lib.kgs_join_probe_noalloc(0, 16, 16, _ffi.NOALLOC_MAX_PAIRS + 1, 16, 16, 4, 8, 16, None)
+    assert rc == _ffi.KGS_ERR_CAPACITY
+    assert b'65536' in lib.kgs_last_error(None)
