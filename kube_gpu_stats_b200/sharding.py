@@ -90,3 +90,50 @@ class TableGather:
             self._src_ptr = ptr
         dist.all_gather_into_tensor(self._dst, self._src)
         return self._dst
+
+
+# ---- host-memory variant of the exchange (any torch.distributed backend, e.g. gloo) -------------
+
+_FIELDS = (('count', np.uint64), ('sum', np.uint64), ('max', np.uint32), ('mean', np.float64), ('pct', np.float64))
+
+
+def pack_tables(table):
+    """One kind's {count,sum,max,mean,pct} -> a single uint8 array (header: n_cells, n_q)."""
+    n_cells = int(np.asarray(table['count']).size)
+    pct = np.asarray(table['pct'], dtype=np.float64).reshape(-1, n_cells) if n_cells else np.zeros((0, 0))
+    head = np.array([n_cells, pct.shape[0]], dtype=np.uint64)
+    parts = [head.view(np.uint8)]
+    for name, dt in _FIELDS:
+        arr = pct if name == 'pct' else np.asarray(table[name], dtype=dt)
+        parts.append(np.ascontiguousarray(arr, dtype=dt).reshape(-1).view(np.uint8))
+    return np.concatenate(parts)
+
+
+def unpack_tables(buf):
+    buf = np.ascontiguousarray(buf, dtype=np.uint8)
+    n_cells, n_q = (int(x) for x in buf[:16].view(np.uint64))
+    out, at = {}, 16
+    for name, dt in _FIELDS:
+        n = n_cells * (n_q if name == 'pct' else 1)
+        nbytes = n * np.dtype(dt).itemsize
+        arr = buf[at:at + nbytes].view(dt).copy()
+        out[name] = arr.reshape(n_q, n_cells) if name == 'pct' else arr
+        at += nbytes
+    return out
+
+
+def all_gather_tables(table):
+    """all_gather of one kind's table over the default process group; shards may differ in size
+    (buffers are padded to the largest).  Returns the list of per-rank tables, rank order."""
+    import torch
+    import torch.distributed as dist
+    world = dist.get_world_size()
+    mine = torch.from_numpy(pack_tables(table))
+    sizes = [torch.zeros(1, dtype=torch.int64) for _ in range(world)]
+    dist.all_gather(sizes, torch.tensor([mine.numel()], dtype=torch.int64))
+    longest = max(int(s) for s in sizes)
+    padded = torch.zeros(longest, dtype=torch.uint8)
+    padded[:mine.numel()] = mine
+    got = [torch.zeros(longest, dtype=torch.uint8) for _ in range(world)]
+    dist.all_gather(got, padded)
+    return [unpack_tables(g[:int(s)].numpy()) for g, s in zip(got, sizes)]

@@ -32,8 +32,9 @@ Q_SM_UTIL = 'avg(container_gpu_sm_util) by (kubernetes_io_hostname, nvidia_gpu_t
 
 
 def naive_sum(xs):
-    """Left-to-right fp64 sum: what Py2 ``sum(list_of_floats)`` does (GUS:51, GUS:78)."""
-    acc = 0.0
+    """Left-to-right fp64 sum: what Py2 ``sum(list_of_floats)`` does (GUS:51, GUS:78).
+    Like ``sum`` it starts from the int 0, so an empty list gives the int 0."""
+    acc = 0
     for x in xs:
         acc += x
     return acc
@@ -137,7 +138,14 @@ def server_weighted_means(json_result, time_range_sec, step_sec):
     last_vals = {}
     for series in json_result['data']['result']:
         last_vals[series['metric']['kubernetes_io_hostname']] = decode_series(series)
-    return {server: naive_sum(vals) * step_sec / time_range_sec for server, vals in last_vals.items()}
+    out = {}
+    for server, vals in last_vals.items():
+        total = naive_sum(vals)
+        if isinstance(total, int) and isinstance(step_sec, int) and isinstance(time_range_sec, int):
+            out[server] = total * step_sec // time_range_sec      # Py2 int / int (only the empty series: 0)
+        else:
+            out[server] = total * step_sec / time_range_sec
+    return out
 
 
 def stats_server_results(json_result, time_range_sec, step_sec, fetch):

@@ -1,0 +1,114 @@
+"""CPU: the host half of the drop-in modules - function surface, transport seam, stdout formats -
+against the hand-written golden vectors and the oracle."""
+import inspect
+import io
+import json
+import os
+from contextlib import redirect_stdout
+from datetime import datetime
+
+import pytest
+
+from kube_gpu_stats_b200 import gpu_util_stats as gus
+from kube_gpu_stats_b200 import py2fmt, replay, synth
+from kube_gpu_stats_b200 import who_use_gpu as wug
+from oracle import ref_who_use_gpu as ref_wug
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), 'golden')
+
+
+def load(name):
+    with open(os.path.join(GOLDEN, name)) as f:
+        return json.load(f)
+
+
+@pytest.fixture()
+def golden_transport():
+    g = load('ref_rules_gus.json')
+    log = []
+    gus.set_transport(replay.transport(g['answers'], log))
+    yield g, log
+    gus.set_transport(None)
+
+
+def test_reference_function_surface():
+    """Names and arity of the reference."""
+    sig = lambda f: list(inspect.signature(f).parameters)   # noqa: E731
+    assert sig(gus.query_prom) == ['query', 'start_time', 'end_time', 'step_sec']
+    assert sig(gus.query_prom_instant) == ['query']
+    assert sig(gus.stats_server_results) == ['json_result', 'time_range_sec', 'step_sec']
+    assert sig(gus.stats_pod_results) == ['json_result', 'start_time', 'end_time']
+    assert sig(gus.get_gpu_servers) == [] and sig(gus.get_pod_by_servers) == ['start_time', 'end_time']
+    assert sig(gus.main) == [] and sig(wug.main) == []
+    assert sig(wug.checkPod) == ['pod_info'] and sig(wug.getGPUType) == ['pod_info']
+    assert gus.prom_base_url == 'http://prometheus.ke-xs-sys.qiniu.io/api/v1'
+    assert gus.proxies == {'http': 'http://10.34.33.80'}
+
+
+def test_inventory_and_requests_match_golden(golden_transport):
+    g, log = golden_transport
+    inv = gus.get_gpu_servers()
+    assert {k: list(v) for k, v in inv.items()} == g['expect']['get_gpu_servers']['value']
+    buf = io.StringIO()
+    with redirect_stdout(buf):
+        table = gus.get_pod_by_servers(datetime(2023, 11, 14), datetime(2023, 11, 15))
+    assert table == g['expect']['get_pod_by_servers']['value']
+    assert buf.getvalue() == g['expect']['get_pod_by_servers']['dump'] + '\n'        # GUS:150
+    # transport details of the reference: timeout 5 everywhere, proxies except on the instant query
+    assert all(t == 5 for _, _, t, _ in log)
+    by_kind = {replay.classify(p): (u, p, px) for u, p, _, px in log}
+    assert by_kind['live_pods'][2] is None and by_kind['total_cards'][2] == gus.proxies
+    assert by_kind['pod_requests'][0].endswith('/query_range') and by_kind['pod_requests'][1]['step'] == 3600
+    assert by_kind['pod_requests'][1]['end'] - by_kind['pod_requests'][1]['start'] == 86400
+
+
+def test_py2_formats():
+    assert py2fmt.py2_repr(['node-1', 'pod-a', '4', 37.5]) == "[u'node-1', u'pod-a', u'4', 37.5]"
+    assert py2fmt.py2_repr(['n', '', 0, 0, '8']) == "[u'n', u'', 0, 0, u'8']"
+    assert py2fmt.py2_json_dump({'a': {'b': '1', 'c': '2'}}) == '{\n  "a": {\n    "b": "1", \n    "c": "2"\n  }\n}'
+    assert py2fmt.py2_json_dump({}) == '{}'
+
+
+def test_who_use_gpu_matches_golden(tmp_path, monkeypatch):
+    g = load('ref_rules_wug.json')
+    path = tmp_path / 'pods.json'
+    path.write_text(json.dumps(g['pods']))
+    monkeypatch.setenv('KGS_KUBECTL_JSON', str(path))
+    buf = io.StringIO()
+    with redirect_stdout(buf):
+        wug.main()
+    assert buf.getvalue() == g['expect']['stdout']
+    with redirect_stdout(io.StringIO()):
+        rows = [wug.checkPod(p) for p in g['pods']['items']]
+    assert [r for r in rows if r] == g['expect']['rows']
+    assert wug.getGPUType({}) == '<unspecified>'
+
+
+def test_who_use_gpu_equals_oracle_on_synthetic_cluster(tmp_path, monkeypatch):
+    tr = synth.config(2, scale=0.005)
+    pods = replay.kubectl_pods(tr)
+    pods['items'][3]['spec'].pop('nodeName')                       # an unscheduled pod
+    pods['items'][5]['spec']['containers'][0]['resources']['limits'] = {}
+    path = tmp_path / 'pods.json'
+    path.write_text(json.dumps(pods))
+    monkeypatch.setenv('KGS_KUBECTL_JSON', str(path))
+    buf = io.StringIO()
+    with redirect_stdout(buf):
+        wug.main()
+    assert buf.getvalue() == ref_wug.main_text(pods)
+
+
+def test_join_pairs_from_identity_rows():
+    rows = [['ava', 'node-a', 'train-1', 'P40', 3], ['ava', 'node-b', 'infer-2', '<unspecified>', 1]]
+    owner = [('node-a', 100, 'ava', 'train-1'), ('node-a', 101, 'ava', 'train-1'), ('node-b', 100, 'ava', 'infer-2'),
+             ('node-b', 7, 'default', 'web'), ('node-q', 9, 'ava', 'train-1')]
+    keys, pods, n = wug.join_pairs(rows, {'node-a': 0, 'node-b': 1}, owner)
+    assert keys.tolist() == [100, 101, (1 << 32) | 100] and pods.tolist() == [0, 0, 1] and n == 2
+
+
+def test_replay_dir_round_trip(tmp_path, monkeypatch):
+    g = load('ref_rules_gus.json')
+    replay.write_replay_dir(g['answers'], str(tmp_path), None, None)
+    monkeypatch.setenv('KGS_REPLAY_DIR', str(tmp_path))
+    gus.set_transport(None)
+    assert {k: list(v) for k, v in gus.get_gpu_servers().items()} == g['expect']['get_gpu_servers']['value']
