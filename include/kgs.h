@@ -86,8 +86,8 @@ int kgs_free_pinned(kgs_handle h, void* p);
  * so the copy of batch i+1 overlaps the kernels still reading batch i. */
 int kgs_ingest(kgs_handle h, const uint32_t* ts, const uint32_t* gpu_gid, const uint32_t* pid,
                const uint32_t* util, uint64_t n);
-/* Same, for columns that already live in this device's memory (no copy is made; the caller
- * keeps them alive and unchanged until the work that reads them has been synchronised). */
+/* Same, for columns that already live in this device's memory, 32-byte aligned (no copy is made;
+ * the caller keeps them alive and unchanged until the work that reads them has been synchronised). */
 int kgs_adopt_device_batch(kgs_handle h, const uint32_t* d_ts, const uint32_t* d_gpu_gid,
                            const uint32_t* d_pid, const uint32_t* d_util, uint64_t n);
 
@@ -134,8 +134,10 @@ int kgs_stats_accumulate(kgs_handle h);
 int kgs_stats_finalize(kgs_handle h);
 int kgs_window_stats(kgs_handle h, const kgs_window_spec* spec);
 /* Capacity, in entries of 16 B, of the run log the next percentile job allocates (0 = automatic:
- * total_samples_hint / 8 + 65536 per key kind, ample for collector-ordered input).  A job whose
- * input is far from collector order needs up to one entry per sample and key kind. */
+ * total_samples_hint / 8 + 65536 per key kind, ample for collector-ordered input).  Three quarters
+ * of the log are handed out as private slabs per warp, one quarter is a shared overflow pool; with a
+ * capacity set here the slabs are sized for the worst case (every sample its own run), which needs
+ * entries >= 2 * samples * key kinds (rounded up per 256-sample tile). */
 int kgs_set_run_log_capacity(kgs_handle h, uint64_t entries);
 /* Copy one key kind's result table to host arrays of n_keys * n_windows entries, cell index
  * key * n_windows + window (pct: n_q rows of that length).  Any pointer may be NULL. Blocking. */

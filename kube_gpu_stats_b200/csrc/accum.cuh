@@ -4,14 +4,18 @@
 //
 // Takes over the per-sample loop of the reference (gpu_util_stats.py:72-78: decode, append,
 // sum/len) and the dict probes of its join (gpu_util_stats.py:86-91).  Design:
-//   * a warp owns a contiguous chunk of 128-sample tiles and reads each tile with one LDG.128
-//     per column and lane (algorithmic traffic: 16 B/sample, read once); the next tile's loads
-//     are issued before the current tile is processed;
+//   * a warp owns a contiguous chunk of 256-sample tiles; each lane reads EIGHT consecutive
+//     samples per column with one 256-bit load (LDG.E.256, sm_100), so a warp instruction moves
+//     1 KB of one column (algorithmic traffic: 16 B/sample, read once); the next tile's loads are
+//     issued before the current tile is processed;
 //   * consecutive samples that share (gpu_gid, pid, pane) form a RUN; in collector order
-//     (sorted by gpu, then time) runs are tens to thousands of samples long.  Lanes whose four
-//     samples are one run are combined with a segmented warp-shuffle reduction into one run
-//     record per segment; records go to a per-warp queue in shared memory, a run that
-//     continues across a tile boundary is merged into the queued record;
+//     (sorted by gpu, then time) runs are tens to thousands of samples long.  A lane walks its
+//     eight samples sequentially; the usual lane is one piece of one run.  Lanes are chained:
+//     a chain starts at a lane's LAST piece, runs over the following single-piece lanes with the
+//     same key and ends by absorbing the FIRST piece of the next lane that has a boundary inside.
+//     One segmented warp-shuffle reduction per tile (not per sample) sums each chain;
+//   * chains become run records in a per-warp queue in shared memory; a run that continues over
+//     a tile boundary is merged into the queued record;
 //   * when 32 records are queued the warp retires them one per LANE: hash probe, one RED per
 //     statistic and key kind, one run-log descriptor per key kind.  The join and all atomics
 //     therefore cost once per run, executed 32 wide, and the run-log cursor (a single hot
@@ -28,7 +32,9 @@
 namespace kgs {
 
 constexpr int kAccumWarps = 8;          // warps per CTA
-constexpr int kQueueCap = 64;           // run records per warp queue (<= 31 kept + 32 new + 1)
+constexpr int kLaneSamples = 8;         // consecutive samples per lane and tile
+constexpr int kTileSamples = 32 * kLaneSamples;
+constexpr int kQueueCap = 32 + 64;      // <= 32 kept + two records per lane
 constexpr uint32_t kMergeMax = 32768;   // longest merged run (keeps the u32 sum exact for u16 metrics)
 
 struct AccumParams {
@@ -36,9 +42,9 @@ struct AccumParams {
     const uint32_t* gid;
     const uint32_t* pid;
     const uint32_t* util;
-    uint64_t n;              // samples in this batch
-    uint64_t vals_base;      // offset of this batch in the value log (multiple of 16)
+    uint32_t n;              // samples in this batch (< 2^32)
     uint32_t tiles_per_warp;
+    uint64_t vals_base;      // offset of this batch in the value log (multiple of 16)
     const JoinSlot* slots;   // join table (nullptr when the pod kind is off)
     uint32_t tmask;
     uint32_t t0;
@@ -55,7 +61,14 @@ struct AccumParams {
     uint8_t* vals;                 // value log
     uint4* desc;                   // run log
     uint32_t desc_cap;
-    uint32_t* ctl;                 // ctl[0] run-log cursor, ctl[1] overflow flag
+    uint32_t log_base;             // this launch's private run-log slab: warp w owns
+    uint32_t log_per_warp;         //   [log_base + w*log_per_warp, +log_per_warp)
+    uint32_t pool_base;            // shared overflow pool [pool_base, desc_cap), cursor ctl[0]
+    uint32_t* ctl;                 // ctl[0] pool cursor, ctl[1] overflow flag
+};
+
+struct LogCursor {   // warp-uniform position inside the warp's private slab
+    uint32_t at, left;
 };
 
 struct RunQueue {   // structure of arrays: lane l touching record l is conflict free
@@ -94,193 +107,266 @@ __device__ __forceinline__ void emit_run(const AccumParams& P, uint32_t g, uint3
     }
 }
 
-// Reserve `count` run-log entries for the warp with one atomic; returns the first index.
-__device__ __forceinline__ uint32_t reserve_log(const AccumParams& P, uint32_t count, bool& log_ok) {
+// Reserve `count` run-log entries for the warp; returns the first index.  Entries come from the
+// warp's private slab (no atomics, nothing to wait for); a warp that exhausts its slab falls back
+// to the shared pool, whose cursor is a single hot address.
+__device__ __forceinline__ uint32_t reserve_log(const AccumParams& P, LogCursor& lc, uint32_t count, bool& log_ok) {
+    if (count <= lc.left) {
+        const uint32_t base = lc.at;
+        lc.at += count;
+        lc.left -= count;
+        log_ok = true;
+        return base;
+    }
     uint32_t base = 0;
-    if (lane_id() == 0 && count) base = atomicAdd(P.ctl, count);
-    base = __shfl_sync(0xFFFFFFFFu, base, 0);
+    if (lane_id() == 0) base = atomicAdd(P.ctl, count);
+    base = __shfl_sync(0xFFFFFFFFu, base, 0) + P.pool_base;
     log_ok = (uint64_t)base + count <= P.desc_cap;
-    if (!log_ok && lane_id() == 0 && count) P.ctl[1] = 1;
+    if (!log_ok && lane_id() == 0) P.ctl[1] = 1;
     return base;
 }
 
 // Retire records [0, n_flush) of the warp's queue, one record per lane.
 template <bool PCT>
-__device__ __forceinline__ void flush_queue(const AccumParams& P, const RunQueue& q, uint32_t n_flush, uint32_t nk) {
+__device__ __forceinline__ void flush_queue(const AccumParams& P, LogCursor& lc, const RunQueue& q, uint32_t n_flush,
+                                            uint32_t nk) {
     const uint32_t lane = lane_id();
     for (uint32_t base = 0; base < n_flush; base += 32) {
         const uint32_t here = min(32u, n_flush - base);
         bool log_ok = false;
         uint32_t di = 0;
-        if (PCT) di = reserve_log(P, here * nk, log_ok) + lane * nk;
+        if (PCT) di = reserve_log(P, lc, here * nk, log_ok) + lane * nk;
         const uint32_t r = base + lane;
         if (lane < here)
             emit_run<PCT>(P, q.gid[r], q.pid[r], q.pane[r], q.cnt[r], q.sum[r], q.mx[r], q.start[r], di, log_ok);
     }
 }
 
-struct Quad {   // one lane's four consecutive samples
-    uint32_t t[4], g[4], p[4], u[4];
+struct Oct {   // one lane's eight consecutive samples
+    uint32_t t[8], g[8], p[8], u[8];
 };
 
-__device__ __forceinline__ void load_quad(const AccumParams& P, uint64_t i0, Quad& q) {
-    if (i0 + 3 < P.n) {
-        const uint4 a = ld_stream_v4(P.ts + i0), b = ld_stream_v4(P.gid + i0);
-        const uint4 c = ld_stream_v4(P.pid + i0), d = ld_stream_v4(P.util + i0);
-        q.t[0] = a.x; q.t[1] = a.y; q.t[2] = a.z; q.t[3] = a.w;
-        q.g[0] = b.x; q.g[1] = b.y; q.g[2] = b.z; q.g[3] = b.w;
-        q.p[0] = c.x; q.p[1] = c.y; q.p[2] = c.z; q.p[3] = c.w;
-        q.u[0] = d.x; q.u[1] = d.y; q.u[2] = d.z; q.u[3] = d.w;
+__device__ __forceinline__ void ld_stream_v8(const uint32_t* p, uint32_t* r) {
+    asm volatile("ld.global.nc.L1::no_allocate.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+                 : "l"(p));
+}
+
+__device__ __forceinline__ void load_oct(const AccumParams& P, uint32_t i0, bool full, Oct& o) {
+    if (full) {
+        ld_stream_v8(P.ts + i0, o.t);
+        ld_stream_v8(P.gid + i0, o.g);
+        ld_stream_v8(P.pid + i0, o.p);
+        ld_stream_v8(P.util + i0, o.u);
     } else {
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const bool in = i0 + j < P.n;
-            q.t[j] = in ? P.ts[i0 + j] : 0u;
-            q.g[j] = in ? P.gid[i0 + j] : 0u;
-            q.p[j] = in ? P.pid[i0 + j] : 0u;
-            q.u[j] = in ? P.util[i0 + j] : 0u;
+        for (int j = 0; j < 8; ++j) {
+            const bool in = i0 + j < P.n;   // the last tile only; i0 + j stays below 2^32 (n < 2^32 - 256)
+            o.t[j] = in ? P.ts[i0 + j] : 0u;
+            o.g[j] = in ? P.gid[i0 + j] : 0u;
+            o.p[j] = in ? P.pid[i0 + j] : 0u;
+            o.u[j] = in ? P.util[i0 + j] : 0u;
         }
     }
 }
 
-template <bool PCT>
+template <bool PCT, bool PREFETCH>
 __global__ void __launch_bounds__(kAccumWarps * 32) k_accum(const __grid_constant__ AccumParams P) {
     __shared__ RunQueue queues[kAccumWarps];
+    constexpr uint32_t kAll = 0xFFFFFFFFu;
     const uint32_t lane = lane_id();
     RunQueue& Q = queues[threadIdx.x >> 5];
     const uint32_t nk = __popc(P.key_mask);
-    const uint64_t n_tiles = (P.n + 127) >> 7;
-    const uint64_t warp = (uint64_t)blockIdx.x * kAccumWarps + (threadIdx.x >> 5);
-    const uint64_t tile_begin = warp * P.tiles_per_warp;
-    if (tile_begin >= n_tiles) return;
-    const uint64_t tile_end = min(n_tiles, tile_begin + P.tiles_per_warp);
-    uint32_t queued = 0;   // warp-uniform
+    const uint32_t n_tiles = (uint32_t)(((uint64_t)P.n + kTileSamples - 1) / kTileSamples);
+    const uint32_t warp = blockIdx.x * kAccumWarps + (threadIdx.x >> 5);
+    const uint64_t tb = (uint64_t)warp * P.tiles_per_warp;
+    if (tb >= n_tiles) return;
+    const uint32_t tile_begin = (uint32_t)tb;
+    const uint32_t tile_end = (uint32_t)min((uint64_t)n_tiles, tb + P.tiles_per_warp);
+    const uint32_t full_tiles = P.n / kTileSamples;   // tiles below this index are complete
+    uint32_t queued = 0;                               // warp-uniform
+    LogCursor lc{P.log_base + warp * P.log_per_warp, P.log_per_warp};
 
-    Quad cur, nxt;
-    load_quad(P, (tile_begin << 7) + 4 * lane, cur);
-    for (uint64_t tile = tile_begin; tile < tile_end; ++tile) {
-        const uint64_t i0 = (tile << 7) + 4 * lane;
-        if (tile + 1 < tile_end) load_quad(P, i0 + 128, nxt);   // in flight while this tile is processed
-        const bool full = i0 + 3 < P.n;
-        uint32_t pane[4], v[4];
+    Oct cur, nxt;
+    if (PREFETCH) load_oct(P, tile_begin * kTileSamples + 8 * lane, tile_begin < full_tiles, cur);
+    for (uint32_t tile = tile_begin; tile < tile_end; ++tile) {
+        const uint32_t i0 = tile * kTileSamples + 8 * lane;
+        const bool full = tile < full_tiles;
+        if (PREFETCH) {
+            if (tile + 1 < tile_end) load_oct(P, i0 + kTileSamples, tile + 1 < full_tiles, nxt);   // in flight during this tile
+        } else {
+            load_oct(P, i0, full, cur);
+        }
+        uint32_t pane[8], v[8];
+        const uint32_t lim = full ? 8u : (P.n > i0 ? P.n - i0 : 0u);   // samples of this lane inside the batch
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const uint32_t x = cur.t[j] - P.t0;
-            const uint32_t pn = fdiv(x, P.dstep);
-            const bool ok = (cur.t[j] >= P.t0) && (pn < P.n_panes) && (full || i0 + j < P.n);
+        for (int j = 0; j < 8; ++j) {
+            const uint32_t pn = fdiv(cur.t[j] - P.t0, P.dstep);
+            const bool ok = (cur.t[j] >= P.t0) & (pn < P.n_panes) & ((uint32_t)j < lim);
             pane[j] = ok ? pn : kInvalid;
             v[j] = (cur.u[j] >> P.mshift) & P.mmask;
         }
         if (PCT) {   // value log, same order as the input (u8 metrics)
             uint8_t* dst = P.vals + P.vals_base + i0;
             if (full) {
-                *reinterpret_cast<uint32_t*>(dst) = v[0] | (v[1] << 8) | (v[2] << 16) | (v[3] << 24);
+                uint2 w;
+                w.x = v[0] | (v[1] << 8) | (v[2] << 16) | (v[3] << 24);
+                w.y = v[4] | (v[5] << 8) | (v[6] << 16) | (v[7] << 24);
+                *reinterpret_cast<uint2*>(dst) = w;
             } else {
 #pragma unroll
-                for (int j = 0; j < 4; ++j)
+                for (int j = 0; j < 8; ++j)
                     if (i0 + j < P.n) dst[j] = (uint8_t)v[j];
             }
         }
-        const uint32_t* g = cur.g;
-        const uint32_t* p = cur.p;
-        // is this lane's quad one valid run?
-        const bool uni = (pane[0] != kInvalid) && g[0] == g[1] && g[1] == g[2] && g[2] == g[3] &&
-                         p[0] == p[1] && p[1] == p[2] && p[2] == p[3] && pane[0] == pane[1] &&
-                         pane[1] == pane[2] && pane[2] == pane[3];
-        // segment heads among uniform lanes
-        const uint32_t pg = __shfl_up_sync(0xFFFFFFFFu, g[0], 1);
-        const uint32_t pp = __shfl_up_sync(0xFFFFFFFFu, p[0], 1);
-        const uint32_t ppn = __shfl_up_sync(0xFFFFFFFFu, pane[0], 1);
-        const uint32_t unis = __ballot_sync(0xFFFFFFFFu, uni);
-        const bool prev_uni = lane > 0 && ((unis >> (lane - 1)) & 1u);
-        const bool head = uni && (!prev_uni || pg != g[0] || pp != p[0] || ppn != pane[0]);
-        const uint32_t heads = __ballot_sync(0xFFFFFFFFu, head);
-        const uint32_t breakers = heads | ~unis;
-        const uint32_t rest = (lane == 31) ? 0u : (breakers & (0xFFFFFFFEu << lane));
-        const uint32_t seg_end = rest ? (uint32_t)(__ffs(rest) - 2) : 31u;
-        uint32_t s = 0, m = 0;
-        if (uni) {
-            s = v[0] + v[1] + v[2] + v[3];
-            m = max(max(v[0], v[1]), max(v[2], v[3]));
+        // boundaries inside the lane: bit j set when sample j starts a new piece
+        uint32_t bm = 0;
+#pragma unroll
+        for (int j = 1; j < 8; ++j) {
+            const uint32_t diff = (cur.g[j] ^ cur.g[j - 1]) | (cur.p[j] ^ cur.p[j - 1]) | (pane[j] ^ pane[j - 1]);
+            bm += min(diff, 1u) << j;   // distinct bits: + is |
         }
+        const bool single = bm == 0;
+        // does my first piece continue the previous lane's last piece?
+        const uint32_t pg = __shfl_up_sync(kAll, cur.g[7], 1);
+        const uint32_t pp = __shfl_up_sync(kAll, cur.p[7], 1);
+        const uint32_t ppn = __shfl_up_sync(kAll, pane[7], 1);
+        const bool cont = lane > 0 && pg == cur.g[0] && pp == cur.p[0] && ppn == pane[0];
+        // a chain starts at every lane with a boundary inside (its last piece) and at every single
+        // lane that does not continue its predecessor
+        const bool head = !single || !cont;
+        const uint32_t heads = __ballot_sync(kAll, head);
+        const uint32_t rest = (lane == 31) ? 0u : (heads & (0xFFFFFFFEu << lane));
+        const uint32_t seg_end = rest ? (uint32_t)(__ffs(rest) - 2) : 31u;
+        // forward piece of this lane (whole lane when single) and, for split lanes, the first piece
+        uint32_t fc = 8, fs, fm, fstart = 0;          // forward: count, sum, max, offset of its first sample
+        uint32_t ac = 0, as = 0, am = 0;              // first piece of a split lane
+        if (single) {
+            fs = ((v[0] + v[1]) + (v[2] + v[3])) + ((v[4] + v[5]) + (v[6] + v[7]));
+            fm = max(max(max(v[0], v[1]), max(v[2], v[3])), max(max(v[4], v[5]), max(v[6], v[7])));
+        } else {
+            const uint32_t first_end = __ffs(bm) - 1;             // first piece = samples [0, first_end)
+            const uint32_t last_begin = 31 - __clz(bm);           // last piece  = samples [last_begin, 8)
+            fs = 0; fm = 0;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                if ((uint32_t)j < first_end) { as += v[j]; am = max(am, v[j]); }
+                if ((uint32_t)j >= last_begin) { fs += v[j]; fm = max(fm, v[j]); }
+            }
+            ac = first_end;
+            fc = 8 - last_begin;
+            fstart = last_begin;
+        }
+        // chain totals: sum and max by a segmented shuffle reduction, count is implied
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {
-            const uint32_t s2 = __shfl_down_sync(0xFFFFFFFFu, s, d);
-            const uint32_t m2 = __shfl_down_sync(0xFFFFFFFFu, m, d);
+            const uint32_t s2 = __shfl_down_sync(kAll, fs, d);
+            const uint32_t m2 = __shfl_down_sync(kAll, fm, d);
             if (lane + d <= seg_end) {
-                s += s2;
-                m = max(m, m2);
+                fs += s2;
+                fm = max(fm, m2);
             }
         }
-        const uint32_t c = 4 * (seg_end - lane + 1);
-        const uint32_t start = (uint32_t)(P.vals_base + i0);
-        // does the run at the head of this tile continue the last queued record?
+        uint32_t cc = fc + 8 * (seg_end - lane);
+        {   // absorb the first piece of the split lane that ends the chain, if it has the chain's key
+            const uint32_t j = min(seg_end + 1, 31u);
+            const bool joins = !single && cont;
+            const uint32_t jj = __shfl_sync(kAll, (uint32_t)joins, j);
+            const uint32_t jc = __shfl_sync(kAll, ac, j);
+            const uint32_t js = __shfl_sync(kAll, as, j);
+            const uint32_t jm = __shfl_sync(kAll, am, j);
+            if (seg_end < 31 && jj) {
+                cc += jc;
+                fs += js;
+                fm = max(fm, jm);
+            }
+        }
+        // records this lane appends: its chain (head lanes, valid key) and a stand-alone first piece
+        const bool rec_chain = head && pane[7] != kInvalid;
+        const bool rec_first = !single && !cont && pane[0] != kInvalid;
+        const uint32_t start0 = (uint32_t)P.vals_base + i0;
+        // the record that starts exactly at the tile's first sample may continue the queued tail
         bool merged = false;
-        if (lane == 0 && head && queued) {
+        if (lane == 0 && queued && (single ? rec_chain : rec_first)) {
             const uint32_t r = queued - 1;
-            if (Q.gid[r] == g[0] && Q.pid[r] == p[0] && Q.pane[r] == pane[0] && Q.start[r] + Q.cnt[r] == start &&
-                Q.cnt[r] + c <= kMergeMax) {
-                Q.cnt[r] += c;
-                Q.sum[r] += s;
-                Q.mx[r] = max(Q.mx[r], m);
+            const uint32_t mc = single ? cc : ac, ms = single ? fs : as, mm = single ? fm : am;
+            if (Q.gid[r] == cur.g[0] && Q.pid[r] == cur.p[0] && Q.pane[r] == pane[0] && Q.start[r] + Q.cnt[r] == start0 &&
+                Q.cnt[r] + mc <= kMergeMax) {
+                Q.cnt[r] += mc;
+                Q.sum[r] += ms;
+                Q.mx[r] = max(Q.mx[r], mm);
                 merged = true;
             }
         }
-        merged = __shfl_sync(0xFFFFFFFFu, merged, 0);
-        if (head && !(lane == 0 && merged)) {
-            const uint32_t r = queued + __popc(heads & ((1u << lane) - 1u)) - (merged ? 1u : 0u);
-            Q.gid[r] = g[0]; Q.pid[r] = p[0]; Q.pane[r] = pane[0];
-            Q.cnt[r] = c; Q.sum[r] = s; Q.mx[r] = m; Q.start[r] = start;
+        merged = __shfl_sync(kAll, (uint32_t)merged, 0) != 0;
+        const uint32_t m_first = __ballot_sync(kAll, rec_first);
+        const uint32_t m_chain = __ballot_sync(kAll, rec_chain);
+        const uint32_t below = (1u << lane) - 1u;
+        // slot order = sample order: a lane's first piece precedes its chain
+        uint32_t slot = queued + __popc(m_first & below) + __popc(m_chain & below) - ((merged && lane > 0) ? 1u : 0u);
+        if (rec_first) {
+            if (!(lane == 0 && merged)) {
+                Q.gid[slot] = cur.g[0]; Q.pid[slot] = cur.p[0]; Q.pane[slot] = pane[0];
+                Q.cnt[slot] = ac; Q.sum[slot] = as; Q.mx[slot] = am; Q.start[slot] = start0;
+            }
+            slot += (lane == 0 && merged) ? 0u : 1u;
         }
-        queued += __popc(heads) - (merged ? 1u : 0u);
-        // ragged quads (a run boundary or an out-of-range sample inside the quad): each lane
-        // retires its own pieces directly; rare in collector order
-        if (unis != 0xFFFFFFFFu) {
+        if (rec_chain && !(lane == 0 && merged && single)) {
+            Q.gid[slot] = cur.g[7]; Q.pid[slot] = cur.p[7]; Q.pane[slot] = pane[7];
+            Q.cnt[slot] = cc; Q.sum[slot] = fs; Q.mx[slot] = fm; Q.start[slot] = start0 + fstart;
+        }
+        queued += __popc(m_first) + __popc(m_chain) - (merged ? 1u : 0u);
+        // lanes with two or more boundaries: the pieces between the first and the last are retired
+        // directly (rare in collector order; every lane in shuffled input, then 32 wide)
+        const bool many = (bm & (bm - 1)) != 0;
+        if (__any_sync(kAll, many)) {
             uint32_t nr = 0;
-            if (!uni) {
+            if (many) {
 #pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const bool first = (j == 0) || g[j] != g[j - 1] || p[j] != p[j - 1] || pane[j] != pane[j - 1];
-                    nr += (first && pane[j] != kInvalid) ? 1u : 0u;
+                for (int j = 1; j < 8; ++j) {      // middle piece starting at j: a boundary at j, another one later
+                    const bool starts = (bm >> j) & 1u;
+                    const bool last = (bm >> (j + 1)) == 0;
+                    nr += (starts && !last && pane[j] != kInvalid) ? 1u : 0u;
                 }
             }
-            if (__any_sync(0xFFFFFFFFu, nr != 0)) {
-                uint32_t di = 0;
-                bool log_ok = false;
-                if (PCT) {
-                    uint32_t incl = nr;
+            uint32_t di = 0;
+            bool log_ok = false;
+            if (PCT) {
+                uint32_t incl = nr;
 #pragma unroll
-                    for (int d = 1; d < 32; d <<= 1) {
-                        const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, incl, d);
-                        if (lane >= (uint32_t)d) incl += o;
-                    }
-                    const uint32_t total = __shfl_sync(0xFFFFFFFFu, incl, 31) * nk;
-                    di = reserve_log(P, total, log_ok) + (incl - nr) * nk;
+                for (int d = 1; d < 32; d <<= 1) {
+                    const uint32_t o = __shfl_up_sync(kAll, incl, d);
+                    if (lane >= (uint32_t)d) incl += o;
                 }
-                if (nr) {
-                    uint32_t rs = 0, rm = 0, rc = 0;
-                    int rstart = 0;
+                const uint32_t total = __shfl_sync(kAll, incl, 31) * nk;
+                di = reserve_log(P, lc, total, log_ok) + (incl - nr) * nk;
+            }
+            if (nr) {
+                uint32_t rs = 0, rm = 0, rc = 0, rstart = 0;
+                bool open = false;
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) {
-                        const bool first = (j == 0) || g[j] != g[j - 1] || p[j] != p[j - 1] || pane[j] != pane[j - 1];
-                        if (first) {
-                            rs = 0; rm = 0; rc = 0; rstart = j;
+                for (int j = 1; j < 8; ++j) {
+                    const bool starts = (bm >> j) & 1u;
+                    const bool last = (bm >> (j + 1)) == 0;
+                    if (starts) {
+                        if (open && pane[j - 1] != kInvalid) {
+                            emit_run<PCT>(P, cur.g[j - 1], cur.p[j - 1], pane[j - 1], rc, rs, rm, start0 + rstart, di, log_ok);
+                            di += nk;
                         }
+                        open = !last;
+                        rs = 0; rm = 0; rc = 0; rstart = j;
+                    }
+                    if (open) {
                         rs += v[j];
                         rm = max(rm, v[j]);
                         rc += 1;
-                        const bool last = (j == 3) || g[j + 1] != g[j] || p[j + 1] != p[j] || pane[j + 1] != pane[j];
-                        if (last && pane[j] != kInvalid) {
-                            emit_run<PCT>(P, g[j], p[j], pane[j], rc, rs, rm, start + rstart, di, log_ok);
-                            di += nk;
-                        }
                     }
                 }
             }
         }
         __syncwarp();
         if (queued > 32) {   // retire all but the newest record (it may still grow)
-            flush_queue<PCT>(P, Q, queued - 1, nk);
+            flush_queue<PCT>(P, lc, Q, queued - 1, nk);
             __syncwarp();
             if (lane == 0) {
                 const uint32_t r = queued - 1;
@@ -290,9 +376,9 @@ __global__ void __launch_bounds__(kAccumWarps * 32) k_accum(const __grid_constan
             queued = 1;
             __syncwarp();
         }
-        cur = nxt;
+        if (PREFETCH) cur = nxt;
     }
-    flush_queue<PCT>(P, Q, queued, nk);
+    flush_queue<PCT>(P, lc, Q, queued, nk);
 }
 
 }  // namespace kgs

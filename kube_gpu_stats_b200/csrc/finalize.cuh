@@ -107,28 +107,35 @@ struct Layout16 {
 using CellLayout = Layout16<128, 128>;   // values 0..127: 256 B per thread, 32 KB per CTA of 128 threads
 using WideLayout = Layout16<64, 256>;    // values 0..255: 512 B per thread, 32 KB per CTA of 64 threads
 
-// Count the bytes of x selected by `mask` (bit k = byte k) into the thread's histogram.  Masked
-// bytes are counted with an increment of 0 rather than skipped: no branches, no divergence.
-template <class L, bool MASKED>
-__device__ __forceinline__ void add16(uint32_t base, const uint4& x, uint32_t mask) {
+// Count the 16 bytes of x into the thread's histogram.
+template <class L>
+__device__ __forceinline__ void add16(uint32_t base, const uint4& x) {
     const uint32_t w[4] = {x.x, x.y, x.z, x.w};
 #pragma unroll
-    for (int k = 0; k < 16; k += 2) {
-        uint32_t ba = (w[k >> 2] >> (8 * (k & 3))) & 0xFFu;
-        uint32_t bb = (w[k >> 2] >> (8 * ((k + 1) & 3))) & 0xFFu;
-        const uint32_t da = MASKED ? ((mask >> k) & 1u) : 1u, db = MASKED ? ((mask >> (k + 1)) & 1u) : 1u;
-        if (MASKED) {   // bytes outside the run may hold any value: keep their (+0) access inside the table
-            ba *= da;
-            bb *= db;
-        }
-        L::inc2(base, ba, bb, da, db);
+    for (int k = 0; k < 4; ++k) {
+        L::inc2(base, w[k] & 0xFFu, (w[k] >> 8) & 0xFFu, 1u, 1u);
+        L::inc2(base, (w[k] >> 16) & 0xFFu, w[k] >> 24, 1u, 1u);
     }
 }
 
+template <class L>
+__device__ __forceinline__ void add4(uint32_t base, uint32_t w) {
+    L::inc2(base, w & 0xFFu, (w >> 8) & 0xFFu, 1u, 1u);
+    L::inc2(base, (w >> 16) & 0xFFu, w >> 24, 1u, 1u);
+}
+
+template <class L>
+__device__ __forceinline__ void add1(uint32_t base, uint32_t b) {
+    const uint32_t a = L::addr(base, b);
+    sts_u16(a, lds_u16(a) + 1u);
+}
+
 // Count the W pane lists of this thread's window cell into its histogram.  WARP-SYNCHRONOUS: all
-// 32 lanes call it together (lanes without a cell pass valid = false) and step through runs and
-// 16-byte blocks in lockstep, so the warp always executes ONE of the two block bodies: the
-// unmasked one when every lane has a whole block, the arithmetic-masked one otherwise.
+// 32 lanes call it together (lanes without a cell pass valid = false) and walk their runs in
+// lockstep through five phases - bytes up to a 4-byte boundary, words up to a 16-byte boundary,
+// 16-byte blocks, trailing words, trailing bytes - each phase a loop that runs as long as ANY
+// lane still has work in it.  Every phase has one branch-free body, so no byte is ever masked
+// and the warp never executes two bodies for one step.
 template <class L>
 __device__ __forceinline__ void add_cell(uint32_t base, const FinParams& P, const FinKind& K, uint32_t pc0,
                                          bool valid) {
@@ -138,19 +145,37 @@ __device__ __forceinline__ void add_cell(uint32_t base, const FinParams& P, cons
         while (__any_sync(kAll, at != 0)) {
             uint4 r = make_uint4(0, 0, 0, 0);
             if (at) r = __ldg(P.desc + (at - 1));
-            const uint32_t start = r.x, end = r.x + r.y;
-            uint32_t blk = start & ~15u;
-            while (__any_sync(kAll, blk < end)) {
-                uint4 x = make_uint4(0, 0, 0, 0);
-                uint32_t mask = 0;
-                if (blk < end) {
-                    x = __ldg(reinterpret_cast<const uint4*>(P.vals + blk));
-                    const uint32_t lo = max(start, blk) - blk, hi = min(end, blk + 16) - blk;
-                    mask = ((1u << hi) - 1u) & ~((1u << lo) - 1u);
+            uint32_t pos = r.x;
+            const uint32_t end = r.x + r.y;
+            while (__any_sync(kAll, (pos & 3u) && pos < end)) {                 // head bytes
+                if ((pos & 3u) && pos < end) {
+                    add1<L>(base, __ldg(P.vals + pos));
+                    pos += 1;
                 }
-                if (__all_sync(kAll, mask == 0xFFFFu)) add16<L, false>(base, x, 0xFFFFu);
-                else add16<L, true>(base, x, mask);
-                blk += 16;
+            }
+            while (__any_sync(kAll, (pos & 15u) && pos + 4 <= end)) {           // head words
+                if ((pos & 15u) && pos + 4 <= end) {
+                    add4<L>(base, __ldg(reinterpret_cast<const uint32_t*>(P.vals + pos)));
+                    pos += 4;
+                }
+            }
+            while (__any_sync(kAll, pos + 16 <= end)) {                         // aligned 16-byte blocks
+                if (pos + 16 <= end) {
+                    add16<L>(base, __ldg(reinterpret_cast<const uint4*>(P.vals + pos)));
+                    pos += 16;
+                }
+            }
+            while (__any_sync(kAll, pos + 4 <= end)) {                          // tail words
+                if (pos + 4 <= end) {
+                    add4<L>(base, __ldg(reinterpret_cast<const uint32_t*>(P.vals + pos)));
+                    pos += 4;
+                }
+            }
+            while (__any_sync(kAll, pos < end)) {                               // tail bytes
+                if (pos < end) {
+                    add1<L>(base, __ldg(P.vals + pos));
+                    pos += 1;
+                }
             }
             at = r.z;
         }

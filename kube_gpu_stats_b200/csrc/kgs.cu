@@ -76,8 +76,10 @@ struct kgs_ctx {
     uint32_t big_cap = 0, wide_cap = 0;
     size_t result_off = 0, result_bytes = 0;
     uint64_t vals_cap = 0, vals_used = 0, accumulated = 0;
-    uint32_t desc_cap = 0;
+    uint32_t desc_cap = 0, desc_pool_base = 0, desc_priv_next = 0;
     uint64_t run_cap_override = 0;
+    bool accum_prefetch = false;   // register double-buffering of the next tile: 109 vs 78 registers
+    int accum_ctas_per_sm = 3;     // resident CTAs of 8 warps per SM at 78 registers
     // measurement
     uint64_t launches = 0;
     bool prof = false;
@@ -205,6 +207,11 @@ int kgs_create(int device, kgs_handle* out) {
         if ((e = cudaEventCreateWithFlags(&h->batch[b].consumed, cudaEventDisableTiming)) != cudaSuccess) return bail(e, "cudaEventCreate");
         if ((e = cudaEventCreate(&h->mark[b])) != cudaSuccess) return bail(e, "cudaEventCreate");
     }
+    if (const char* e = getenv("KGS_ACCUM_PREFETCH")) h->accum_prefetch = atoi(e) != 0;
+    if (const char* e = getenv("KGS_ACCUM_CTAS_PER_SM")) {   // tuning knob for experiments
+        const int v = atoi(e);
+        if (v >= 1 && v <= 8) h->accum_ctas_per_sm = v;
+    }
     *out = h;
     return KGS_OK;
 }
@@ -264,7 +271,7 @@ int kgs_free_pinned(kgs_handle h, void* p) {
 int kgs_ingest(kgs_handle h, const uint32_t* ts, const uint32_t* gpu_gid, const uint32_t* pid,
                const uint32_t* util, uint64_t n) {
     if (!h || (n && (!ts || !gpu_gid || !pid || !util))) return fail(h, KGS_ERR_ARG, "kgs_ingest: null column");
-    if (n >= (1ull << 32)) return fail(h, KGS_ERR_ARG, "kgs_ingest: a batch holds fewer than 2^32 samples");
+    if (n >= 0xFFFFFC00ull) return fail(h, KGS_ERR_ARG, "kgs_ingest: a batch holds fewer than 2^32 - 1024 samples");
     KGS_CUDA(h, cudaSetDevice(h->device));
     const int b = (h->cur + 1) & 1;
     Batch& B = h->batch[b];
@@ -272,12 +279,12 @@ int kgs_ingest(kgs_handle h, const uint32_t* ts, const uint32_t* gpu_gid, const 
     // the slot may still be read by kernels queued on the compute stream
     KGS_CUDA(h, cudaStreamWaitEvent(h->copy, B.consumed, 0));
     for (int c = 0; c < 4; ++c) {
-        if (n * 4 + 16 > B.col[c].cap) {
+        if (n * 4 + 64 > B.col[c].cap) {
             // growing a slot frees device memory: make sure nothing is still using it
             KGS_CUDA(h, cudaStreamSynchronize(h->compute));
             KGS_CUDA(h, cudaStreamSynchronize(h->copy));
         }
-        int rc = reserve(h, B.col[c], n * 4 + 16);
+        int rc = reserve(h, B.col[c], n * 4 + 64);
         if (rc) return rc;
         B.ptr[c] = static_cast<const uint32_t*>(B.col[c].p);
         if (n) KGS_CUDA(h, cudaMemcpyAsync(B.col[c].p, src[c], n * 4, cudaMemcpyHostToDevice, h->copy));
@@ -291,9 +298,9 @@ int kgs_ingest(kgs_handle h, const uint32_t* ts, const uint32_t* gpu_gid, const 
 int kgs_adopt_device_batch(kgs_handle h, const uint32_t* d_ts, const uint32_t* d_gpu_gid,
                            const uint32_t* d_pid, const uint32_t* d_util, uint64_t n) {
     if (!h || (n && (!d_ts || !d_gpu_gid || !d_pid || !d_util))) return fail(h, KGS_ERR_ARG, "kgs_adopt_device_batch: null column");
-    if (n >= (1ull << 32)) return fail(h, KGS_ERR_ARG, "a batch holds fewer than 2^32 samples");
+    if (n >= 0xFFFFFC00ull) return fail(h, KGS_ERR_ARG, "a batch holds fewer than 2^32 - 1024 samples");
     const uintptr_t all = (uintptr_t)d_ts | (uintptr_t)d_gpu_gid | (uintptr_t)d_pid | (uintptr_t)d_util;
-    if (all & 15) return fail(h, KGS_ERR_ARG, "device columns must be 16-byte aligned");
+    if (all & 31) return fail(h, KGS_ERR_ARG, "device columns must be 32-byte aligned");
     KGS_CUDA(h, cudaSetDevice(h->device));
     const int b = (h->cur + 1) & 1;
     Batch& B = h->batch[b];
@@ -501,6 +508,8 @@ int kgs_stats_begin(kgs_handle h, const kgs_window_spec* sp) {
         if ((rc = reserve(h, h->desc, dcap * 16))) return rc;
         h->vals_cap = vals_cap;
         h->desc_cap = (uint32_t)dcap;
+        h->desc_pool_base = (uint32_t)(dcap - dcap / 4);   // last quarter: shared overflow pool
+        h->desc_priv_next = 0;
     } else {
         h->vals_cap = 0;
         h->desc_cap = 0;
@@ -529,7 +538,7 @@ int kgs_stats_accumulate(kgs_handle h) {
         return fail(h, KGS_ERR_CAPACITY, "value log full: total_samples_hint was smaller than the samples accumulated");
     AccumParams P{};
     P.ts = B.ptr[0]; P.gid = B.ptr[1]; P.pid = B.ptr[2]; P.util = B.ptr[3];
-    P.n = B.n;
+    P.n = (uint32_t)B.n;
     P.vals_base = h->vals_used;
     P.slots = static_cast<const JoinSlot*>(h->slots.p);
     P.tmask = h->n_slots ? h->n_slots - 1 : 0;
@@ -553,15 +562,33 @@ int kgs_stats_accumulate(kgs_handle h) {
     P.ctl = h->ctl;
     cudaStream_t st = h->compute;
     KGS_CUDA(h, cudaStreamWaitEvent(st, B.ready, 0));
-    // 4 CTAs of 8 warps per SM; every warp owns a contiguous chunk of 128-sample tiles
-    const uint64_t n_tiles = (B.n + 127) / 128;
-    const uint64_t max_warps = 148ull * 4 * kAccumWarps;
+    // every warp owns a contiguous chunk of 256-sample tiles; ctas_per_sm resident CTAs of 8 warps
+    const uint64_t n_tiles = (B.n + kTileSamples - 1) / kTileSamples;
+    const uint64_t max_warps = 148ull * h->accum_ctas_per_sm * kAccumWarps;
     const uint64_t tpw = (n_tiles + max_warps - 1) / max_warps;
-    P.tiles_per_warp = (uint32_t)(tpw < 4 ? 4 : tpw);
+    P.tiles_per_warp = (uint32_t)(tpw < 2 ? 2 : tpw);
     const int grid = (int)((n_tiles + (uint64_t)P.tiles_per_warp * kAccumWarps - 1) / ((uint64_t)P.tiles_per_warp * kAccumWarps));
+    if (pct) {
+        // a private run-log slab per warp for this launch (16 entries per tile and key kind is > 3x what
+        // collector-ordered input needs); what does not fit goes to the shared pool
+        const uint64_t warps = (uint64_t)grid * kAccumWarps;
+        uint64_t per_warp = (uint64_t)P.tiles_per_warp * 16 * __builtin_popcount(sp.key_mask);
+        if (h->run_cap_override) per_warp = (uint64_t)P.tiles_per_warp * kTileSamples * __builtin_popcount(sp.key_mask);   // every sample its own run
+        const uint64_t room = h->desc_pool_base - h->desc_priv_next;
+        if (per_warp * warps > room) per_warp = room / warps;
+        P.log_base = h->desc_priv_next;
+        P.log_per_warp = (uint32_t)per_warp;
+        P.pool_base = h->desc_pool_base;
+        h->desc_priv_next += (uint32_t)(per_warp * warps);
+    }
     launch(h, KGS_K_ACCUM, st, [&] {
-        if (pct) k_accum<true><<<grid, 256, 0, st>>>(P);
-        else k_accum<false><<<grid, 256, 0, st>>>(P);
+        if (h->accum_prefetch) {
+            if (pct) k_accum<true, true><<<grid, 256, 0, st>>>(P);
+            else k_accum<false, true><<<grid, 256, 0, st>>>(P);
+        } else {
+            if (pct) k_accum<true, false><<<grid, 256, 0, st>>>(P);
+            else k_accum<false, false><<<grid, 256, 0, st>>>(P);
+        }
     });
     KGS_CUDA(h, cudaGetLastError());
     KGS_CUDA(h, cudaEventRecord(B.consumed, st));
@@ -635,7 +662,7 @@ static int check_job_flags(kgs_handle h) {
     KGS_CUDA(h, cudaStreamSynchronize(h->compute));
     if (ctl[1])
         return fail(h, KGS_ERR_CAPACITY,
-                    "run log overflow: " + std::to_string(ctl[0]) + " run descriptors needed, capacity " +
+                    "run log overflow: the shared pool needed " + std::to_string(ctl[0]) + " entries, total capacity " +
                         std::to_string(h->desc_cap) + " (input far from collector order; raise it with kgs_set_run_log_capacity)");
     return KGS_OK;
 }

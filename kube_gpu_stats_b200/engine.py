@@ -183,7 +183,7 @@ class Engine:
             except KgsError as e:
                 if e.code != _ffi.KGS_ERR_CAPACITY or attempt:
                     raise
-                self.set_run_log_capacity((self.n_resident + 64) * len(kinds))
+                self.set_run_log_capacity(2 * (self.n_resident + 4096) * len(kinds))
         raise AssertionError('unreachable')
 
     def result_device_ptr(self, kind, which):

@@ -124,7 +124,7 @@ def test_streamed_batches_equal_one_batch(engine, cfg1):
     """begin / (ingest, accumulate)* / finalize over 7 uneven batches == the one-shot job."""
     tr = cfg1
     engine.build_join(tr.keys, tr.pod_ids, tr.n_pods)
-    engine.set_run_log_capacity(3 * tr.n)     # 8 interleaved processes per GPU: every sample is its own run
+    engine.set_run_log_capacity(2 * 3 * (tr.n + 8 * 4096))   # 8 interleaved processes per GPU: every sample is its own run
     spec = engine.make_spec(kinds=('pod', 'gpu', 'node'), metric='sm', gpus_per_node=8, t0=tr.t0, step=60,
                             n_windows=60, n_gpus=tr.n_gpus, n_nodes=tr.n_nodes, qs=QS, total_samples_hint=tr.n)
     engine.stats_begin(spec)
