@@ -67,6 +67,19 @@ struct AccumParams {
     uint32_t* ctl;                 // ctl[0] pool cursor, ctl[1] overflow flag
 };
 
+__device__ __forceinline__ uint64_t policy_evict_last() {
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+__device__ __forceinline__ void st_keep_v2(void* p, uint32_t a, uint32_t b, uint64_t pol) {
+    asm volatile("st.global.L2::cache_hint.v2.u32 [%0], {%1,%2}, %3;" ::"l"(p), "r"(a), "r"(b), "l"(pol) : "memory");
+}
+__device__ __forceinline__ void st_keep_v4(void* p, uint4 v, uint64_t pol) {
+    asm volatile("st.global.L2::cache_hint.v4.u32 [%0], {%1,%2,%3,%4}, %5;" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w), "l"(pol)
+                 : "memory");
+}
+
 struct LogCursor {   // warp-uniform position inside the warp's private slab
     uint32_t at, left;
 };
@@ -101,7 +114,7 @@ __device__ __forceinline__ void emit_run(const AccumParams& P, uint32_t g, uint3
         if (PCT && log_ok) {
             uint32_t next = 0;
             if (valid) next = atomicExch(P.head[kind] + cell, di + 1);
-            P.desc[di] = make_uint4(start, c, next, cell);
+            st_keep_v4(P.desc + di, make_uint4(start, c, next, cell), policy_evict_last());
             ++di;
         }
     }
@@ -147,7 +160,9 @@ struct Oct {   // one lane's eight consecutive samples
 };
 
 __device__ __forceinline__ void ld_stream_v8(const uint32_t* p, uint32_t* r) {
-    asm volatile("ld.global.nc.L1::no_allocate.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+    // read once: keep it out of L1 and first in line for eviction from L2, so the value log, run log
+    // and accumulators this kernel writes are still L2-resident when the finalize kernels read them
+    asm volatile("ld.global.nc.L1::no_allocate.L2::evict_first.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
                  : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
                  : "l"(p));
 }
@@ -209,10 +224,8 @@ __global__ void __launch_bounds__(kAccumWarps * 32) k_accum(const __grid_constan
         if (PCT) {   // value log, same order as the input (u8 metrics)
             uint8_t* dst = P.vals + P.vals_base + i0;
             if (full) {
-                uint2 w;
-                w.x = v[0] | (v[1] << 8) | (v[2] << 16) | (v[3] << 24);
-                w.y = v[4] | (v[5] << 8) | (v[6] << 16) | (v[7] << 24);
-                *reinterpret_cast<uint2*>(dst) = w;
+                st_keep_v2(dst, v[0] | (v[1] << 8) | (v[2] << 16) | (v[3] << 24),
+                           v[4] | (v[5] << 8) | (v[6] << 16) | (v[7] << 24), policy_evict_last());
             } else {
 #pragma unroll
                 for (int j = 0; j < 8; ++j)

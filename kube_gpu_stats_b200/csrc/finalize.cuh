@@ -107,17 +107,6 @@ struct Layout16 {
 using CellLayout = Layout16<128, 128>;   // values 0..127: 256 B per thread, 32 KB per CTA of 128 threads
 using WideLayout = Layout16<64, 256>;    // values 0..255: 512 B per thread, 32 KB per CTA of 64 threads
 
-// Count the 16 bytes of x into the thread's histogram.
-template <class L>
-__device__ __forceinline__ void add16(uint32_t base, const uint4& x) {
-    const uint32_t w[4] = {x.x, x.y, x.z, x.w};
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-        L::inc2(base, w[k] & 0xFFu, (w[k] >> 8) & 0xFFu, 1u, 1u);
-        L::inc2(base, (w[k] >> 16) & 0xFFu, w[k] >> 24, 1u, 1u);
-    }
-}
-
 template <class L>
 __device__ __forceinline__ void add4(uint32_t base, uint32_t w) {
     L::inc2(base, w & 0xFFu, (w >> 8) & 0xFFu, 1u, 1u);
@@ -132,50 +121,50 @@ __device__ __forceinline__ void add1(uint32_t base, uint32_t b) {
 
 // Count the W pane lists of this thread's window cell into its histogram.  WARP-SYNCHRONOUS: all
 // 32 lanes call it together (lanes without a cell pass valid = false) and walk their runs in
-// lockstep through five phases - bytes up to a 4-byte boundary, words up to a 16-byte boundary,
-// 16-byte blocks, trailing words, trailing bytes - each phase a loop that runs as long as ANY
-// lane still has work in it.  Every phase has one branch-free body, so no byte is ever masked
-// and the warp never executes two bodies for one step.
+// lockstep.  A run is covered by 16-byte ALIGNED blocks of the value log; kChunk of them are
+// loaded at once (one round trip to L2 per chunk, not per block) and then counted word by word:
+// a word that lies completely inside the run takes the branch-free 4-byte body, the at most two
+// words cut by the run's ends take a byte loop that the warp only enters when some lane needs it.
 template <class L>
 __device__ __forceinline__ void add_cell(uint32_t base, const FinParams& P, const FinKind& K, uint32_t pc0,
                                          bool valid) {
     constexpr uint32_t kAll = 0xFFFFFFFFu;
+    constexpr int kChunk = 5;   // 80 bytes: a 60-sample run at any alignment
     for (uint32_t d = 0; d < P.W; ++d) {
         uint32_t at = valid ? K.head[pc0 + d] : 0u;
         while (__any_sync(kAll, at != 0)) {
             uint4 r = make_uint4(0, 0, 0, 0);
             if (at) r = __ldg(P.desc + (at - 1));
-            uint32_t pos = r.x;
-            const uint32_t end = r.x + r.y;
-            while (__any_sync(kAll, (pos & 3u) && pos < end)) {                 // head bytes
-                if ((pos & 3u) && pos < end) {
-                    add1<L>(base, __ldg(P.vals + pos));
-                    pos += 1;
+            const uint32_t start = r.x, end = r.x + r.y;
+            uint32_t blk = start & ~15u;
+            while (__any_sync(kAll, blk < end)) {
+                uint4 x[kChunk];
+#pragma unroll
+                for (int b = 0; b < kChunk; ++b) {
+                    x[b] = make_uint4(0, 0, 0, 0);
+                    if (blk + 16 * b < end) x[b] = __ldg(reinterpret_cast<const uint4*>(P.vals + blk + 16 * b));
                 }
-            }
-            while (__any_sync(kAll, (pos & 15u) && pos + 4 <= end)) {           // head words
-                if ((pos & 15u) && pos + 4 <= end) {
-                    add4<L>(base, __ldg(reinterpret_cast<const uint32_t*>(P.vals + pos)));
-                    pos += 4;
+#pragma unroll
+                for (int b = 0; b < kChunk; ++b) {
+                    const uint32_t a = blk + 16 * b;
+                    if (!__any_sync(kAll, a < end)) break;
+                    const int lo = (int)(start - a), hi = (int)(end - a);   // run = bytes [lo, hi) of this block
+                    const uint32_t w[4] = {x[b].x, x[b].y, x[b].z, x[b].w};
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const bool whole = lo <= 4 * k && hi >= 4 * k + 4;
+                        const bool cut = !whole && lo < 4 * k + 4 && hi > 4 * k;
+                        if (whole) add4<L>(base, w[k]);
+                        if (__any_sync(kAll, cut)) {
+                            if (cut) {
+#pragma unroll
+                                for (int j = 0; j < 4; ++j)
+                                    if (lo <= 4 * k + j && 4 * k + j < hi) add1<L>(base, (w[k] >> (8 * j)) & 0xFFu);
+                            }
+                        }
+                    }
                 }
-            }
-            while (__any_sync(kAll, pos + 16 <= end)) {                         // aligned 16-byte blocks
-                if (pos + 16 <= end) {
-                    add16<L>(base, __ldg(reinterpret_cast<const uint4*>(P.vals + pos)));
-                    pos += 16;
-                }
-            }
-            while (__any_sync(kAll, pos + 4 <= end)) {                          // tail words
-                if (pos + 4 <= end) {
-                    add4<L>(base, __ldg(reinterpret_cast<const uint32_t*>(P.vals + pos)));
-                    pos += 4;
-                }
-            }
-            while (__any_sync(kAll, pos < end)) {                               // tail bytes
-                if (pos < end) {
-                    add1<L>(base, __ldg(P.vals + pos));
-                    pos += 1;
-                }
+                blk += 16 * kChunk;
             }
             at = r.z;
         }
