@@ -141,16 +141,21 @@ int kgs_window_stats(kgs_handle h, const kgs_window_spec* spec);
 int kgs_set_run_log_capacity(kgs_handle h, uint64_t entries);
 /* Copy one key kind's result table to host arrays of n_keys * n_windows entries, cell index
  * key * n_windows + window (pct: n_q rows of that length).  Any pointer may be NULL. Blocking. */
-int kgs_fetch_stats(kgs_handle h, int key_kind, uint64_t* count, uint64_t* sum, uint32_t* max,
+int kgs_fetch_stats(kgs_handle h, int key_kind, uint32_t* count, uint64_t* sum, uint32_t* max,
                     double* mean, double* pct);
 /* Device addresses of the same tables, for a caller that exchanges them GPU-to-GPU (the
- * allgather of per-shard partial tables in north_star).  which: 0 count(u64) 1 sum(u64)
+ * allgather of per-shard partial tables in north_star).  which: 0 count(u32) 1 sum(u64)
  * 2 max(u32) 3 mean(f64) 4 pct(f64, n_q rows). */
 int kgs_result_device_ptr(kgs_handle h, int key_kind, int which, void** d_ptr, size_t* nbytes);
 /* All result tables of the finalized job are one contiguous device region (every table starts
- * 256-byte aligned inside it): its address and size, so one collective can move them all.
- * kgs_result_device_ptr addresses lie inside this region. */
-int kgs_result_region(kgs_handle h, void** d_ptr, size_t* nbytes);
+ * 256-byte aligned inside it).  Its first exchange_bytes hold what another shard needs - sum, pct,
+ * count, max of every kind, 16 + 8*n_q bytes per cell - so ONE collective can move them all; the
+ * mean tables (derivable: sum / count) follow, up to total_bytes.  kgs_result_offset gives a
+ * table's offset inside the region; kgs_fetch_region copies the first nbytes of the region to
+ * the host in one transfer (blocking; use a pinned destination). */
+int kgs_result_region(kgs_handle h, void** d_ptr, size_t* exchange_bytes, size_t* total_bytes);
+int kgs_result_offset(kgs_handle h, int key_kind, int which, size_t* offset, size_t* nbytes);
+int kgs_fetch_region(kgs_handle h, void* host_dst, size_t nbytes);
 
 /* ---- the reference's own statistic, exactly ------------------------------------------- */
 /* GUS:77-80 and GUS:51 on a CSR layout: series s owns values[offsets[s] .. offsets[s+1]).

@@ -25,7 +25,7 @@ struct FinKind {
     const unsigned long long* sum;
     const uint32_t* mx;
     const uint32_t* head;
-    unsigned long long* o_count;         // window results
+    uint32_t* o_count;                   // window results
     unsigned long long* o_sum;
     uint32_t* o_max;
     double* o_mean;
@@ -274,7 +274,7 @@ __global__ void __launch_bounds__(CellLayout::NT) k_finalize_cells(const __grid_
             total += K.sum[pc0 + d];
             vmax = max(vmax, K.mx[pc0 + d]);
         }
-        K.o_count[c] = count;
+        K.o_count[c] = (uint32_t)count;
         K.o_sum[c] = total;
         K.o_max[c] = vmax;
         K.o_mean[c] = count ? __ddiv_rn((double)total, (double)count) : 0.0;

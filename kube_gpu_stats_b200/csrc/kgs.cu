@@ -39,7 +39,7 @@ struct KindState {
     unsigned long long* sum = nullptr;
     uint32_t* mx = nullptr;
     uint32_t* head = nullptr;
-    unsigned long long* o_count = nullptr;
+    uint32_t* o_count = nullptr;
     unsigned long long* o_sum = nullptr;
     uint32_t* o_max = nullptr;
     double* o_mean = nullptr;
@@ -74,7 +74,7 @@ struct kgs_ctx {
     uint32_t* big_list = nullptr;
     uint32_t* wide_list = nullptr;
     uint32_t big_cap = 0, wide_cap = 0;
-    size_t result_off = 0, result_bytes = 0;
+    size_t result_off = 0, result_bytes = 0, exchange_bytes = 0;
     uint64_t vals_cap = 0, vals_used = 0, accumulated = 0;
     uint32_t desc_cap = 0, desc_pool_base = 0, desc_priv_next = 0;
     uint64_t run_cap_override = 0;
@@ -455,11 +455,16 @@ int kgs_stats_begin(kgs_handle h, const kgs_window_spec* sp) {
     for (int k = 0; k < 3; ++k) {
         if (!(sp->key_mask & (1u << k))) continue;
         const uint64_t wc = (uint64_t)nk_in[k] * sp->n_windows;
-        lay[k].oc = off; off = align_up(off + wc * 8, 256);
+        // exchange part (what another shard needs): sum, percentiles, count, max = 24 B/cell at one percentile
         lay[k].os = off; off = align_up(off + wc * 8, 256);
-        lay[k].omean = off; off = align_up(off + wc * 8, 256);
         lay[k].opct = off; off = align_up(off + wc * 8 * sp->n_q, 256);
+        lay[k].oc = off; off = align_up(off + wc * 4, 256);
         lay[k].om = off; off = align_up(off + wc * 4, 256);
+    }
+    const size_t exchange_end = off;
+    for (int k = 0; k < 3; ++k) {   // means follow the exchange part (derivable from sum and count, never exchanged)
+        if (!(sp->key_mask & (1u << k))) continue;
+        lay[k].omean = off; off = align_up(off + (uint64_t)nk_in[k] * sp->n_windows * 8, 256);
     }
     const uint32_t big_cap = (uint32_t)(total_hint / kSmallMax * (W) + 16) * (uint32_t)n_kinds;
     const size_t big_off = off;
@@ -485,7 +490,7 @@ int kgs_stats_begin(kgs_handle h, const kgs_window_spec* sp) {
         K.cnt = reinterpret_cast<uint32_t*>(base + lay[k].cnt);
         K.mx = reinterpret_cast<uint32_t*>(base + lay[k].mx);
         K.head = pct ? reinterpret_cast<uint32_t*>(base + lay[k].head) : nullptr;
-        K.o_count = reinterpret_cast<unsigned long long*>(base + lay[k].oc);
+        K.o_count = reinterpret_cast<uint32_t*>(base + lay[k].oc);
         K.o_sum = reinterpret_cast<unsigned long long*>(base + lay[k].os);
         K.o_mean = reinterpret_cast<double*>(base + lay[k].omean);
         K.o_pct = reinterpret_cast<double*>(base + lay[k].opct);
@@ -493,6 +498,7 @@ int kgs_stats_begin(kgs_handle h, const kgs_window_spec* sp) {
     }
     h->result_off = clear_bytes;
     h->result_bytes = big_off - clear_bytes;
+    h->exchange_bytes = exchange_end - clear_bytes;
     h->big_list = reinterpret_cast<uint32_t*>(base + big_off);
     h->big_cap = big_cap;
     h->wide_list = reinterpret_cast<uint32_t*>(base + wide_off);
@@ -667,7 +673,7 @@ static int check_job_flags(kgs_handle h) {
     return KGS_OK;
 }
 
-int kgs_fetch_stats(kgs_handle h, int key_kind, uint64_t* count, uint64_t* sum, uint32_t* max, double* mean, double* pct) {
+int kgs_fetch_stats(kgs_handle h, int key_kind, uint32_t* count, uint64_t* sum, uint32_t* max, double* mean, double* pct) {
     if (!h) return KGS_ERR_ARG;
     if (!h->job_final) return fail(h, KGS_ERR_STATE, "kgs_fetch_stats: no finalized job");
     if (key_kind < 0 || key_kind > 2 || !(h->spec.key_mask & (1u << key_kind))) return fail(h, KGS_ERR_ARG, "key kind not part of this job");
@@ -678,7 +684,7 @@ int kgs_fetch_stats(kgs_handle h, int key_kind, uint64_t* count, uint64_t* sum, 
     const size_t wc = (size_t)K.n_keys * h->spec.n_windows;
     cudaStream_t st = h->compute;
     if (wc) {
-        if (count) KGS_CUDA(h, cudaMemcpyAsync(count, K.o_count, wc * 8, cudaMemcpyDeviceToHost, st));
+        if (count) KGS_CUDA(h, cudaMemcpyAsync(count, K.o_count, wc * 4, cudaMemcpyDeviceToHost, st));
         if (sum) KGS_CUDA(h, cudaMemcpyAsync(sum, K.o_sum, wc * 8, cudaMemcpyDeviceToHost, st));
         if (max) KGS_CUDA(h, cudaMemcpyAsync(max, K.o_max, wc * 4, cudaMemcpyDeviceToHost, st));
         if (mean) KGS_CUDA(h, cudaMemcpyAsync(mean, K.o_mean, wc * 8, cudaMemcpyDeviceToHost, st));
@@ -695,7 +701,7 @@ int kgs_result_device_ptr(kgs_handle h, int key_kind, int which, void** d_ptr, s
     const KindState& K = h->kind[key_kind];
     const size_t wc = (size_t)K.n_keys * h->spec.n_windows;
     switch (which) {
-        case 0: *d_ptr = K.o_count; *nbytes = wc * 8; break;
+        case 0: *d_ptr = K.o_count; *nbytes = wc * 4; break;
         case 1: *d_ptr = K.o_sum; *nbytes = wc * 8; break;
         case 2: *d_ptr = K.o_max; *nbytes = wc * 4; break;
         case 3: *d_ptr = K.o_mean; *nbytes = wc * 8; break;
@@ -705,11 +711,34 @@ int kgs_result_device_ptr(kgs_handle h, int key_kind, int which, void** d_ptr, s
     return KGS_OK;
 }
 
-int kgs_result_region(kgs_handle h, void** d_ptr, size_t* nbytes) {
-    if (!h || !d_ptr || !nbytes) return KGS_ERR_ARG;
+int kgs_result_region(kgs_handle h, void** d_ptr, size_t* exchange_bytes, size_t* total_bytes) {
+    if (!h || !d_ptr || !exchange_bytes || !total_bytes) return KGS_ERR_ARG;
     if (!h->job_final) return fail(h, KGS_ERR_STATE, "kgs_result_region: no finalized job");
     *d_ptr = static_cast<char*>(h->arena.p) + h->result_off;
-    *nbytes = h->result_bytes;
+    *exchange_bytes = h->exchange_bytes;
+    *total_bytes = h->result_bytes;
+    return KGS_OK;
+}
+
+int kgs_result_offset(kgs_handle h, int key_kind, int which, size_t* offset, size_t* nbytes) {
+    void* p = nullptr;
+    int rc = kgs_result_device_ptr(h, key_kind, which, &p, nbytes);
+    if (rc) return rc;
+    if (!offset) return KGS_ERR_ARG;
+    *offset = (size_t)(static_cast<char*>(p) - (static_cast<char*>(h->arena.p) + h->result_off));
+    return KGS_OK;
+}
+
+int kgs_fetch_region(kgs_handle h, void* host_dst, size_t nbytes) {
+    if (!h || (nbytes && !host_dst)) return KGS_ERR_ARG;
+    if (!h->job_final) return fail(h, KGS_ERR_STATE, "kgs_fetch_region: no finalized job");
+    if (nbytes > h->result_bytes) return fail(h, KGS_ERR_ARG, "kgs_fetch_region: more bytes than the result region holds");
+    KGS_CUDA(h, cudaSetDevice(h->device));
+    int rc;
+    if (h->spec.n_q && (rc = check_job_flags(h))) return rc;
+    if (nbytes)
+        KGS_CUDA(h, cudaMemcpyAsync(host_dst, static_cast<char*>(h->arena.p) + h->result_off, nbytes, cudaMemcpyDeviceToHost, h->compute));
+    KGS_CUDA(h, cudaStreamSynchronize(h->compute));
     return KGS_OK;
 }
 

@@ -153,7 +153,7 @@ class Engine:
         ncell = self._n_keys[kind] * sp.n_windows
         out = {}
         if 'count' in want:
-            out['count'] = np.empty(ncell, dtype=np.uint64)
+            out['count'] = np.empty(ncell, dtype=np.uint32)
         if 'sum' in want:
             out['sum'] = np.empty(ncell, dtype=np.uint64)
         if 'max' in want:
@@ -169,6 +169,35 @@ class Engine:
         self._ck(self._lib.kgs_fetch_stats(self._h, KIND_ID[kind], ptr('count'), ptr('sum'), ptr('max'),
                                            ptr('mean'), ptr('pct')))
         self._keep = []
+        if 'count' in out:
+            out['count'] = out['count'].astype(np.uint64)
+        return out
+
+    def fetch_all(self, kinds, with_mean=True):
+        """Every table of the given kinds with ONE device-to-host copy of the result region into a
+        pinned staging buffer.  Returns {kind: {count,sum,max,mean,pct}} as views of that buffer
+        (valid until the next fetch_all)."""
+        _, exchange, total = self.result_region()
+        nbytes = total if with_mean else exchange
+        if getattr(self, '_stage', None) is None or self._stage.size < nbytes:
+            self._stage = self.pinned(nbytes + 4096, dtype=np.uint8)
+        self._ck(self._lib.kgs_fetch_region(self._h, self._stage.ctypes.data, nbytes))
+        self._keep = []
+        sp = self._spec
+        out = {}
+        fields = (('count', 0, np.uint32), ('sum', 1, np.uint64), ('max', 2, np.uint32), ('pct', 4, np.float64))
+        for k in kinds:
+            ncell = self._n_keys[k] * sp.n_windows
+            t = {}
+            for name, which, dt in fields + ((('mean', 3, np.float64),) if with_mean else ()):
+                off, nb = C.c_size_t(), C.c_size_t()
+                self._ck(self._lib.kgs_result_offset(self._h, KIND_ID[k], which, C.byref(off), C.byref(nb)))
+                arr = self._stage[off.value:off.value + nb.value].view(dt)
+                t[name] = arr.reshape(sp.n_q, ncell) if name == 'pct' else arr
+            if not with_mean:
+                cnt = t['count'].astype(np.float64)
+                t['mean'] = np.divide(t['sum'].astype(np.float64), cnt, out=np.zeros(ncell), where=cnt > 0)
+            out[k] = t
         return out
 
     def window_stats(self, kinds=('pod',), **kw):
@@ -192,9 +221,10 @@ class Engine:
         return p.value, n.value
 
     def result_region(self):
-        p, n = C.c_void_p(), C.c_size_t()
-        self._ck(self._lib.kgs_result_region(self._h, C.byref(p), C.byref(n)))
-        return p.value, n.value
+        """(device address, exchange bytes, total bytes) of the finalized job's result region."""
+        p, e, t = C.c_void_p(), C.c_size_t(), C.c_size_t()
+        self._ck(self._lib.kgs_result_region(self._h, C.byref(p), C.byref(e), C.byref(t)))
+        return p.value, e.value, t.value
 
     # -- the reference's statistic ------------------------------------------------------
     def segmented_mean(self, values, offsets, mul=0.0, div=0.0):

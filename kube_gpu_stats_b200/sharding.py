@@ -83,7 +83,7 @@ class TableGather:
     def all_gather(self):
         import torch
         import torch.distributed as dist
-        ptr, nbytes = self.eng.result_region()
+        ptr, nbytes, _ = self.eng.result_region()      # the exchange part only: 16 + 8*n_q bytes per cell
         if ptr != self._src_ptr or self._src is None or self._src.numel() != nbytes:
             self._src = torch.as_tensor(_DeviceBytes(ptr, nbytes), device=torch.device('cuda', self.eng.device))
             self._dst = torch.empty(nbytes * self.world, dtype=torch.uint8, device=self._src.device)

@@ -137,6 +137,22 @@ def test_streamed_batches_equal_one_batch(engine, cfg1):
         assert_stats_equal(engine.fetch(k), oracle(tr, k, 'sm', tr.t0, 60, 60, 60, QS), what='streamed ' + k)
 
 
+def test_fetch_all_single_copy_equals_per_table_fetch(engine, cfg1):
+    """The one-transfer fetch of the result region (pinned staging) against the per-table fetch."""
+    tr = cfg1
+    engine.build_join(tr.keys, tr.pod_ids, tr.n_pods)
+    engine.ingest(tr.ts, tr.gpu_gid, tr.pid, tr.util)
+    engine.set_run_log_capacity(2 * 3 * (tr.n + 8 * 4096))
+    spec = engine.make_spec(kinds=('pod', 'gpu', 'node'), metric='mem', gpus_per_node=8, t0=tr.t0, step=60,
+                            n_windows=60, n_gpus=tr.n_gpus, n_nodes=tr.n_nodes, qs=QS, total_samples_hint=tr.n)
+    engine.window_stats_device(spec)
+    for with_mean in (True, False):
+        both = engine.fetch_all(('pod', 'gpu', 'node'), with_mean=with_mean)
+        for k in ('pod', 'gpu', 'node'):
+            assert_stats_equal({n: np.array(v) for n, v in both[k].items()}, engine.fetch(k), what='fetch_all ' + k)
+            assert_stats_equal(engine.fetch(k), oracle(tr, k, 'mem', tr.t0, 60, 60, 60, QS), what='mem ' + k)
+
+
 def test_state_and_argument_errors(engine, cfg1):
     from kube_gpu_stats_b200 import _ffi
     from kube_gpu_stats_b200.engine import KgsError
