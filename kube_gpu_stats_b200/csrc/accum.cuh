@@ -65,6 +65,7 @@ struct AccumParams {
     uint32_t log_per_warp;         //   [log_base + w*log_per_warp, +log_per_warp)
     uint32_t pool_base;            // shared overflow pool [pool_base, desc_cap), cursor ctl[0]
     uint32_t* ctl;                 // ctl[0] pool cursor, ctl[1] overflow flag
+    uint32_t agg_on;               // every cell index < 2^30: the per-CTA accumulator cache may be used
 };
 
 __device__ __forceinline__ uint64_t policy_evict_last() {
@@ -89,10 +90,39 @@ struct RunQueue {   // structure of arrays: lane l touching record l is conflict
         start[kQueueCap];
 };
 
+// Per-CTA accumulator cache for input that is far from collector order (the flat random stream of
+// BASELINE configs[2]): there a few hot cells (Zipf-sized pods) receive a large share of all
+// samples and their global atomics serialise on one L2 address each.  Runs are first folded into
+// this shared-memory table (open addressing, 4 probes, tag = cell*4 + kind + 1); the table is
+// written out with one global RED per occupied slot when the CTA ends.  A run whose cell finds no
+// slot goes to global memory directly, as always.
+constexpr int kAggSlots = 1024;
+struct AggTable {
+    unsigned long long sum[kAggSlots];
+    uint32_t tag[kAggSlots], cnt[kAggSlots], mx[kAggSlots];
+};
+
+__device__ __forceinline__ bool agg_add(AggTable& T, uint32_t tag, uint32_t c, uint32_t s, uint32_t m) {
+    const uint32_t h = (tag * 0x9E3779B1u) >> 22;
+#pragma unroll 1
+    for (uint32_t probe = 0; probe < 4; ++probe) {
+        const uint32_t slot = (h + probe) & (kAggSlots - 1);
+        uint32_t old = *reinterpret_cast<volatile uint32_t*>(&T.tag[slot]);
+        if (old == 0) old = atomicCAS(&T.tag[slot], 0u, tag);
+        if (old == 0 || old == tag) {
+            atomicAdd(&T.cnt[slot], c);
+            atomicAdd(&T.sum[slot], (unsigned long long)s);
+            atomicMax(&T.mx[slot], m);
+            return true;
+        }
+    }
+    return false;
+}
+
 // Retire one run: probe the join table once, then one RED per statistic and key kind and one
 // run-log descriptor per key kind (slots di .. di+nk-1).
 template <bool PCT>
-__device__ __forceinline__ void emit_run(const AccumParams& P, uint32_t g, uint32_t pid, uint32_t pane,
+__device__ __forceinline__ void emit_run(const AccumParams& P, AggTable* agg, uint32_t g, uint32_t pid, uint32_t pane,
                                          uint32_t c, uint32_t s, uint32_t m, uint32_t start, uint32_t di,
                                          bool log_ok) {
     const uint32_t node = fdiv(g, P.dgpn);
@@ -107,9 +137,11 @@ __device__ __forceinline__ void emit_run(const AccumParams& P, uint32_t g, uint3
         uint32_t cell = kInvalid;
         if (valid) {
             cell = key * P.n_panes + pane;
-            atomicAdd(P.cnt[kind] + cell, c);
-            atomicAdd(P.sum[kind] + cell, (unsigned long long)s);
-            atomicMax(P.mx[kind] + cell, m);
+            if (!(agg && agg_add(*agg, cell * 4 + kind + 1, c, s, m))) {
+                atomicAdd(P.cnt[kind] + cell, c);
+                atomicAdd(P.sum[kind] + cell, (unsigned long long)s);
+                atomicMax(P.mx[kind] + cell, m);
+            }
         }
         if (PCT && log_ok) {
             uint32_t next = 0;
@@ -141,8 +173,8 @@ __device__ __forceinline__ uint32_t reserve_log(const AccumParams& P, LogCursor&
 
 // Retire records [0, n_flush) of the warp's queue, one record per lane.
 template <bool PCT>
-__device__ __forceinline__ void flush_queue(const AccumParams& P, LogCursor& lc, const RunQueue& q, uint32_t n_flush,
-                                            uint32_t nk) {
+__device__ __forceinline__ void flush_queue(const AccumParams& P, AggTable* agg, LogCursor& lc, const RunQueue& q,
+                                            uint32_t n_flush, uint32_t nk) {
     const uint32_t lane = lane_id();
     for (uint32_t base = 0; base < n_flush; base += 32) {
         const uint32_t here = min(32u, n_flush - base);
@@ -151,7 +183,7 @@ __device__ __forceinline__ void flush_queue(const AccumParams& P, LogCursor& lc,
         if (PCT) di = reserve_log(P, lc, here * nk, log_ok) + lane * nk;
         const uint32_t r = base + lane;
         if (lane < here)
-            emit_run<PCT>(P, q.gid[r], q.pid[r], q.pane[r], q.cnt[r], q.sum[r], q.mx[r], q.start[r], di, log_ok);
+            emit_run<PCT>(P, agg, q.gid[r], q.pid[r], q.pane[r], q.cnt[r], q.sum[r], q.mx[r], q.start[r], di, log_ok);
     }
 }
 
@@ -188,15 +220,22 @@ __device__ __forceinline__ void load_oct(const AccumParams& P, uint32_t i0, bool
 template <bool PCT, bool PREFETCH>
 __global__ void __launch_bounds__(kAccumWarps * 32) k_accum(const __grid_constant__ AccumParams P) {
     __shared__ RunQueue queues[kAccumWarps];
+    __shared__ AggTable table;
     constexpr uint32_t kAll = 0xFFFFFFFFu;
+    if (P.agg_on) {
+        for (uint32_t i = threadIdx.x; i < kAggSlots; i += blockDim.x) {
+            table.tag[i] = 0; table.cnt[i] = 0; table.mx[i] = 0; table.sum[i] = 0;
+        }
+        __syncthreads();
+    }
+    AggTable* agg = nullptr;   // switched on (per warp) by the first tile that is mostly many-piece lanes
     const uint32_t lane = lane_id();
     RunQueue& Q = queues[threadIdx.x >> 5];
     const uint32_t nk = __popc(P.key_mask);
     const uint32_t n_tiles = (uint32_t)(((uint64_t)P.n + kTileSamples - 1) / kTileSamples);
     const uint32_t warp = blockIdx.x * kAccumWarps + (threadIdx.x >> 5);
     const uint64_t tb = (uint64_t)warp * P.tiles_per_warp;
-    if (tb >= n_tiles) return;
-    const uint32_t tile_begin = (uint32_t)tb;
+    const uint32_t tile_begin = (uint32_t)min((uint64_t)n_tiles, tb);
     const uint32_t tile_end = (uint32_t)min((uint64_t)n_tiles, tb + P.tiles_per_warp);
     const uint32_t full_tiles = P.n / kTileSamples;   // tiles below this index are complete
     uint32_t queued = 0;                               // warp-uniform
@@ -332,7 +371,9 @@ __global__ void __launch_bounds__(kAccumWarps * 32) k_accum(const __grid_constan
         // lanes with two or more boundaries: the pieces between the first and the last are retired
         // directly (rare in collector order; every lane in shuffled input, then 32 wide)
         const bool many = (bm & (bm - 1)) != 0;
-        if (__any_sync(kAll, many)) {
+        const uint32_t many_mask = __ballot_sync(kAll, many);
+        if (P.agg_on && __popc(many_mask) >= 16) agg = &table;
+        if (many_mask) {
             uint32_t nr = 0;
             if (many) {
 #pragma unroll
@@ -363,7 +404,7 @@ __global__ void __launch_bounds__(kAccumWarps * 32) k_accum(const __grid_constan
                     const bool last = (bm >> (j + 1)) == 0;
                     if (starts) {
                         if (open && pane[j - 1] != kInvalid) {
-                            emit_run<PCT>(P, cur.g[j - 1], cur.p[j - 1], pane[j - 1], rc, rs, rm, start0 + rstart, di, log_ok);
+                            emit_run<PCT>(P, agg, cur.g[j - 1], cur.p[j - 1], pane[j - 1], rc, rs, rm, start0 + rstart, di, log_ok);
                             di += nk;
                         }
                         open = !last;
@@ -379,7 +420,7 @@ __global__ void __launch_bounds__(kAccumWarps * 32) k_accum(const __grid_constan
         }
         __syncwarp();
         if (queued > 32) {   // retire all but the newest record (it may still grow)
-            flush_queue<PCT>(P, lc, Q, queued - 1, nk);
+            flush_queue<PCT>(P, agg, lc, Q, queued - 1, nk);
             __syncwarp();
             if (lane == 0) {
                 const uint32_t r = queued - 1;
@@ -391,7 +432,19 @@ __global__ void __launch_bounds__(kAccumWarps * 32) k_accum(const __grid_constan
         }
         if (PREFETCH) cur = nxt;
     }
-    flush_queue<PCT>(P, lc, Q, queued, nk);
+    flush_queue<PCT>(P, agg, lc, Q, queued, nk);
+    if (P.agg_on) {   // write the CTA's accumulator cache out: one RED per occupied slot and statistic
+        __syncthreads();
+        for (uint32_t i = threadIdx.x; i < kAggSlots; i += blockDim.x) {
+            const uint32_t tag = table.tag[i];
+            if (tag) {
+                const uint32_t kind = (tag - 1) & 3u, cell = (tag - 1) >> 2;
+                atomicAdd(P.cnt[kind] + cell, table.cnt[i]);
+                atomicAdd(P.sum[kind] + cell, table.sum[i]);
+                atomicMax(P.mx[kind] + cell, table.mx[i]);
+            }
+        }
+    }
 }
 
 }  // namespace kgs

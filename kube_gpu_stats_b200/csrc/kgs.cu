@@ -566,6 +566,9 @@ int kgs_stats_accumulate(kgs_handle h) {
     P.desc = static_cast<uint4*>(h->desc.p);
     P.desc_cap = h->desc_cap;
     P.ctl = h->ctl;
+    P.agg_on = 1;
+    for (int k = 0; k < 3; ++k)
+        if ((uint64_t)h->kind[k].n_keys * h->n_panes >= (1ull << 30)) P.agg_on = 0;
     cudaStream_t st = h->compute;
     KGS_CUDA(h, cudaStreamWaitEvent(st, B.ready, 0));
     // every warp owns a contiguous chunk of 256-sample tiles; ctas_per_sm resident CTAs of 8 warps
