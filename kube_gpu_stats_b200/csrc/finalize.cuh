@@ -35,6 +35,7 @@ struct FinKind {
 struct FinParams {
     FinKind kind[3];
     uint32_t n_kinds;                    // kinds actually present, packed at the front
+    int twin_pod, twin_gpu;              // kind slots of the pod and gpu tables when both exist and W == 1, else -1
     uint32_t total_cells;
     uint32_t n_windows, n_panes, W;
     uint32_t n_q;
@@ -225,14 +226,19 @@ __device__ __forceinline__ void select2(uint32_t base, uint32_t count, uint32_t 
 // Rule R5 for every requested percentile of one cell.
 template <class L>
 __device__ __forceinline__ void select_store(uint32_t base, const FinParams& P, const FinKind& K, uint32_t c,
-                                             uint32_t count, uint32_t vmax) {
+                                             uint32_t count, uint32_t vmax, uint32_t twin_cell = kInvalid) {
     const uint32_t ncell = K.n_keys * P.n_windows;
     for (uint32_t iq = 0; iq < P.n_q; ++iq) {
         uint32_t ilo, ihi, vlo, vhi;
         double wt;
         pct_ranks(P.q[iq], count, ilo, ihi, wt);
         select2<L>(base, count, vmax, ilo, ihi, vlo, vhi);
-        K.o_pct[(size_t)iq * ncell + c] = pct_lerp(vlo, vhi, wt);
+        const double res = pct_lerp(vlo, vhi, wt);
+        K.o_pct[(size_t)iq * ncell + c] = res;
+        if (twin_cell != kInvalid) {
+            const FinKind& G = P.kind[P.twin_gpu];
+            G.o_pct[(size_t)iq * (G.n_keys * P.n_windows) + twin_cell] = res;
+        }
     }
 }
 
@@ -301,8 +307,32 @@ __global__ void __launch_bounds__(CellLayout::NT) k_finalize_cells(const __grid_
         const uint32_t ncell = K.n_keys * P.n_windows;
         for (uint32_t iq = 0; iq < P.n_q; ++iq) K.o_pct[(size_t)iq * ncell + c] = nan_f64();
     }
-    add_cell<L>(base, P, K, pc0, fast);   // warp-synchronous: every lane takes part
-    if (fast) select_store<L>(base, P, K, c, (uint32_t)count, vmax);
+    // Twin cells.  With one process per GPU a (gpu, window) cell and its (pod, window) cell usually
+    // consist of the very same single run, and k_accum wrote that run's descriptors side by side
+    // (pod at index i, gpu at i + 1).  The pod cell's thread then selects once and stores the
+    // percentiles in both tables; the gpu cell's thread, seeing the mirror-image condition on the
+    // same immutable lists, does nothing.  Both sides test "my list is exactly this run" AND "the
+    // sibling's list is exactly the sibling descriptor", so they always agree.
+    bool work = fast;
+    uint32_t twin_cell = kInvalid;
+    if (fast && P.twin_pod >= 0) {
+        const uint32_t h = K.head[pc0];
+        if ((int)ks == P.twin_pod) {
+            const uint4 mine = __ldg(P.desc + (h - 1));
+            const uint4 sib = __ldg(P.desc + h);              // the gpu descriptor of the same run
+            if (mine.z == 0 && sib.z == 0 && sib.w != kInvalid && sib.x == mine.x && sib.y == mine.y &&
+                P.kind[P.twin_gpu].head[sib.w] == h + 1)
+                twin_cell = sib.w;
+        } else if ((int)ks == P.twin_gpu && h >= 2) {
+            const uint4 mine = __ldg(P.desc + (h - 1));
+            const uint4 sib = __ldg(P.desc + (h - 2));        // the pod descriptor of the same run
+            if (mine.z == 0 && sib.z == 0 && sib.w != kInvalid && sib.x == mine.x && sib.y == mine.y &&
+                P.kind[P.twin_pod].head[sib.w] == h - 1)
+                work = false;                                  // the pod cell's thread stores my percentiles
+        }
+    }
+    add_cell<L>(base, P, K, pc0, work);   // warp-synchronous: every lane takes part
+    if (work) select_store<L>(base, P, K, c, (uint32_t)count, vmax, twin_cell);
 }
 
 // The wide list: values up to 255 (u16 bins, 256 values); cells above 65 535 samples move on to

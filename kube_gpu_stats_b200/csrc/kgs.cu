@@ -627,6 +627,11 @@ int kgs_stats_finalize(kgs_handle h) {
     }
     for (uint32_t s = slot; s < 3; ++s) P.kind[s].cell_begin = 0xFFFFFFFFu;
     P.n_kinds = slot;
+    P.twin_pod = P.twin_gpu = -1;
+    if (h->W == 1 && (sp.key_mask & 3u) == 3u) {   // pod is slot 0 and gpu slot 1 when both are on
+        P.twin_pod = 0;
+        P.twin_gpu = 1;
+    }
     P.total_cells = cells;
     P.n_windows = sp.n_windows;
     P.n_panes = h->n_panes;
