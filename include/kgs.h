@@ -46,7 +46,8 @@ enum { KGS_METRIC_SM = 0, KGS_METRIC_MEM = 1, KGS_METRIC_FB = 2 };
 #define KGS_MAX_Q 8
 
 /* One windowed-statistics job.  Windows: pane p = (ts - t0) / step, window j covers panes
- * j .. j + width/step - 1 (width == step: tumbling; width a larger multiple: sliding).
+ * j .. j + width/step - 1 (width == step: tumbling; width a larger multiple: sliding; width shorter
+ * than step: sampled windows [t0 + j*step, t0 + j*step + width) with gaps between them).
  * Rules R1-R6 in oracle/window_stats.py are the specification. */
 typedef struct kgs_window_spec {
     uint32_t key_mask;       /* bit k set: produce the table for key kind k */
@@ -54,7 +55,7 @@ typedef struct kgs_window_spec {
     uint32_t gpus_per_node;  /* node = gpu_gid / gpus_per_node */
     uint32_t t0;             /* start of window 0, seconds */
     uint32_t step;           /* seconds between window starts (> 0) */
-    uint32_t width;          /* window width in seconds, a positive multiple of step */
+    uint32_t width;          /* window width in seconds: a positive multiple of step, or shorter than step */
     uint32_t n_windows;      /* windows per key */
     uint32_t n_gpus;         /* key domain of KGS_KEY_GPU  (gpu_gid  < n_gpus)  */
     uint32_t n_nodes;        /* key domain of KGS_KEY_NODE (node     < n_nodes) */

@@ -50,6 +50,7 @@ struct AccumParams {
     uint32_t t0;
     FastDiv dstep;
     uint32_t n_panes;
+    uint32_t step, win_len;  // win_len < step: sampled windows, only the first win_len seconds of a pane count
     FastDiv dgpn;
     uint32_t mshift, mmask;  // metric = (util >> mshift) & mmask
     uint32_t key_mask;
@@ -256,7 +257,8 @@ __global__ void __launch_bounds__(kAccumWarps * 32) k_accum(const __grid_constan
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
             const uint32_t pn = fdiv(cur.t[j] - P.t0, P.dstep);
-            const bool ok = (cur.t[j] >= P.t0) & (pn < P.n_panes) & ((uint32_t)j < lim);
+            bool ok = (cur.t[j] >= P.t0) & (pn < P.n_panes) & ((uint32_t)j < lim);
+            if (P.win_len < P.step) ok &= (cur.t[j] - P.t0) - pn * P.step < P.win_len;   // warp-uniform branch
             pane[j] = ok ? pn : kInvalid;
             v[j] = (cur.u[j] >> P.mshift) & P.mmask;
         }

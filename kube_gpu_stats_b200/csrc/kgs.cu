@@ -422,7 +422,8 @@ int kgs_stats_begin(kgs_handle h, const kgs_window_spec* sp) {
     if (!h || !sp) return KGS_ERR_ARG;
     if (sp->key_mask == 0 || sp->key_mask > 7) return fail(h, KGS_ERR_ARG, "key_mask must select 1..3 key kinds");
     if (sp->metric > KGS_METRIC_FB) return fail(h, KGS_ERR_ARG, "unknown metric");
-    if (sp->step == 0 || sp->width == 0 || sp->width % sp->step) return fail(h, KGS_ERR_ARG, "width must be a positive multiple of step");
+    if (sp->step == 0 || sp->width == 0 || (sp->width > sp->step && sp->width % sp->step))
+        return fail(h, KGS_ERR_ARG, "width must be a positive multiple of step, or shorter than step");
     if (sp->n_windows == 0) return fail(h, KGS_ERR_ARG, "n_windows is 0");
     if (sp->gpus_per_node == 0) return fail(h, KGS_ERR_ARG, "gpus_per_node is 0");
     if (sp->n_q > KGS_MAX_Q) return fail(h, KGS_ERR_ARG, "too many percentiles");
@@ -432,7 +433,7 @@ int kgs_stats_begin(kgs_handle h, const kgs_window_spec* sp) {
         return fail(h, KGS_ERR_ARG, "percentiles of fb_mib (16-bit domain) are not available yet; use mean/max");
     if ((sp->key_mask & 1) && !h->has_table) return fail(h, KGS_ERR_STATE, "per-pod statistics need kgs_build_join first");
     KGS_CUDA(h, cudaSetDevice(h->device));
-    const uint32_t W = sp->width / sp->step;
+    const uint32_t W = sp->width < sp->step ? 1u : sp->width / sp->step;
     const uint64_t n_panes = (uint64_t)sp->n_windows + W - 1;
     const uint32_t nk_in[3] = {h->n_pods, sp->n_gpus, sp->n_nodes};
     uint64_t total_hint = sp->total_samples_hint;
@@ -551,6 +552,8 @@ int kgs_stats_accumulate(kgs_handle h) {
     P.t0 = sp.t0;
     P.dstep = make_fastdiv(sp.step);
     P.n_panes = h->n_panes;
+    P.step = sp.step;
+    P.win_len = sp.width < sp.step ? sp.width : sp.step;
     P.dgpn = make_fastdiv(sp.gpus_per_node);
     P.mshift = sp.metric == KGS_METRIC_SM ? 0 : sp.metric == KGS_METRIC_MEM ? 8 : 16;
     P.mmask = sp.metric == KGS_METRIC_FB ? 0xFFFFu : 0xFFu;

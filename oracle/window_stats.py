@@ -19,6 +19,9 @@ R2  Join key = (gpu_gid // gpus_per_node, pid).  The table is built from
 R3  Pane p = (ts - t0) // step for t0 <= ts < t0 + P*step, P = n_windows + W - 1,
     W = width // step (width is a multiple of step; W == 1 is a tumbling window).
     Window j covers panes j .. j+W-1, i.e. [t0 + j*step, t0 + j*step + width).
+    A width SHORTER than step gives sampled windows with gaps (the instant vectors a PromQL
+    range query evaluates every step, gpu_util_stats.py:159): W = 1, window j =
+    [t0 + j*step, t0 + j*step + width), samples in the gaps are left out.
 R4  Cell (key, window): count, integer sum, max (0 when empty),
     mean = float(sum)/float(count), 0.0 when empty (gpu_util_stats.py:77-80).
 R5  Percentile q in [0,1] over the cell's sorted values v[0..n-1] (Hyndman-Fan
@@ -76,8 +79,9 @@ def probe_py(table, gpu_gid, pid, gpus_per_node):
 def window_stats_py(ts, gpu_gid, pid, util, table, *, key_kind, metric, gpus_per_node,
                     t0, step, width, n_windows, n_keys, qs=()):
     """R1-R6 with plain loops.  Returns dict of lists indexed [key*n_windows + j]."""
-    W = width // step
-    assert W >= 1 and W * step == width
+    sparse = width < step
+    W = 1 if sparse else width // step
+    assert sparse or W * step == width
     n_panes = n_windows + W - 1
     panes = {}                                   # (key, pane) -> list of values
     for i in range(len(ts)):
@@ -86,6 +90,8 @@ def window_stats_py(ts, gpu_gid, pid, util, table, *, key_kind, metric, gpus_per
             continue
         p = (t - t0) // step
         if p >= n_panes:
+            continue
+        if sparse and (t - t0) - p * step >= width:
             continue
         g = int(gpu_gid[i])
         if key_kind == KEY_GPU:
@@ -172,8 +178,9 @@ def window_stats_np(ts, gpu_gid, pid, util, keys, pod_ids, *, key_kind, metric, 
     ts = np.asarray(ts, dtype=np.uint32)
     gpu_gid = np.asarray(gpu_gid, dtype=np.uint32)
     util = np.asarray(util, dtype=np.uint32)
-    W = width // step
-    assert W >= 1 and W * step == width
+    sparse = width < step
+    W = 1 if sparse else width // step
+    assert sparse or W * step == width
     n_panes = n_windows + W - 1
     ncell = n_keys * n_windows
     if key_kind == KEY_GPU:
@@ -185,6 +192,8 @@ def window_stats_np(ts, gpu_gid, pid, util, keys, pod_ids, *, key_kind, metric, 
     t = ts.astype(np.int64) - int(t0)
     pane = np.floor_divide(t, int(step))
     ok = (t >= 0) & (pane < n_panes) & (key < n_keys)
+    if sparse:
+        ok &= (t - pane * int(step)) < int(width)
     key, pane = key[ok], pane[ok]
     val = metric_of(util[ok], metric).astype(np.int64)
     count = np.zeros(ncell, dtype=np.int64)

@@ -91,6 +91,24 @@ def test_sliding_windows(engine, cfg1):
     check(engine, cfg1, ('pod', 'gpu', 'node'), 'sm', cfg1.t0, 10, 50, 356, (0.5, 0.99))
 
 
+def test_sampled_windows_and_promql_instants(engine, cfg1):
+    """width < step (R3): the instants a PromQL range query evaluates.  Also the avg-by-pod emulation
+    of gpu_util_stats.py:159 against the host rendering used for the replay fixtures."""
+    check(engine, cfg1, ('pod', 'gpu', 'node'), 'sm', cfg1.t0 + 7, 60, 5, 59, (0.5, 0.95))
+    from kube_gpu_stats_b200 import promql, replay
+    tr = synth.config(2, scale=0.01)
+    engine.build_join(tr.keys, tr.pod_ids, tr.n_pods)
+    engine.ingest(tr.ts, tr.gpu_gid, tr.pid, tr.util)
+    step, n_steps = 300, 12
+    table = promql.instant_by_pod(engine, tr.t0, step, n_steps)
+    node_name, pod_name = replay.names(tr)
+    labels = [{'kubernetes_io_hostname': node_name[int(tr.pod_node[p])], 'nvidia_gpu_type': 'P40', 'pod_name': pod_name[p]}
+              for p in range(tr.n_pods)]
+    got = promql.matrix_json(table, tr.t0, step, n_steps, labels)
+    want = replay.prometheus_answers(tr, step)['sm_util']
+    assert got == want
+
+
 def test_whole_range_big_cells(engine, cfg1):
     """One window over the hour: the node cell holds 230 400 samples (> 65 535: the u32-bin path)."""
     check(engine, cfg1, ('pod', 'gpu', 'node'), 'sm', cfg1.t0, 3600, 3600, 1, QS)

@@ -135,3 +135,17 @@ def test_synth_configs_shape():
     # pods are node-local (a pod is bound to one node, who_use_gpu.py:33)
     node_of_key = (c2.keys >> np.uint64(32)).astype(np.int64)
     assert np.array_equal(c2.pod_node[c2.pod_ids], node_of_key)
+
+
+def test_sampled_windows_rule():
+    """R3, width < step: only the first `width` seconds of every step count (PromQL instants)."""
+    ts = np.array([100, 101, 104, 105, 109, 110, 111, 115], dtype=np.uint32)
+    gid = np.zeros(8, dtype=np.uint32)
+    util = np.array([1, 2, 3, 4, 5, 6, 7, 8], dtype=np.uint32)
+    kw = dict(key_kind=ws.KEY_GPU, metric=0, gpus_per_node=8, t0=100, step=5, width=2, n_windows=3, n_keys=1, qs=(0.5,))
+    got = ws.window_stats_np(ts, gid, gid, util, np.zeros(0, np.uint64), np.zeros(0, np.uint32), **kw)
+    # windows [100,102) [105,107) [110,112): values {1,2} {4} {6,7}
+    assert got['count'].tolist() == [2, 1, 2] and got['sum'].tolist() == [3, 4, 13] and got['max'].tolist() == [2, 4, 7]
+    assert got['pct'][0].tolist() == [1.5, 4.0, 6.5]
+    py = ws.window_stats_py(ts, gid, gid, util, {}, **kw)
+    assert_stats_equal({k: np.array(v) for k, v in py.items()}, got, 'sampled')
