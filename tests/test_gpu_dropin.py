@@ -80,3 +80,30 @@ def test_main_prints_reference_format(built_lib, capsys):
         gus.set_transport(None)
     out = capsys.readouterr().out
     assert out == g['expect']['get_pod_by_servers']['dump'] + '\n' + '\n'.join(g['expect']['stats_pod_results']['printed']) + '\n'
+
+
+def test_pmon_text_to_pinned_columns_to_tables(engine):
+    """Collector text -> pinned SoA columns -> join + per-GPU table, against the oracle."""
+    from kube_gpu_stats_b200 import ingest
+    from oracle import window_stats as ws
+    rng = np.random.default_rng(4)
+    cols = ingest.SampleColumns(engine, 4096)
+    for t in range(100):
+        rows = ['# gpu pid type sm mem enc dec fb command']
+        for g in range(4):
+            rows.append('%5d %8d C %5d %5d - - %6d python' % (g, 500 + g, rng.integers(0, 101), rng.integers(0, 101), rng.integers(0, 40000)))
+        cols.append_pmon('\n'.join(rows), ts=1000 + t, node_id=3, gpus_per_node=8)
+    ts, gid, pid, util = cols.views()
+    assert cols.n == 400 and gid.min() == 24 and gid.max() == 27
+    keys = np.array([(3 << 32) | 500, (3 << 32) | 502], dtype=np.uint64)
+    pods = np.array([0, 1], dtype=np.uint32)
+    engine.build_join(keys, pods, 2)
+    engine.ingest(ts, gid, pid, util)
+    got = engine.window_stats(kinds=('pod', 'gpu'), metric='sm', t0=1000, step=20, n_windows=5, n_gpus=32, n_nodes=4, qs=(0.5,))
+    for kind, kid, nk in (('pod', ws.KEY_POD, 2), ('gpu', ws.KEY_GPU, 32)):
+        want = ws.window_stats_np(ts, gid, pid, util, keys, pods, key_kind=kid, metric=0, gpus_per_node=8, t0=1000,
+                                  step=20, width=20, n_windows=5, n_keys=nk, qs=(0.5,))
+        for f in ('count', 'sum', 'max'):
+            np.testing.assert_array_equal(np.asarray(got[kind][f]).astype(np.uint64), want[f].astype(np.uint64))
+        np.testing.assert_array_equal(bits(got[kind]['mean']), bits(want['mean']))
+        np.testing.assert_array_equal(bits(got[kind]['pct']), bits(want['pct']))
