@@ -153,7 +153,8 @@ int kgs_result_device_ptr(kgs_handle h, int key_kind, int which, void** d_ptr, s
  * count, max of every kind, 16 + 8*n_q bytes per cell - so ONE collective can move them all; the
  * mean tables (derivable: sum / count) follow, up to total_bytes.  kgs_result_offset gives a
  * table's offset inside the region; kgs_fetch_region copies the first nbytes of the region to
- * the host in one transfer (blocking; use a pinned destination). */
+ * the host in one transfer (blocking; use a pinned destination).  Consecutive jobs alternate between
+ * two result regions, so job i's region stays intact while job i+1 is computed (not job i+2). */
 int kgs_result_region(kgs_handle h, void** d_ptr, size_t* exchange_bytes, size_t* total_bytes);
 int kgs_result_offset(kgs_handle h, int key_kind, int which, size_t* offset, size_t* nbytes);
 int kgs_fetch_region(kgs_handle h, void* host_dst, size_t nbytes);

@@ -78,6 +78,7 @@ struct kgs_ctx {
     uint64_t vals_cap = 0, vals_used = 0, accumulated = 0;
     uint32_t desc_cap = 0, desc_pool_base = 0, desc_priv_next = 0;
     uint64_t run_cap_override = 0;
+    uint64_t job_seq = 0;
     bool accum_prefetch = false;   // register double-buffering of the next tile: 109 vs 78 registers
     int accum_ctas_per_sm = 3;     // resident CTAs of 8 warps per SM at 78 registers
     // measurement
@@ -467,6 +468,11 @@ int kgs_stats_begin(kgs_handle h, const kgs_window_spec* sp) {
         if (!(sp->key_mask & (1u << k))) continue;
         lay[k].omean = off; off = align_up(off + (uint64_t)nk_in[k] * sp->n_windows * 8, 256);
     }
+    // two result slots, used by alternate jobs: a caller may still be moving job i's tables (to the
+    // host, to other GPUs) while job i+1 is being computed
+    const size_t result_area = off - clear_bytes;
+    off += result_area;
+    const size_t slot_shift = (h->job_seq++ & 1) ? result_area : 0;
     const uint32_t big_cap = (uint32_t)(total_hint / kSmallMax * (W) + 16) * (uint32_t)n_kinds;
     const size_t big_off = off;
     off = align_up(off + (size_t)big_cap * 8, 256);
@@ -491,14 +497,14 @@ int kgs_stats_begin(kgs_handle h, const kgs_window_spec* sp) {
         K.cnt = reinterpret_cast<uint32_t*>(base + lay[k].cnt);
         K.mx = reinterpret_cast<uint32_t*>(base + lay[k].mx);
         K.head = pct ? reinterpret_cast<uint32_t*>(base + lay[k].head) : nullptr;
-        K.o_count = reinterpret_cast<uint32_t*>(base + lay[k].oc);
-        K.o_sum = reinterpret_cast<unsigned long long*>(base + lay[k].os);
-        K.o_mean = reinterpret_cast<double*>(base + lay[k].omean);
-        K.o_pct = reinterpret_cast<double*>(base + lay[k].opct);
-        K.o_max = reinterpret_cast<uint32_t*>(base + lay[k].om);
+        K.o_count = reinterpret_cast<uint32_t*>(base + slot_shift + lay[k].oc);
+        K.o_sum = reinterpret_cast<unsigned long long*>(base + slot_shift + lay[k].os);
+        K.o_mean = reinterpret_cast<double*>(base + slot_shift + lay[k].omean);
+        K.o_pct = reinterpret_cast<double*>(base + slot_shift + lay[k].opct);
+        K.o_max = reinterpret_cast<uint32_t*>(base + slot_shift + lay[k].om);
     }
-    h->result_off = clear_bytes;
-    h->result_bytes = big_off - clear_bytes;
+    h->result_off = clear_bytes + slot_shift;
+    h->result_bytes = result_area;
     h->exchange_bytes = exchange_end - clear_bytes;
     h->big_list = reinterpret_cast<uint32_t*>(base + big_off);
     h->big_cap = big_cap;

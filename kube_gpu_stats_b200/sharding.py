@@ -71,25 +71,69 @@ class _DeviceBytes:
 
 
 class TableGather:
-    """all_gather of the job's whole result region (every table of every key kind) in ONE NCCL
-    collective, issued on the stream that is current when all_gather() is called."""
+    """all_gather of the job's exchange region (sum, pct, count, max of every key kind) in ONE NCCL
+    collective.
+
+    ``all_gather()`` issues it on the stream that is current (serial with the kernels).
+    ``all_gather_async(stream)`` issues it on a side stream once the library's compute stream has
+    finished the job, so it overlaps the NEXT job's kernels: consecutive jobs write alternate result
+    regions (include/kgs.h), and a region is only reused two jobs later, by which time the compute
+    stream has been made to wait for the collective that read it.  ``wait()`` joins the side stream.
+    """
 
     def __init__(self, engine, kinds, world):
         self.eng, self.kinds, self.world = engine, kinds, world
-        self._src_ptr = None
-        self._src = None
-        self._dst = None
+        self._views = {}          # region address -> (src alias, dst buffer, done event)
+        self._side = None
+        self._last = None         # region of the most recent job
+
+    def _buffers(self):
+        import torch
+        ptr, nbytes, _ = self.eng.result_region()      # the exchange part only: 16 + 8*n_q bytes per cell
+        v = self._views.get(ptr)
+        if v is None or v[0].numel() != nbytes:
+            dev = torch.device('cuda', self.eng.device)
+            src = torch.as_tensor(_DeviceBytes(ptr, nbytes), device=dev)
+            v = (src, torch.empty(nbytes * self.world, dtype=torch.uint8, device=dev), torch.cuda.Event())
+            self._views[ptr] = v
+        self._last = ptr
+        return v
 
     def all_gather(self):
+        import torch.distributed as dist
+        src, dst, _ = self._buffers()
+        dist.all_gather_into_tensor(dst, src)
+        return dst
+
+    def all_gather_async(self, compute_stream):
         import torch
         import torch.distributed as dist
-        ptr, nbytes, _ = self.eng.result_region()      # the exchange part only: 16 + 8*n_q bytes per cell
-        if ptr != self._src_ptr or self._src is None or self._src.numel() != nbytes:
-            self._src = torch.as_tensor(_DeviceBytes(ptr, nbytes), device=torch.device('cuda', self.eng.device))
-            self._dst = torch.empty(nbytes * self.world, dtype=torch.uint8, device=self._src.device)
-            self._src_ptr = ptr
-        dist.all_gather_into_tensor(self._dst, self._src)
-        return self._dst
+        if self._side is None:
+            self._side = torch.cuda.Stream(device=torch.device('cuda', self.eng.device))
+        src, dst, done = self._buffers()
+        self._side.wait_stream(compute_stream)          # the job's finalize kernels
+        with torch.cuda.stream(self._side):
+            dist.all_gather_into_tensor(dst, src)
+            done.record(self._side)
+        return dst
+
+    def before_next_job(self, compute_stream):
+        """Call before starting a job: its result region was last read by the collective issued two
+        jobs ago; make the compute stream wait for that one (normally long finished)."""
+        for ptr, (_, _, done) in self._views.items():
+            if ptr != self._last:                       # the next job writes the OTHER region
+                compute_stream.wait_event(done)
+
+    def join(self, compute_stream):
+        """Order everything issued on the side stream before whatever comes next on compute_stream."""
+        if self._side is not None:
+            compute_stream.wait_stream(self._side)
+
+    def wait(self):
+        import torch
+        if self._side is not None:
+            torch.cuda.current_stream().wait_stream(self._side)
+            self._side.synchronize()
 
 
 # ---- host-memory variant of the exchange (any torch.distributed backend, e.g. gloo) -------------
