@@ -304,6 +304,15 @@ def run_b200(args):
                 traffic = None
         # bounded CPU baseline on the same trace
         cpu = None
+        crossover = None
+        if not args.no_cpu_baseline and world == 1:
+            # trace size from which the GPU path, transfers included, beats the CPU path (north_star)
+            sys.path.insert(0, os.path.join(ROOT, 'tools'))
+            import crossover as xo
+            xrows, xn = xo.measure(sizes=(8, 32, 128, 512, 2048, 8192))
+            crossover = {'gpu_faster_from_samples': xn,
+                         'points': [{'samples': n_, 'gpu_e2e_ms': g_ * 1e3, 'cpu_ms': c_ * 1e3 if c_ else None} for n_, g_, c_ in xrows],
+                         'note': 'GPU = table build + pinned H2D + join + 3 tables with p95 + D2H; CPU = pure-Python oracle, 1 core'}
         if not args.no_cpu_baseline:
             rate = cpu_rate_probe(tr)
             nodes = int(max(1, min(n_nodes, rate * 15.0 / (8 * 3600))))
@@ -330,6 +339,7 @@ def run_b200(args):
                          'step_kernel_ms': {k: v[0] / prof_steps for k, v in ktimes.items() if v[1]},
                          'accum_share_of_step_kernels': (acc_ms / prof_steps) / step_kernel_ms if step_kernel_ms else None},
             'cpu_baseline': cpu,
+            'crossover': crossover,
         }
         # keep the result honest: the last e2e step's tables must not be empty
         assert int(res['node']['count'].sum()) == n, 'e2e tables do not cover the batch'
