@@ -87,6 +87,12 @@ int kgs_free_pinned(kgs_handle h, void* p);
  * so the copy of batch i+1 overlaps the kernels still reading batch i. */
 int kgs_ingest(kgs_handle h, const uint32_t* ts, const uint32_t* gpu_gid, const uint32_t* pid,
                const uint32_t* util, uint64_t n);
+/* Build one large resident batch from several host pieces (a shard that fits HBM but not one pinned
+ * buffer): reserve makes an empty batch of the given capacity resident, append copies n more samples
+ * behind those already there (asynchronous, same lifetime rule as kgs_ingest). */
+int kgs_batch_reserve(kgs_handle h, uint64_t capacity);
+int kgs_batch_append(kgs_handle h, const uint32_t* ts, const uint32_t* gpu_gid, const uint32_t* pid,
+                     const uint32_t* util, uint64_t n);
 /* Same, for columns that already live in this device's memory, 32-byte aligned (no copy is made;
  * the caller keeps them alive and unchanged until the work that reads them has been synchronised). */
 int kgs_adopt_device_batch(kgs_handle h, const uint32_t* d_ts, const uint32_t* d_gpu_gid,

@@ -53,6 +53,8 @@ def load(path=LIB_PATH):
         'kgs_alloc_pinned': [H, C.c_size_t, C.POINTER(vp)],
         'kgs_free_pinned': [H, vp],
         'kgs_ingest': [H, vp, vp, vp, vp, C.c_uint64],
+        'kgs_batch_reserve': [H, C.c_uint64],
+        'kgs_batch_append': [H, vp, vp, vp, vp, C.c_uint64],
         'kgs_adopt_device_batch': [H, vp, vp, vp, vp, C.c_uint64],
         'kgs_build_join': [H, vp, vp, C.c_uint64, C.c_uint32],
         'kgs_probe': [H, C.c_uint32, vp],

@@ -296,6 +296,44 @@ int kgs_ingest(kgs_handle h, const uint32_t* ts, const uint32_t* gpu_gid, const 
     return KGS_OK;
 }
 
+int kgs_batch_reserve(kgs_handle h, uint64_t capacity) {
+    if (!h) return KGS_ERR_ARG;
+    if (capacity >= 0xFFFFFC00ull) return fail(h, KGS_ERR_ARG, "kgs_batch_reserve: a batch holds fewer than 2^32 - 1024 samples");
+    KGS_CUDA(h, cudaSetDevice(h->device));
+    const int b = (h->cur + 1) & 1;
+    Batch& B = h->batch[b];
+    KGS_CUDA(h, cudaStreamSynchronize(h->compute));   // the slot may be freed and reallocated
+    KGS_CUDA(h, cudaStreamSynchronize(h->copy));
+    for (int c = 0; c < 4; ++c) {
+        int rc = reserve(h, B.col[c], capacity * 4 + 64);
+        if (rc) return rc;
+        B.ptr[c] = static_cast<const uint32_t*>(B.col[c].p);
+    }
+    B.n = 0;
+    KGS_CUDA(h, cudaEventRecord(B.ready, h->copy));
+    h->cur = b;
+    return KGS_OK;
+}
+
+int kgs_batch_append(kgs_handle h, const uint32_t* ts, const uint32_t* gpu_gid, const uint32_t* pid,
+                     const uint32_t* util, uint64_t n) {
+    if (!h || (n && (!ts || !gpu_gid || !pid || !util))) return fail(h, KGS_ERR_ARG, "kgs_batch_append: null column");
+    if (h->cur < 0) return fail(h, KGS_ERR_STATE, "kgs_batch_append: no resident batch (call kgs_batch_reserve)");
+    KGS_CUDA(h, cudaSetDevice(h->device));
+    Batch& B = h->batch[h->cur];
+    const uint32_t* src[4] = {ts, gpu_gid, pid, util};
+    for (int c = 0; c < 4; ++c) {
+        if (B.col[c].p != B.ptr[c] || (B.n + n) * 4 + 64 > B.col[c].cap)
+            return fail(h, KGS_ERR_CAPACITY, "kgs_batch_append: beyond the capacity given to kgs_batch_reserve");
+    }
+    // kernels queued on the compute stream may be reading the part already there; appending does not touch it
+    for (int c = 0; c < 4; ++c)
+        if (n) KGS_CUDA(h, cudaMemcpyAsync(static_cast<uint32_t*>(B.col[c].p) + B.n, src[c], n * 4, cudaMemcpyHostToDevice, h->copy));
+    B.n += n;
+    KGS_CUDA(h, cudaEventRecord(B.ready, h->copy));
+    return KGS_OK;
+}
+
 int kgs_adopt_device_batch(kgs_handle h, const uint32_t* d_ts, const uint32_t* d_gpu_gid,
                            const uint32_t* d_pid, const uint32_t* d_util, uint64_t n) {
     if (!h || (n && (!d_ts || !d_gpu_gid || !d_pid || !d_util))) return fail(h, KGS_ERR_ARG, "kgs_adopt_device_batch: null column");

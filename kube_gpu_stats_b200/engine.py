@@ -88,6 +88,18 @@ class Engine:
         self._ck(self._lib.kgs_ingest(self._h, *[c.ctypes.data for c in cols], n))
         self.n_resident = n
 
+    def batch_reserve(self, capacity):
+        """Make an empty batch of the given capacity resident; fill it with batch_append."""
+        self._ck(self._lib.kgs_batch_reserve(self._h, int(capacity)))
+        self.n_resident = 0
+
+    def batch_append(self, ts, gpu_gid, pid, util):
+        cols = [_u32(ts), _u32(gpu_gid), _u32(pid), _u32(util)]
+        n = len(cols[0])
+        self._keep.append(cols)
+        self._ck(self._lib.kgs_batch_append(self._h, *[c.ctypes.data for c in cols], n))
+        self.n_resident += n
+
     def adopt_device_batch(self, d_ts, d_gid, d_pid, d_util, n):
         self._ck(self._lib.kgs_adopt_device_batch(self._h, int(d_ts), int(d_gid), int(d_pid), int(d_util), int(n)))
         self.n_resident = int(n)
