@@ -262,7 +262,17 @@ __global__ void __launch_bounds__(kAccumWarps * 32) k_accum(const __grid_constan
             pane[j] = ok ? pn : kInvalid;
             v[j] = (cur.u[j] >> P.mshift) & P.mmask;
         }
-        if (PCT) {   // value log, same order as the input (u8 metrics)
+        if (PCT && P.mmask > 0xFFu) {   // value log of a 16-bit metric (fb_mib): 2 B/sample (warp-uniform branch)
+            uint16_t* dst = reinterpret_cast<uint16_t*>(P.vals) + P.vals_base + i0;
+            if (full) {
+                st_keep_v4(dst, make_uint4(v[0] | (v[1] << 16), v[2] | (v[3] << 16), v[4] | (v[5] << 16), v[6] | (v[7] << 16)),
+                           policy_evict_last());
+            } else {
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                    if (i0 + j < P.n) dst[j] = (uint16_t)v[j];
+            }
+        } else if (PCT) {   // value log, same order as the input (u8 metrics): 1 B/sample
             uint8_t* dst = P.vals + P.vals_base + i0;
             if (full) {
                 st_keep_v2(dst, v[0] | (v[1] << 8) | (v[2] << 16) | (v[3] << 24),

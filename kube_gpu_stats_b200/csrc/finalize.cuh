@@ -14,6 +14,10 @@
 #pragma once
 #include "common.cuh"
 
+#ifndef KGS_MAX_Q
+#define KGS_MAX_Q 8
+#endif
+
 namespace kgs {
 
 constexpr uint32_t kSmallMax = 65535;  // largest cell the u16-bin histogram can count
@@ -46,6 +50,7 @@ struct FinParams {
     uint32_t* big_list;                  // pairs left to k_finalize_big
     uint32_t* ctl;                       // ctl[2] = big_list length, ctl[3] = wide_list length
     uint32_t wide_cap, big_cap;
+    uint32_t u16;                        // 16-bit metric: the value log holds 2 B/sample, cells go to k_finalize_u16
 };
 
 __device__ __forceinline__ double nan_f64() { return __longlong_as_double(0x7FF8000000000000ll); }
@@ -288,7 +293,7 @@ __global__ void __launch_bounds__(CellLayout::NT) k_finalize_cells(const __grid_
     // a run log that overflowed holds incomplete lists: the host reports the error, skip selection
     if (P.n_q == 0 || P.ctl[1]) return;
     const FinKind& K = P.kind[ks];
-    const bool fast = live && count > 0 && count <= kSmallMax && vmax < (uint32_t)L::BINS;
+    const bool fast = live && count > 0 && count <= kSmallMax && vmax < (uint32_t)L::BINS && !P.u16;
     const bool later = live && count > 0 && !fast;
     const uint32_t later_mask = __ballot_sync(0xFFFFFFFFu, later);   // one atomic per warp
     if (later_mask) {
@@ -417,6 +422,80 @@ __global__ void __launch_bounds__(128) k_finalize_big(const __grid_constant__ Fi
                 }
                 K.o_pct[(size_t)iq * ncell + c] = pct_lerp(vlo, vhi, w);
             }
+        }
+        __syncwarp();
+    }
+}
+
+// 16-bit metrics (fb_mib): a two-digit radix select, one warp per cell.  Pass 1 counts the HIGH
+// byte of every value of the cell (256 u32 bins in shared memory) and finds, for each wanted rank,
+// the high byte that holds it; pass 2 counts the LOW byte of the values with that high byte and
+// finishes the selection.  Ranks that share a high byte share the second pass.  Consumes the wide
+// list (k_finalize_cells sends every non-empty cell there when P.u16 is set).
+__global__ void __launch_bounds__(128) k_finalize_u16(const __grid_constant__ FinParams P) {
+    __shared__ uint32_t hist_all[4][256];
+    const uint32_t lane = lane_id(), wib = threadIdx.x >> 5;
+    uint32_t* hist = hist_all[wib];
+    const uint16_t* vals = reinterpret_cast<const uint16_t*>(P.vals);
+    const uint32_t n_cells = P.ctl[1] ? 0u : min(P.ctl[3], P.wide_cap);
+    const uint32_t warps = gridDim.x * 4;
+    for (uint32_t it = blockIdx.x * 4 + wib; it < n_cells; it += warps) {
+        const FinKind& K = P.kind[P.wide_list[2 * it]];
+        const uint32_t c = P.wide_list[2 * it + 1];
+        const uint32_t key = c / P.n_windows, pc0 = key * P.n_panes + (c - key * P.n_windows);
+        const uint32_t ncell = K.n_keys * P.n_windows;
+        const uint32_t count = K.o_count[c];
+        // digit pass over the cell's runs: `want` < 256 restricts to values with that high byte
+        auto digit_pass = [&](uint32_t want) {
+            for (uint32_t b = lane; b < 256; b += 32) hist[b] = 0;
+            __syncwarp();
+            for (uint32_t d = 0; d < P.W; ++d) {
+                uint32_t at = K.head[pc0 + d];
+                while (at) {   // warp-uniform: every lane reads the same descriptor
+                    const uint4 r = __ldg(P.desc + (at - 1));
+                    for (uint32_t o = lane; o < r.y; o += 32) {
+                        const uint32_t v = vals[(uint64_t)r.x + o];
+                        if (want > 255u) atomicAdd(hist + (v >> 8), 1u);
+                        else if ((v >> 8) == want) atomicAdd(hist + (v & 0xFFu), 1u);
+                    }
+                    at = r.z;
+                }
+            }
+            __syncwarp();
+        };
+        // rank -> (digit, rank inside that digit's bin); every lane computes the same answer
+        auto locate = [&](uint32_t rank, uint32_t& digit, uint32_t& inside) {
+            uint32_t cum = 0;
+            digit = 255; inside = 0;
+            for (uint32_t b = 0; b < 256; ++b) {
+                const uint32_t cb = hist[b];
+                if (rank - cum < cb) { digit = b; inside = rank - cum; break; }
+                cum += cb;
+            }
+        };
+        uint32_t hi_digit[2 * KGS_MAX_Q], hi_inside[2 * KGS_MAX_Q];
+        double wq[KGS_MAX_Q];
+        digit_pass(0xFFFFu);
+        for (uint32_t iq = 0; iq < P.n_q; ++iq) {
+            uint32_t ilo, ihi;
+            pct_ranks(P.q[iq], count, ilo, ihi, wq[iq]);
+            locate(ilo, hi_digit[2 * iq], hi_inside[2 * iq]);
+            locate(ihi, hi_digit[2 * iq + 1], hi_inside[2 * iq + 1]);
+        }
+        uint32_t have = 0xFFFFu;   // high byte the second-pass histogram currently holds
+        for (uint32_t iq = 0; iq < P.n_q; ++iq) {
+            uint32_t val[2];
+            for (int e = 0; e < 2; ++e) {
+                const uint32_t hd = hi_digit[2 * iq + e];
+                if (hd != have) {
+                    digit_pass(hd);
+                    have = hd;
+                }
+                uint32_t ld, unused;
+                locate(hi_inside[2 * iq + e], ld, unused);
+                val[e] = (hd << 8) | ld;
+            }
+            if (lane == 0) K.o_pct[(size_t)iq * ncell + c] = pct_lerp(val[0], val[1], wq[iq]);
         }
         __syncwarp();
     }

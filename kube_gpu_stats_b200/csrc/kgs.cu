@@ -468,8 +468,6 @@ int kgs_stats_begin(kgs_handle h, const kgs_window_spec* sp) {
     if (sp->n_q > KGS_MAX_Q) return fail(h, KGS_ERR_ARG, "too many percentiles");
     for (uint32_t i = 0; i < sp->n_q; ++i)
         if (!(sp->q[i] >= 0.0 && sp->q[i] <= 1.0)) return fail(h, KGS_ERR_ARG, "percentile outside [0,1]");
-    if (sp->n_q && sp->metric == KGS_METRIC_FB)
-        return fail(h, KGS_ERR_ARG, "percentiles of fb_mib (16-bit domain) are not available yet; use mean/max");
     if ((sp->key_mask & 1) && !h->has_table) return fail(h, KGS_ERR_STATE, "per-pod statistics need kgs_build_join first");
     KGS_CUDA(h, cudaSetDevice(h->device));
     const uint32_t W = sp->width < sp->step ? 1u : sp->width / sp->step;
@@ -550,12 +548,14 @@ int kgs_stats_begin(kgs_handle h, const kgs_window_spec* sp) {
     h->wide_cap = (uint32_t)wide_cap;
     h->clear_bytes = clear_bytes;
     if (pct) {
-        const uint64_t vals_cap = total_hint + 16 * 4096 + 64;
+        const uint64_t vals_cap = total_hint + 16 * 4096 + 64;     // in samples; fb_mib takes 2 B each
         if (vals_cap >= (1ull << 32)) return fail(h, KGS_ERR_ARG, "percentile jobs hold fewer than 2^32 samples per handle; shard the trace");
         uint64_t dcap = h->run_cap_override ? h->run_cap_override : (total_hint / 8 + 65536) * n_kinds;
         if (dcap > 0xFFFFFFF0ull) dcap = 0xFFFFFFF0ull;
         if (vals_cap > h->vals.cap || dcap * 16 > h->desc.cap) KGS_CUDA(h, cudaStreamSynchronize(h->compute));
-        if ((rc = reserve(h, h->vals, vals_cap))) return rc;
+        const uint64_t vbytes = sp->metric == KGS_METRIC_FB ? 2 : 1;
+        if (vals_cap * vbytes > h->vals.cap) KGS_CUDA(h, cudaStreamSynchronize(h->compute));
+        if ((rc = reserve(h, h->vals, vals_cap * vbytes))) return rc;
         if ((rc = reserve(h, h->desc, dcap * 16))) return rc;
         h->vals_cap = vals_cap;
         h->desc_cap = (uint32_t)dcap;
@@ -692,16 +692,19 @@ int kgs_stats_finalize(kgs_handle h) {
     P.ctl = h->ctl;
     P.big_cap = h->big_cap;
     P.wide_cap = h->wide_cap;
+    P.u16 = sp.metric == KGS_METRIC_FB ? 1u : 0u;
     cudaStream_t st = h->compute;
     if (cells) {
         launch(h, KGS_K_FINALIZE, st, [&] {
             k_finalize_cells<<<(cells + CellLayout::NT - 1) / CellLayout::NT, CellLayout::NT, 0, st>>>(P);
         });
-        if (sp.n_q) {   // cells with values >= 128 (and, through the big list, above 65 535 samples)
+        if (sp.n_q && sp.metric == KGS_METRIC_FB) {   // 16-bit values: two-digit radix select, warp per cell
+            launch(h, KGS_K_FINALIZE_WIDE, st, [&] { k_finalize_u16<<<148 * 8, 128, 0, st>>>(P); });
+        } else if (sp.n_q) {   // cells with values >= 128 (and, through the big list, above 65 535 samples)
             const int wide_grid = grid_for(cells, WideLayout::NT, 148 * 6);
             launch(h, KGS_K_FINALIZE_WIDE, st, [&] { k_finalize_wide<<<wide_grid, WideLayout::NT, 0, st>>>(P); });
         }
-        if (sp.n_q && h->accumulated * h->W > kSmallMax) {
+        if (sp.n_q && sp.metric != KGS_METRIC_FB && h->accumulated * h->W > kSmallMax) {
             launch(h, KGS_K_FINALIZE_BIG, st, [&] { k_finalize_big<<<148, 128, 0, st>>>(P); });
         }
     }

@@ -78,6 +78,18 @@ def test_mean_max_only_and_fb_metric(engine, cfg1):
     check(engine, cfg1, ('pod', 'node'), 'fb', cfg1.t0, 300, 300, 12, (), ingest=False)
 
 
+def test_fb_mib_percentiles_two_digit_radix_select(engine, cfg1):
+    """16-bit metric: percentiles by the two-pass (high byte, low byte) radix select; bit-exact."""
+    check(engine, cfg1, ('pod', 'gpu', 'node'), 'fb', cfg1.t0, 300, 300, 12, QS)
+    check(engine, cfg1, ('gpu',), 'fb', cfg1.t0, 10, 50, 100, (0.0, 0.5, 1.0), ingest=False)    # sliding
+    rng = np.random.default_rng(9)                                                               # full 16-bit domain
+    n = 5000
+    tr = synth.Trace(np.sort(rng.integers(100, 400, n)).astype(np.uint32), rng.integers(0, 4, n).astype(np.uint32),
+                     rng.integers(1, 3, n).astype(np.uint32), rng.integers(0, 1 << 32, n, dtype=np.uint64).astype(np.uint32),
+                     np.array([1, 2], np.uint64), np.array([0, 1], np.uint32), 2, 1, 8, 100, 300)
+    check(engine, tr, ('pod', 'gpu', 'node'), 'fb', 100, 60, 60, 5, (0.01, 0.5, 0.95, 0.99))
+
+
 def test_window_edges_and_odd_step(engine, cfg1):
     """t0 inside the trace, a step that divides nothing, fewer windows than the trace covers:
     samples before t0 and after the last window are left out (R3)."""
