@@ -141,7 +141,7 @@ int kgs_stats_accumulate(kgs_handle h);
 int kgs_stats_finalize(kgs_handle h);
 int kgs_window_stats(kgs_handle h, const kgs_window_spec* spec);
 /* Capacity, in entries of 16 B, of the run log the next percentile job allocates (0 = automatic:
- * total_samples_hint / 8 + 65536 per key kind, ample for collector-ordered input).  Three quarters
+ * sized for runs of min(8, step/2) samples, ample for collector-ordered input at 1 Hz).  Three quarters
  * of the log are handed out as private slabs per warp, one quarter is a shared overflow pool; with a
  * capacity set here the slabs are sized for the worst case (every sample its own run), which needs
  * entries >= 2 * samples * key kinds (rounded up per 256-sample tile). */
@@ -182,7 +182,7 @@ int kgs_launch_count(kgs_handle h, uint64_t* out);
  * on; kgs_kernel_time returns the accumulated device time and launch count of one kernel
  * (ids: KGS_K_*), kgs_reset_kernel_times clears them. */
 enum { KGS_K_BUILD = 0, KGS_K_BUILD_FIN = 1, KGS_K_PROBE = 2, KGS_K_ACCUM = 3, KGS_K_FINALIZE = 4,
-       KGS_K_FINALIZE_BIG = 5, KGS_K_SEGMEAN = 6, KGS_K_CLEAR = 7, KGS_K_FINALIZE_WIDE = 8, KGS_N_KERNELS = 9 };
+       KGS_K_FINALIZE_BIG = 5, KGS_K_SEGMEAN = 6, KGS_K_CLEAR = 7, KGS_K_FINALIZE_WIDE = 8, KGS_K_FINALIZE_BASIC = 9, KGS_N_KERNELS = 10 };
 int kgs_set_profiling(kgs_handle h, int on);
 int kgs_kernel_time(kgs_handle h, int kernel_id, double* total_ms, uint64_t* launches);
 int kgs_reset_kernel_times(kgs_handle h);

@@ -17,9 +17,9 @@ METRIC_SM, METRIC_MEM, METRIC_FB = 0, 1, 2
 POD_NONE = 0xFFFFFFFF
 MAX_Q = 8
 NOALLOC_MAX_PAIRS = 65536
-(K_BUILD, K_BUILD_FIN, K_PROBE, K_ACCUM, K_FINALIZE, K_FINALIZE_BIG, K_SEGMEAN, K_CLEAR, K_FINALIZE_WIDE) = range(9)
+(K_BUILD, K_BUILD_FIN, K_PROBE, K_ACCUM, K_FINALIZE, K_FINALIZE_BIG, K_SEGMEAN, K_CLEAR, K_FINALIZE_WIDE, K_FINALIZE_BASIC) = range(10)
 KERNEL_NAMES = ['join_build', 'join_resolve', 'join_probe', 'accum', 'finalize_cells', 'finalize_big',
-                'segmean', 'join_clear', 'finalize_wide']
+                'segmean', 'join_clear', 'finalize_wide', 'finalize_basic']
 
 
 class WindowSpec(C.Structure):

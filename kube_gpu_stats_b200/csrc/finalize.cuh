@@ -50,6 +50,7 @@ struct FinParams {
     uint32_t* big_list;                  // pairs left to k_finalize_big
     uint32_t* ctl;                       // ctl[2] = big_list length, ctl[3] = wide_list length
     uint32_t wide_cap, big_cap;
+    uint32_t slide_chunk;                // windows per thread of k_finalize_slide
     uint32_t u16;                        // 16-bit metric: the value log holds 2 B/sample, cells go to k_finalize_u16
 };
 
@@ -113,68 +114,74 @@ struct Layout16 {
 using CellLayout = Layout16<128, 128>;   // values 0..127: 256 B per thread, 32 KB per CTA of 128 threads
 using WideLayout = Layout16<64, 256>;    // values 0..255: 512 B per thread, 32 KB per CTA of 64 threads
 
+// delta = 1 counts a value in, delta = 0xFFFF (-1 modulo 2^16, the bins are u16) takes it out again
+// (sliding windows drop the pane that left the window).
 template <class L>
-__device__ __forceinline__ void add4(uint32_t base, uint32_t w) {
-    L::inc2(base, w & 0xFFu, (w >> 8) & 0xFFu, 1u, 1u);
-    L::inc2(base, (w >> 16) & 0xFFu, w >> 24, 1u, 1u);
+__device__ __forceinline__ void add4(uint32_t base, uint32_t w, uint32_t delta = 1u) {
+    L::inc2(base, w & 0xFFu, (w >> 8) & 0xFFu, delta, delta);
+    L::inc2(base, (w >> 16) & 0xFFu, w >> 24, delta, delta);
 }
 
 template <class L>
-__device__ __forceinline__ void add1(uint32_t base, uint32_t b) {
+__device__ __forceinline__ void add1(uint32_t base, uint32_t b, uint32_t delta = 1u) {
     const uint32_t a = L::addr(base, b);
-    sts_u16(a, lds_u16(a) + 1u);
+    sts_u16(a, lds_u16(a) + delta);
 }
 
-// Count the W pane lists of this thread's window cell into its histogram.  WARP-SYNCHRONOUS: all
-// 32 lanes call it together (lanes without a cell pass valid = false) and walk their runs in
-// lockstep.  A run is covered by 16-byte ALIGNED blocks of the value log; kChunk of them are
-// loaded at once (one round trip to L2 per chunk, not per block) and then counted word by word:
-// a word that lies completely inside the run takes the branch-free 4-byte body, the at most two
-// words cut by the run's ends take a byte loop that the warp only enters when some lane needs it.
+// Count (delta = 1) or un-count (delta = 0xFFFF) every run of the list that starts at descriptor
+// `at` (1-based, 0 = none) in the lane's histogram.  WARP-SYNCHRONOUS: all 32 lanes call it together
+// (idle lanes pass at = 0) and walk their runs in lockstep.  A run is covered by 16-byte ALIGNED
+// blocks of the value log; kChunk of them are loaded at once (one round trip to L2 per chunk, not
+// per block) and then counted word by word: a word that lies completely inside the run takes the
+// branch-free 4-byte body, the at most two words cut by the run's ends take a byte loop that the
+// warp only enters when some lane needs it.
 template <class L>
-__device__ __forceinline__ void add_cell(uint32_t base, const FinParams& P, const FinKind& K, uint32_t pc0,
-                                         bool valid) {
+__device__ __forceinline__ void add_list_sync(uint32_t base, const FinParams& P, uint32_t at, uint32_t delta = 1u) {
     constexpr uint32_t kAll = 0xFFFFFFFFu;
     constexpr int kChunk = 5;   // 80 bytes: a 60-sample run at any alignment
-    for (uint32_t d = 0; d < P.W; ++d) {
-        uint32_t at = valid ? K.head[pc0 + d] : 0u;
-        while (__any_sync(kAll, at != 0)) {
-            uint4 r = make_uint4(0, 0, 0, 0);
-            if (at) r = __ldg(P.desc + (at - 1));
-            const uint32_t start = r.x, end = r.x + r.y;
-            uint32_t blk = start & ~15u;
-            while (__any_sync(kAll, blk < end)) {
-                uint4 x[kChunk];
+    while (__any_sync(kAll, at != 0)) {
+        uint4 r = make_uint4(0, 0, 0, 0);
+        if (at) r = __ldg(P.desc + (at - 1));
+        const uint32_t start = r.x, end = r.x + r.y;
+        uint32_t blk = start & ~15u;
+        while (__any_sync(kAll, blk < end)) {
+            uint4 x[kChunk];
 #pragma unroll
-                for (int b = 0; b < kChunk; ++b) {
-                    x[b] = make_uint4(0, 0, 0, 0);
-                    if (blk + 16 * b < end) x[b] = __ldg(reinterpret_cast<const uint4*>(P.vals + blk + 16 * b));
-                }
+            for (int b = 0; b < kChunk; ++b) {
+                x[b] = make_uint4(0, 0, 0, 0);
+                if (blk + 16 * b < end) x[b] = __ldg(reinterpret_cast<const uint4*>(P.vals + blk + 16 * b));
+            }
 #pragma unroll
-                for (int b = 0; b < kChunk; ++b) {
-                    const uint32_t a = blk + 16 * b;
-                    if (!__any_sync(kAll, a < end)) break;
-                    const int lo = (int)(start - a), hi = (int)(end - a);   // run = bytes [lo, hi) of this block
-                    const uint32_t w[4] = {x[b].x, x[b].y, x[b].z, x[b].w};
+            for (int b = 0; b < kChunk; ++b) {
+                const uint32_t a = blk + 16 * b;
+                if (!__any_sync(kAll, a < end)) break;
+                const int lo = (int)(start - a), hi = (int)(end - a);   // run = bytes [lo, hi) of this block
+                const uint32_t w[4] = {x[b].x, x[b].y, x[b].z, x[b].w};
 #pragma unroll
-                    for (int k = 0; k < 4; ++k) {
-                        const bool whole = lo <= 4 * k && hi >= 4 * k + 4;
-                        const bool cut = !whole && lo < 4 * k + 4 && hi > 4 * k;
-                        if (whole) add4<L>(base, w[k]);
-                        if (__any_sync(kAll, cut)) {
-                            if (cut) {
+                for (int k = 0; k < 4; ++k) {
+                    const bool whole = lo <= 4 * k && hi >= 4 * k + 4;
+                    const bool cut = !whole && lo < 4 * k + 4 && hi > 4 * k;
+                    if (whole) add4<L>(base, w[k], delta);
+                    if (__any_sync(kAll, cut)) {
+                        if (cut) {
 #pragma unroll
-                                for (int j = 0; j < 4; ++j)
-                                    if (lo <= 4 * k + j && 4 * k + j < hi) add1<L>(base, (w[k] >> (8 * j)) & 0xFFu);
-                            }
+                            for (int j = 0; j < 4; ++j)
+                                if (lo <= 4 * k + j && 4 * k + j < hi) add1<L>(base, (w[k] >> (8 * j)) & 0xFFu, delta);
                         }
                     }
                 }
-                blk += 16 * kChunk;
             }
-            at = r.z;
+            blk += 16 * kChunk;
         }
+        at = r.z;
     }
+}
+
+// Count the W pane lists of this thread's window cell (lanes without a cell pass valid = false).
+template <class L>
+__device__ __forceinline__ void add_cell(uint32_t base, const FinParams& P, const FinKind& K, uint32_t pc0,
+                                         bool valid) {
+    for (uint32_t d = 0; d < P.W; ++d) add_list_sync<L>(base, P, valid ? K.head[pc0 + d] : 0u);
 }
 
 // The value of rank `ilo` and of rank `ihi` (ihi = ilo or ilo + 1) among the `count` values of the

@@ -1,0 +1,130 @@
+// finalize_slide.cuh - percentiles of SLIDING windows (width = W panes, W > 1) without re-counting.
+//
+// k_finalize_cells counts all W panes of every window cell: with BASELINE configs[4] (5-min windows
+// every 10 s, W = 30) each sample is counted 30 times per key kind.  Here one thread owns a CHUNK of
+// consecutive windows of one key and keeps the window's histogram alive while it slides: entering
+// window j+1 it takes pane j out (delta 0xFFFF = -1 in the u16 bins) and counts pane j+W in, then
+// selects.  Only the first window of a chunk counts W panes.  Same exact selection (rule R5).
+//   * count / sum / max / mean of every window cell come from k_finalize_basic (no shared memory);
+//   * a chunk that meets a value >= 128 or a window above 65 535 samples hands its windows to the
+//     wide list (k_finalize_wide / k_finalize_big count them the slow way).
+#pragma once
+#include "finalize.cuh"
+
+namespace kgs {
+
+// count / sum / max / mean of every window cell, NaN percentiles for empty cells.
+__global__ void __launch_bounds__(256) k_finalize_basic(const __grid_constant__ FinParams P) {
+    const uint32_t gc = blockIdx.x * 256 + threadIdx.x;
+    if (gc >= P.total_cells) return;
+    uint32_t ks;
+    const FinKind& K = kind_of_cell(P, gc, ks);
+    const uint32_t c = gc - K.cell_begin;
+    const uint32_t key = c / P.n_windows;
+    const uint32_t pc0 = key * P.n_panes + (c - key * P.n_windows);
+    unsigned long long count = 0, total = 0;
+    uint32_t vmax = 0;
+    for (uint32_t d = 0; d < P.W; ++d) {
+        count += K.cnt[pc0 + d];
+        total += K.sum[pc0 + d];
+        vmax = max(vmax, K.mx[pc0 + d]);
+    }
+    K.o_count[c] = (uint32_t)count;
+    K.o_sum[c] = total;
+    K.o_max[c] = vmax;
+    K.o_mean[c] = count ? __ddiv_rn((double)total, (double)count) : 0.0;
+    if (count == 0) {
+        const uint32_t ncell = K.n_keys * P.n_windows;
+        for (uint32_t iq = 0; iq < P.n_q; ++iq) K.o_pct[(size_t)iq * ncell + c] = nan_f64();
+    }
+}
+
+// One thread per (key kind, key, chunk of P.slide_chunk windows); a warp's lanes are consecutive
+// chunks of (mostly) the same key, so they step through their windows in lockstep.
+__global__ void __launch_bounds__(CellLayout::NT) k_finalize_slide(const __grid_constant__ FinParams P) {
+    using L = CellLayout;
+    constexpr uint32_t kAll = 0xFFFFFFFFu;
+    __shared__ uint32_t hist[L::WORDS * L::NT];
+    if (P.ctl[1]) return;   // overflowed run log: the host reports the error
+    const uint32_t tid = threadIdx.x;
+    {   // clear the CTA's histograms together
+        uint4* z = reinterpret_cast<uint4*>(hist);
+#pragma unroll
+        for (int i = 0; i < L::WORDS / 4; ++i) z[i * L::NT + tid] = make_uint4(0, 0, 0, 0);
+        __syncthreads();
+    }
+    const uint32_t base = (uint32_t)__cvta_generic_to_shared(hist) + tid * 4;
+    const uint32_t C = P.slide_chunk;
+    const uint32_t chunks_per_key = (P.n_windows + C - 1) / C;
+    // which (kind, key, chunk): kinds are laid out one after the other
+    uint32_t idx = blockIdx.x * L::NT + tid, ks = 0;
+    bool live = false;
+    for (uint32_t k = 0; k < P.n_kinds; ++k) {
+        const uint32_t span = P.kind[k].n_keys * chunks_per_key;
+        if (idx < span) { ks = k; live = true; break; }
+        idx -= span;
+    }
+    const FinKind& K = P.kind[ks];
+    const uint32_t key = live ? idx / chunks_per_key : 0;
+    const uint32_t j0 = live ? (idx - key * chunks_per_key) * C : 0;
+    const uint32_t j1 = live ? min(P.n_windows, j0 + C) : 0;
+    const uint32_t prow = key * P.n_panes;          // first pane cell of the key
+    const uint32_t ncell = K.n_keys * P.n_windows;
+    uint32_t count = 0, vub = 0;                    // samples in the window; upper bound of its values
+    bool bad = false;                               // met a value the 128-bin histogram cannot hold
+    // first window of the chunk: count its W panes
+    for (uint32_t d = 0; d < P.W; ++d) {
+        uint32_t at = 0;
+        if (live && j0 < j1) {
+            const uint32_t pc = prow + j0 + d;
+            const uint32_t m = K.mx[pc];
+            count += K.cnt[pc];
+            vub = max(vub, m);
+            bad |= m >= (uint32_t)L::BINS;
+            if (!bad) at = K.head[pc];
+        }
+        add_list_sync<L>(base, P, at);
+    }
+    for (uint32_t s = 0; s < C; ++s) {              // warp-uniform trip count
+        const uint32_t j = j0 + s;
+        const bool on = live && j < j1;
+        if (s > 0) {                                // slide: pane j-1 leaves, pane j+W-1 enters
+            uint32_t out = 0, in = 0;
+            if (on) {
+                const uint32_t po = prow + j - 1, pi = prow + j + P.W - 1;
+                const uint32_t m = K.mx[pi];
+                count += K.cnt[pi] - K.cnt[po];
+                vub = max(vub, m);
+                const bool was_bad = bad;
+                bad |= m >= (uint32_t)L::BINS;
+                if (!was_bad) out = K.head[po];     // un-count only what was counted
+                if (!bad) in = K.head[pi];
+            }
+            add_list_sync<L>(base, P, out, 0xFFFFu);
+            add_list_sync<L>(base, P, in);
+        }
+        const uint32_t c = key * P.n_windows + j;
+        const bool later = on && count > 0 && (bad || count > kSmallMax);
+        const uint32_t later_mask = __ballot_sync(kAll, later);
+        if (later_mask) {                           // the slow kernels count these windows pane by pane
+            uint32_t at = 0;
+            if (lane_id() == 0) at = atomicAdd(P.ctl + 3, (uint32_t)__popc(later_mask));
+            at = __shfl_sync(kAll, at, 0) + __popc(later_mask & ((1u << lane_id()) - 1u));
+            if (later && at < P.wide_cap) {
+                P.wide_list[2 * at] = ks;
+                P.wide_list[2 * at + 1] = c;
+            }
+        }
+        if (on && count > 0 && !later) {
+            for (uint32_t iq = 0; iq < P.n_q; ++iq) {
+                uint32_t ilo, ihi, vlo, vhi;
+                double wt;
+                pct_ranks(P.q[iq], count, ilo, ihi, wt);
+                select2<L>(base, count, vub, ilo, ihi, vlo, vhi);
+                K.o_pct[(size_t)iq * ncell + c] = pct_lerp(vlo, vhi, wt);
+            }
+        }
+    }
+}
+
+}  // namespace kgs

@@ -11,6 +11,7 @@
 #include "accum.cuh"
 #include "common.cuh"
 #include "finalize.cuh"
+#include "finalize_slide.cuh"
 #include "join.cuh"
 #include "noalloc.cuh"
 #include "segmean.cuh"
@@ -79,6 +80,8 @@ struct kgs_ctx {
     uint32_t desc_cap = 0, desc_pool_base = 0, desc_priv_next = 0;
     uint64_t run_cap_override = 0;
     uint64_t job_seq = 0;
+    bool slide = true;             // W > 1 jobs keep a sliding histogram per chunk of windows (finalize_slide.cuh)
+    uint32_t slide_chunk = 8;      // measured best on B200 (4: 3.0 ms, 8: 1.9, 16: 2.1, 64: 5.0 for the cfg5-shaped test)
     bool accum_prefetch = false;   // register double-buffering of the next tile: 109 vs 78 registers
     int accum_ctas_per_sm = 3;     // resident CTAs of 8 warps per SM at 78 registers
     // measurement
@@ -208,6 +211,8 @@ int kgs_create(int device, kgs_handle* out) {
         if ((e = cudaEventCreateWithFlags(&h->batch[b].consumed, cudaEventDisableTiming)) != cudaSuccess) return bail(e, "cudaEventCreate");
         if ((e = cudaEventCreate(&h->mark[b])) != cudaSuccess) return bail(e, "cudaEventCreate");
     }
+    if (const char* e = getenv("KGS_SLIDE")) h->slide = atoi(e) != 0;
+    if (const char* e = getenv("KGS_SLIDE_CHUNK")) { const int v = atoi(e); if (v >= 1 && v <= 4096) h->slide_chunk = (uint32_t)v; }
     if (const char* e = getenv("KGS_ACCUM_PREFETCH")) h->accum_prefetch = atoi(e) != 0;
     if (const char* e = getenv("KGS_ACCUM_CTAS_PER_SM")) {   // tuning knob for experiments
         const int v = atoi(e);
@@ -550,7 +555,10 @@ int kgs_stats_begin(kgs_handle h, const kgs_window_spec* sp) {
     if (pct) {
         const uint64_t vals_cap = total_hint + 16 * 4096 + 64;     // in samples; fb_mib takes 2 B each
         if (vals_cap >= (1ull << 32)) return fail(h, KGS_ERR_ARG, "percentile jobs hold fewer than 2^32 samples per handle; shard the trace");
-        uint64_t dcap = h->run_cap_override ? h->run_cap_override : (total_hint / 8 + 65536) * n_kinds;
+        // a run cannot outlast its pane: assume runs of step/2 samples, between 2 and 8 (1 Hz sampling, 60 s panes
+        // give 60); a third more for the shared pool
+        const uint64_t run_guess = sp->step / 2 < 2 ? 2 : (sp->step / 2 > 8 ? 8 : sp->step / 2);
+        uint64_t dcap = h->run_cap_override ? h->run_cap_override : (total_hint / run_guess + 65536) * n_kinds * 4 / 3;
         if (dcap > 0xFFFFFFF0ull) dcap = 0xFFFFFFF0ull;
         if (vals_cap > h->vals.cap || dcap * 16 > h->desc.cap) KGS_CUDA(h, cudaStreamSynchronize(h->compute));
         const uint64_t vbytes = sp->metric == KGS_METRIC_FB ? 2 : 1;
@@ -628,7 +636,8 @@ int kgs_stats_accumulate(kgs_handle h) {
         // a private run-log slab per warp for this launch (16 entries per tile and key kind is > 3x what
         // collector-ordered input needs); what does not fit goes to the shared pool
         const uint64_t warps = (uint64_t)grid * kAccumWarps;
-        uint64_t per_warp = (uint64_t)P.tiles_per_warp * 16 * __builtin_popcount(sp.key_mask);
+        const uint64_t run_guess = sp.step / 2 < 2 ? 2 : (sp.step / 2 > 8 ? 8 : sp.step / 2);
+        uint64_t per_warp = (uint64_t)P.tiles_per_warp * (kTileSamples / run_guess) * __builtin_popcount(sp.key_mask);
         if (h->run_cap_override) per_warp = (uint64_t)P.tiles_per_warp * kTileSamples * __builtin_popcount(sp.key_mask);   // every sample its own run
         const uint64_t room = h->desc_pool_base - h->desc_priv_next;
         if (per_warp * warps > room) per_warp = room / warps;
@@ -693,11 +702,24 @@ int kgs_stats_finalize(kgs_handle h) {
     P.big_cap = h->big_cap;
     P.wide_cap = h->wide_cap;
     P.u16 = sp.metric == KGS_METRIC_FB ? 1u : 0u;
+    P.slide_chunk = h->slide_chunk;
     cudaStream_t st = h->compute;
     if (cells) {
-        launch(h, KGS_K_FINALIZE, st, [&] {
-            k_finalize_cells<<<(cells + CellLayout::NT - 1) / CellLayout::NT, CellLayout::NT, 0, st>>>(P);
-        });
+        if (h->W > 1 && h->slide && sp.metric != KGS_METRIC_FB) {
+            // sliding windows: per-cell basics, then one thread per chunk of windows keeps the histogram sliding
+            launch(h, KGS_K_FINALIZE_BASIC, st, [&] { k_finalize_basic<<<(cells + 255) / 256, 256, 0, st>>>(P); });
+            if (sp.n_q) {
+                const uint64_t chunks_per_key = (sp.n_windows + h->slide_chunk - 1) / h->slide_chunk;
+                uint64_t threads = 0;
+                for (uint32_t k = 0; k < P.n_kinds; ++k) threads += (uint64_t)P.kind[k].n_keys * chunks_per_key;
+                const unsigned grid = (unsigned)((threads + CellLayout::NT - 1) / CellLayout::NT);
+                if (grid) launch(h, KGS_K_FINALIZE, st, [&] { k_finalize_slide<<<grid, CellLayout::NT, 0, st>>>(P); });
+            }
+        } else {
+            launch(h, KGS_K_FINALIZE, st, [&] {
+                k_finalize_cells<<<(cells + CellLayout::NT - 1) / CellLayout::NT, CellLayout::NT, 0, st>>>(P);
+            });
+        }
         if (sp.n_q && sp.metric == KGS_METRIC_FB) {   // 16-bit values: two-digit radix select, warp per cell
             launch(h, KGS_K_FINALIZE_WIDE, st, [&] { k_finalize_u16<<<148 * 8, 128, 0, st>>>(P); });
         } else if (sp.n_q) {   // cells with values >= 128 (and, through the big list, above 65 535 samples)
