@@ -24,56 +24,64 @@ def _kubectl_pods():
     return proc.stdout.read()
 
 
+LEGACY_GPU_KEY = 'alpha.kubernetes.io/nvidia-gpu'        # the only resource key the reference counts (WUG:40)
+TABLE_HEADER = ['Namespace', 'Node', 'Pod', 'GPU Type', 'GPU Cores']
+_AFFINITY_PATH = ('spec', 'affinity', 'nodeAffinity', 'requiredDuringSchedulingIgnoredDuringExecution',
+                  'nodeSelectorTerms', 0, 'matchExpressions', 0, 'values', 0)
+
+
+def _gpu_limits(containers):
+    """Sum of the containers' legacy GPU limits; containers without resources/limits count 0."""
+    asked = (c['resources']['limits'].get(LEGACY_GPU_KEY, 0)
+             for c in containers if 'limits' in c.get('resources', ()))
+    return sum(int(v) for v in asked)
+
+
+def ownership_rows(items):
+    """(rows, grand total, totals per GPU type in first-seen order) over the pods that own GPUs."""
+    rows, per_type = [], {}
+    for item in items:
+        rec = checkPod(item)
+        if rec:
+            rows.append(rec)
+            per_type[rec[3]] = per_type.get(rec[3], 0) + rec[4]
+    return rows, sum(r[4] for r in rows), per_type
+
+
 def main():
-    """WUG:7-25."""
-    info = json.loads(_kubectl_pods())
-    rows = []
-    type_gpu_map = {}
-    total_gpu_num = 0
-    for pod_info in info['items']:
-        row = checkPod(pod_info)
-        if len(row) == 0:
-            continue
-        gpu_type, gpu_num = row[3], row[4]
-        total_gpu_num += gpu_num
-        type_gpu_map[gpu_type] = type_gpu_map.get(gpu_type, 0) + gpu_num
-        rows.append(row)
-    print(pretty_table(['Namespace', 'Node', 'Pod', 'GPU Type', 'GPU Cores'], rows))
-    print('Total GPU: %d' % total_gpu_num)
-    for gpu_type, gpu_num in type_gpu_map.items():
-        print('%s\t%d' % (gpu_type, gpu_num))
+    """WUG:7-25: table, grand total, one line per GPU type."""
+    rows, total, per_type = ownership_rows(json.loads(_kubectl_pods())['items'])
+    lines = [pretty_table(TABLE_HEADER, rows), 'Total GPU: %d' % total]
+    lines += ['%s\t%d' % kv for kv in per_type.items()]
+    print('\n'.join(lines))
 
 
 def checkPod(pod_info):
-    """WUG:27-49: [namespace, node, pod, gpu_type, sum of container GPU limits] or []."""
+    """WUG:27-49: ``[namespace, node, pod, gpu_type, sum of container GPU limits]`` for a pod that
+    owns GPUs, else ``[]``.  Any missing field prints the exception and yields ``[]`` (WUG:46-48);
+    the node name is looked up before the GPUs are counted, as in the reference (WUG:33)."""
     try:
-        metadata = pod_info['metadata']
-        pod_name = metadata['name']
-        namespace = metadata['namespace']
-        containers = pod_info['spec']['containers']
-        node_name = pod_info['spec']['nodeName']
-        total_gpu_num = 0
-        for container in containers:
-            if 'resources' not in container:
-                continue
-            if 'limits' not in container['resources']:
-                continue
-            total_gpu_num += int(container['resources']['limits'].get('alpha.kubernetes.io/nvidia-gpu', 0))
-        if total_gpu_num > 0:
-            return [namespace, node_name, pod_name, getGPUType(pod_info), total_gpu_num]
-    except Exception as e:
-        print(e)
+        meta, spec = pod_info['metadata'], pod_info['spec']
+        ident = (meta['name'], meta['namespace'])
+        containers, node = spec['containers'], spec['nodeName']
+        gpus = _gpu_limits(containers)
+    except Exception as err:
+        print(err)
         return []
-    return []
+    if gpus <= 0:
+        return []
+    return [ident[1], node, ident[0], getGPUType(pod_info), gpus]
 
 
 def getGPUType(pod_info):
-    """WUG:51-58."""
+    """WUG:51-58: first value of the first required node-affinity expression, else '<unspecified>'."""
+    here = pod_info
     try:
-        return (pod_info['spec']['affinity']['nodeAffinity']['requiredDuringSchedulingIgnoredDuringExecution']
-                ['nodeSelectorTerms'][0]['matchExpressions'][0]['values'][0])
+        for step in _AFFINITY_PATH:
+            here = here[step]
     except Exception:
         return '<unspecified>'
+    return here
 
 
 def join_pairs(rows, node_ids, pid_owner):
