@@ -67,6 +67,7 @@ struct AccumParams {
     uint32_t pool_base;            // shared overflow pool [pool_base, desc_cap), cursor ctl[0]
     uint32_t* ctl;                 // ctl[0] pool cursor, ctl[1] overflow flag
     uint32_t agg_on;               // every cell index < 2^30: the per-CTA accumulator cache may be used
+    uint32_t dense_ok;             // step >= 8 and no sampled windows: the dense-tile shortcut applies
 };
 
 __device__ __forceinline__ uint64_t policy_evict_last() {
@@ -252,15 +253,44 @@ __global__ void __launch_bounds__(kAccumWarps * 32) k_accum(const __grid_constan
         } else {
             load_oct(P, i0, full, cur);
         }
-        uint32_t pane[8], v[8];
-        const uint32_t lim = full ? 8u : (P.n > i0 ? P.n - i0 : 0u);   // samples of this lane inside the batch
+        uint32_t pane[8], v[8], bm = 0;   // bm: bit j set when sample j starts a new piece inside the lane
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            const uint32_t pn = fdiv(cur.t[j] - P.t0, P.dstep);
-            bool ok = (cur.t[j] >= P.t0) & (pn < P.n_panes) & ((uint32_t)j < lim);
-            if (P.win_len < P.step) ok &= (cur.t[j] - P.t0) - pn * P.step < P.win_len;   // warp-uniform branch
-            pane[j] = ok ? pn : kInvalid;
-            v[j] = (cur.u[j] >> P.mshift) & P.mmask;
+        for (int j = 0; j < 8; ++j) v[j] = (cur.u[j] >> P.mshift) & P.mmask;
+        // Dense tile: every lane holds 8 consecutive seconds of one (gpu, pid).  Then the lane's panes
+        // follow from ONE division: at most one pane boundary falls inside it (step >= 8), at a
+        // position known from the remainder.  Collector-ordered 1 Hz data takes this path except
+        // where a GPU stream or a tenancy ends inside the tile.
+        bool dense = false;
+        if (full && P.dense_ok) {
+            uint32_t acc = 0;
+#pragma unroll
+            for (int j = 1; j < 8; ++j)
+                acc |= ((cur.t[j] - cur.t[0]) ^ (uint32_t)j) | (cur.g[j] ^ cur.g[0]) | (cur.p[j] ^ cur.p[0]);
+            dense = __all_sync(kAll, acc == 0 && cur.t[0] >= P.t0 && cur.t[0] < 0xFFFFFF00u);
+        }
+        if (dense) {
+            const uint32_t x0 = cur.t[0] - P.t0;
+            const uint32_t pn0 = fdiv(x0, P.dstep);
+            const uint32_t left = P.step - (x0 - pn0 * P.step);          // samples from t[0] to the end of pane pn0
+            const uint32_t p_a = pn0 < P.n_panes ? pn0 : kInvalid;
+            const uint32_t p_b = pn0 + 1 < P.n_panes ? pn0 + 1 : kInvalid;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) pane[j] = (uint32_t)j < left ? p_a : p_b;
+            if (left < 8 && p_a != p_b) bm = 1u << left;
+        } else {
+            const uint32_t lim = full ? 8u : (P.n > i0 ? P.n - i0 : 0u);   // samples of this lane inside the batch
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const uint32_t pn = fdiv(cur.t[j] - P.t0, P.dstep);
+                bool ok = (cur.t[j] >= P.t0) & (pn < P.n_panes) & ((uint32_t)j < lim);
+                if (P.win_len < P.step) ok &= (cur.t[j] - P.t0) - pn * P.step < P.win_len;   // warp-uniform branch
+                pane[j] = ok ? pn : kInvalid;
+            }
+#pragma unroll
+            for (int j = 1; j < 8; ++j) {
+                const uint32_t diff = (cur.g[j] ^ cur.g[j - 1]) | (cur.p[j] ^ cur.p[j - 1]) | (pane[j] ^ pane[j - 1]);
+                bm += min(diff, 1u) << j;   // distinct bits: + is |
+            }
         }
         if (PCT && P.mmask > 0xFFu) {   // value log of a 16-bit metric (fb_mib): 2 B/sample (warp-uniform branch)
             uint16_t* dst = reinterpret_cast<uint16_t*>(P.vals) + P.vals_base + i0;
@@ -282,13 +312,6 @@ __global__ void __launch_bounds__(kAccumWarps * 32) k_accum(const __grid_constan
                 for (int j = 0; j < 8; ++j)
                     if (i0 + j < P.n) dst[j] = (uint8_t)v[j];
             }
-        }
-        // boundaries inside the lane: bit j set when sample j starts a new piece
-        uint32_t bm = 0;
-#pragma unroll
-        for (int j = 1; j < 8; ++j) {
-            const uint32_t diff = (cur.g[j] ^ cur.g[j - 1]) | (cur.p[j] ^ cur.p[j - 1]) | (pane[j] ^ pane[j - 1]);
-            bm += min(diff, 1u) << j;   // distinct bits: + is |
         }
         const bool single = bm == 0;
         // does my first piece continue the previous lane's last piece?

@@ -82,8 +82,9 @@ struct kgs_ctx {
     uint64_t job_seq = 0;
     bool slide = true;             // W > 1 jobs keep a sliding histogram per chunk of windows (finalize_slide.cuh)
     uint32_t slide_chunk = 8;      // measured best on B200 (4: 3.0 ms, 8: 1.9, 16: 2.1, 64: 5.0 for the cfg5-shaped test)
+    bool dense_path = true;
     bool accum_prefetch = false;   // register double-buffering of the next tile: 109 vs 78 registers
-    int accum_ctas_per_sm = 3;     // resident CTAs of 8 warps per SM at 78 registers
+    int accum_ctas_per_sm = 4;     // resident CTAs of 8 warps per SM at 64 registers
     // measurement
     uint64_t launches = 0;
     bool prof = false;
@@ -213,6 +214,7 @@ int kgs_create(int device, kgs_handle* out) {
     }
     if (const char* e = getenv("KGS_SLIDE")) h->slide = atoi(e) != 0;
     if (const char* e = getenv("KGS_SLIDE_CHUNK")) { const int v = atoi(e); if (v >= 1 && v <= 4096) h->slide_chunk = (uint32_t)v; }
+    if (const char* e = getenv("KGS_DENSE")) h->dense_path = atoi(e) != 0;
     if (const char* e = getenv("KGS_ACCUM_PREFETCH")) h->accum_prefetch = atoi(e) != 0;
     if (const char* e = getenv("KGS_ACCUM_CTAS_PER_SM")) {   // tuning knob for experiments
         const int v = atoi(e);
@@ -622,6 +624,7 @@ int kgs_stats_accumulate(kgs_handle h) {
     P.desc_cap = h->desc_cap;
     P.ctl = h->ctl;
     P.agg_on = 1;
+    P.dense_ok = (sp.step >= 8 && sp.width >= sp.step && h->dense_path) ? 1u : 0u;
     for (int k = 0; k < 3; ++k)
         if ((uint64_t)h->kind[k].n_keys * h->n_panes >= (1ull << 30)) P.agg_on = 0;
     cudaStream_t st = h->compute;
