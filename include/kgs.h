@@ -162,6 +162,19 @@ int kgs_result_device_ptr(kgs_handle h, int key_kind, int which, void** d_ptr, s
  * the host in one transfer (blocking; use a pinned destination).  Consecutive jobs alternate between
  * two result regions, so job i's region stays intact while job i+1 is computed (not job i+2). */
 int kgs_result_region(kgs_handle h, void** d_ptr, size_t* exchange_bytes, size_t* total_bytes);
+/* Packed exchange tables, for jobs whose tables travel between GPUs every step.  With the option on
+ * (it applies from the next kgs_stats_begin), finalize also writes, per key kind, sum (u32 when a
+ * cell's sum provably fits - total_samples_hint * metric maximum < 2^32 - else u64), count u32,
+ * max u16, and per percentile the two selected values (u8 | u8<<8; u16 | u16<<16 for fb_mib):
+ * 10 + 2*n_q bytes per cell instead of 16 + 8*n_q.  The receiver rebuilds mean = sum/count and the
+ * percentile with the same two roundings as the sender (rule R5), so nothing is lost.
+ * kgs_exchange_region returns the region one collective has to move: the packed tables when they
+ * are on (*packed = 1 for u32 sums, 2 for u64 sums), else the exchange part of kgs_result_region
+ * (*packed = 0).  kgs_packed_offset: offset and size of one packed table inside that region
+ * (which: 0 count, 1 sum, 2 max, 4 selected values). */
+int kgs_set_packed_exchange(kgs_handle h, int on);
+int kgs_exchange_region(kgs_handle h, void** d_ptr, size_t* nbytes, int* packed);
+int kgs_packed_offset(kgs_handle h, int key_kind, int which, size_t* offset, size_t* nbytes);
 int kgs_result_offset(kgs_handle h, int key_kind, int which, size_t* offset, size_t* nbytes);
 int kgs_fetch_region(kgs_handle h, void* host_dst, size_t nbytes);
 

@@ -67,6 +67,9 @@ def load(path=LIB_PATH):
         'kgs_fetch_stats': [H, C.c_int, vp, vp, vp, vp, vp],
         'kgs_result_device_ptr': [H, C.c_int, C.c_int, C.POINTER(vp), C.POINTER(C.c_size_t)],
         'kgs_result_region': [H, C.POINTER(vp), C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)],
+        'kgs_set_packed_exchange': [H, C.c_int],
+        'kgs_exchange_region': [H, C.POINTER(vp), C.POINTER(C.c_size_t), C.POINTER(C.c_int)],
+        'kgs_packed_offset': [H, C.c_int, C.c_int, C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)],
         'kgs_result_offset': [H, C.c_int, C.c_int, C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)],
         'kgs_fetch_region': [H, vp, C.c_size_t],
         'kgs_segmented_mean_f64': [H, vp, vp, C.c_uint64, C.c_double, C.c_double, vp],

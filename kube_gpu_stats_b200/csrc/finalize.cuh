@@ -34,6 +34,11 @@ struct FinKind {
     uint32_t* o_max;
     double* o_mean;
     double* o_pct;                       // [n_q][n_keys * n_windows]
+    // packed exchange tables (optional, nullptr = off): what another shard needs to rebuild the cell
+    void* p_sum;                         // u32 or u64 per cell (FinParams::packed_sum64)
+    uint32_t* p_count;
+    uint16_t* p_max;
+    void* p_rank;                        // per percentile and cell: the two selected values, u8|u8<<8 (u16|u16<<16 for fb_mib)
 };
 
 struct FinParams {
@@ -50,6 +55,7 @@ struct FinParams {
     uint32_t* big_list;                  // pairs left to k_finalize_big
     uint32_t* ctl;                       // ctl[2] = big_list length, ctl[3] = wide_list length
     uint32_t wide_cap, big_cap;
+    uint32_t packed_sum64;               // packed sums are u64 (a cell's sum may not fit 32 bits)
     uint32_t slide_chunk;                // windows per thread of k_finalize_slide
     uint32_t u16;                        // 16-bit metric: the value log holds 2 B/sample, cells go to k_finalize_u16
 };
@@ -69,6 +75,44 @@ __device__ __forceinline__ void pct_ranks(double q, uint32_t n, uint32_t& ilo, u
 
 __device__ __forceinline__ double pct_lerp(uint32_t vlo, uint32_t vhi, double w) {
     return __dadd_rn(__dmul_rn((double)vlo, __dsub_rn(1.0, w)), __dmul_rn((double)vhi, w));
+}
+
+// One percentile of one cell: the interpolated value into the result table and, when the packed
+// exchange tables are on, the two selected values (the receiver repeats pct_ranks + pct_lerp on
+// them, which gives the same bits).
+__device__ __forceinline__ void store_pct(const FinParams& P, const FinKind& K, uint32_t c, uint32_t iq,
+                                          uint32_t vlo, uint32_t vhi, double w) {
+    const size_t at = (size_t)iq * (K.n_keys * P.n_windows) + c;
+    K.o_pct[at] = pct_lerp(vlo, vhi, w);
+    if (K.p_rank) {
+        if (P.u16) static_cast<uint32_t*>(K.p_rank)[at] = vlo | (vhi << 16);
+        else static_cast<uint16_t*>(K.p_rank)[at] = (uint16_t)(vlo | (vhi << 8));
+    }
+}
+
+// count / sum / max / mean of one cell (and NaN percentiles when it is empty).
+__device__ __forceinline__ void store_basics(const FinParams& P, const FinKind& K, uint32_t c, unsigned long long count,
+                                             unsigned long long total, uint32_t vmax) {
+    K.o_count[c] = (uint32_t)count;
+    K.o_sum[c] = total;
+    K.o_max[c] = vmax;
+    K.o_mean[c] = count ? __ddiv_rn((double)total, (double)count) : 0.0;
+    if (K.p_count) {
+        K.p_count[c] = (uint32_t)count;
+        K.p_max[c] = (uint16_t)vmax;
+        if (P.packed_sum64) static_cast<unsigned long long*>(K.p_sum)[c] = total;
+        else static_cast<uint32_t*>(K.p_sum)[c] = (uint32_t)total;
+    }
+    if (count == 0) {
+        const size_t ncell = (size_t)K.n_keys * P.n_windows;
+        for (uint32_t iq = 0; iq < P.n_q; ++iq) {
+            K.o_pct[iq * ncell + c] = nan_f64();
+            if (K.p_rank) {
+                if (P.u16) static_cast<uint32_t*>(K.p_rank)[iq * ncell + c] = 0;
+                else static_cast<uint16_t*>(K.p_rank)[iq * ncell + c] = 0;
+            }
+        }
+    }
 }
 
 // ---- private histogram layouts -----------------------------------------------------------------
@@ -239,18 +283,13 @@ __device__ __forceinline__ void select2(uint32_t base, uint32_t count, uint32_t 
 template <class L>
 __device__ __forceinline__ void select_store(uint32_t base, const FinParams& P, const FinKind& K, uint32_t c,
                                              uint32_t count, uint32_t vmax, uint32_t twin_cell = kInvalid) {
-    const uint32_t ncell = K.n_keys * P.n_windows;
     for (uint32_t iq = 0; iq < P.n_q; ++iq) {
         uint32_t ilo, ihi, vlo, vhi;
         double wt;
         pct_ranks(P.q[iq], count, ilo, ihi, wt);
         select2<L>(base, count, vmax, ilo, ihi, vlo, vhi);
-        const double res = pct_lerp(vlo, vhi, wt);
-        K.o_pct[(size_t)iq * ncell + c] = res;
-        if (twin_cell != kInvalid) {
-            const FinKind& G = P.kind[P.twin_gpu];
-            G.o_pct[(size_t)iq * (G.n_keys * P.n_windows) + twin_cell] = res;
-        }
+        store_pct(P, K, c, iq, vlo, vhi, wt);
+        if (twin_cell != kInvalid) store_pct(P, P.kind[P.twin_gpu], twin_cell, iq, vlo, vhi, wt);
     }
 }
 
@@ -292,10 +331,7 @@ __global__ void __launch_bounds__(CellLayout::NT) k_finalize_cells(const __grid_
             total += K.sum[pc0 + d];
             vmax = max(vmax, K.mx[pc0 + d]);
         }
-        K.o_count[c] = (uint32_t)count;
-        K.o_sum[c] = total;
-        K.o_max[c] = vmax;
-        K.o_mean[c] = count ? __ddiv_rn((double)total, (double)count) : 0.0;
+        store_basics(P, K, c, count, total, vmax);
     }
     // a run log that overflowed holds incomplete lists: the host reports the error, skip selection
     if (P.n_q == 0 || P.ctl[1]) return;
@@ -314,10 +350,6 @@ __global__ void __launch_bounds__(CellLayout::NT) k_finalize_cells(const __grid_
                 P.wide_list[2 * at + 1] = c;
             }
         }
-    }
-    if (live && count == 0) {
-        const uint32_t ncell = K.n_keys * P.n_windows;
-        for (uint32_t iq = 0; iq < P.n_q; ++iq) K.o_pct[(size_t)iq * ncell + c] = nan_f64();
     }
     // Twin cells.  With one process per GPU a (gpu, window) cell and its (pod, window) cell usually
     // consist of the very same single run, and k_accum wrote that run's descriptors side by side
@@ -401,7 +433,6 @@ __global__ void __launch_bounds__(128) k_finalize_big(const __grid_constant__ Fi
         const uint32_t c = P.big_list[2 * it + 1];
         const uint32_t key = c / P.n_windows, j = c - key * P.n_windows;
         const uint32_t pc0 = key * P.n_panes + j;
-        const uint32_t ncell = K.n_keys * P.n_windows;
         for (uint32_t b = lane; b < 256; b += 32) hist[b] = 0;
         __syncwarp();
         for (uint32_t d = 0; d < P.W; ++d) {
@@ -427,7 +458,7 @@ __global__ void __launch_bounds__(128) k_finalize_big(const __grid_constant__ Fi
                     if (ihi - cum < cb) vhi = b;
                     cum += cb;
                 }
-                K.o_pct[(size_t)iq * ncell + c] = pct_lerp(vlo, vhi, w);
+                store_pct(P, K, c, iq, vlo, vhi, w);
             }
         }
         __syncwarp();
@@ -450,7 +481,6 @@ __global__ void __launch_bounds__(128) k_finalize_u16(const __grid_constant__ Fi
         const FinKind& K = P.kind[P.wide_list[2 * it]];
         const uint32_t c = P.wide_list[2 * it + 1];
         const uint32_t key = c / P.n_windows, pc0 = key * P.n_panes + (c - key * P.n_windows);
-        const uint32_t ncell = K.n_keys * P.n_windows;
         const uint32_t count = K.o_count[c];
         // digit pass over the cell's runs: `want` < 256 restricts to values with that high byte
         auto digit_pass = [&](uint32_t want) {
@@ -502,7 +532,7 @@ __global__ void __launch_bounds__(128) k_finalize_u16(const __grid_constant__ Fi
                 locate(hi_inside[2 * iq + e], ld, unused);
                 val[e] = (hd << 8) | ld;
             }
-            if (lane == 0) K.o_pct[(size_t)iq * ncell + c] = pct_lerp(val[0], val[1], wq[iq]);
+            if (lane == 0) store_pct(P, K, c, iq, val[0], val[1], wq[iq]);
         }
         __syncwarp();
     }

@@ -29,14 +29,7 @@ __global__ void __launch_bounds__(256) k_finalize_basic(const __grid_constant__ 
         total += K.sum[pc0 + d];
         vmax = max(vmax, K.mx[pc0 + d]);
     }
-    K.o_count[c] = (uint32_t)count;
-    K.o_sum[c] = total;
-    K.o_max[c] = vmax;
-    K.o_mean[c] = count ? __ddiv_rn((double)total, (double)count) : 0.0;
-    if (count == 0) {
-        const uint32_t ncell = K.n_keys * P.n_windows;
-        for (uint32_t iq = 0; iq < P.n_q; ++iq) K.o_pct[(size_t)iq * ncell + c] = nan_f64();
-    }
+    store_basics(P, K, c, count, total, vmax);
 }
 
 // One thread per (key kind, key, chunk of P.slide_chunk windows); a warp's lanes are consecutive
@@ -69,7 +62,6 @@ __global__ void __launch_bounds__(CellLayout::NT) k_finalize_slide(const __grid_
     const uint32_t j0 = live ? (idx - key * chunks_per_key) * C : 0;
     const uint32_t j1 = live ? min(P.n_windows, j0 + C) : 0;
     const uint32_t prow = key * P.n_panes;          // first pane cell of the key
-    const uint32_t ncell = K.n_keys * P.n_windows;
     uint32_t count = 0, vub = 0;                    // samples in the window; upper bound of its values
     bool bad = false;                               // met a value the 128-bin histogram cannot hold
     // first window of the chunk: count its W panes
@@ -121,7 +113,7 @@ __global__ void __launch_bounds__(CellLayout::NT) k_finalize_slide(const __grid_
                 double wt;
                 pct_ranks(P.q[iq], count, ilo, ihi, wt);
                 select2<L>(base, count, vub, ilo, ihi, vlo, vhi);
-                K.o_pct[(size_t)iq * ncell + c] = pct_lerp(vlo, vhi, wt);
+                store_pct(P, K, c, iq, vlo, vhi, wt);
             }
         }
     }

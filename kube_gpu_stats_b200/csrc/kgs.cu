@@ -45,6 +45,10 @@ struct KindState {
     uint32_t* o_max = nullptr;
     double* o_mean = nullptr;
     double* o_pct = nullptr;
+    void* p_sum = nullptr;
+    uint32_t* p_count = nullptr;
+    uint16_t* p_max = nullptr;
+    void* p_rank = nullptr;
 };
 
 struct TimedLaunch {
@@ -76,6 +80,8 @@ struct kgs_ctx {
     uint32_t* wide_list = nullptr;
     uint32_t big_cap = 0, wide_cap = 0;
     size_t result_off = 0, result_bytes = 0, exchange_bytes = 0;
+    bool packed_exchange = false, packed_on = false, packed_sum64 = false;   // option; state of the open job
+    size_t packed_off = 0, packed_bytes = 0;
     uint64_t vals_cap = 0, vals_used = 0, accumulated = 0;
     uint32_t desc_cap = 0, desc_pool_base = 0, desc_priv_next = 0;
     uint64_t run_cap_override = 0;
@@ -511,6 +517,25 @@ int kgs_stats_begin(kgs_handle h, const kgs_window_spec* sp) {
         if (!(sp->key_mask & (1u << k))) continue;
         lay[k].omean = off; off = align_up(off + (uint64_t)nk_in[k] * sp->n_windows * 8, 256);
     }
+    // optional packed exchange tables: sum (u32 if a cell's sum provably fits, else u64), count u32,
+    // max u16, and per percentile the two selected values (u8 pair, u16 pair for fb_mib)
+    const bool packed = h->packed_exchange;
+    const uint64_t metric_max = sp->metric == KGS_METRIC_FB ? 65535u : 255u;
+    const bool sum64 = total_hint * metric_max >= (1ull << 32);
+    const size_t rank_bytes = sp->metric == KGS_METRIC_FB ? 4 : 2;
+    struct PLay { size_t sum, cnt, mx, rank; } play[3];
+    const size_t packed_begin = off;
+    if (packed) {
+        for (int k = 0; k < 3; ++k) {
+            if (!(sp->key_mask & (1u << k))) continue;
+            const uint64_t wc = (uint64_t)nk_in[k] * sp->n_windows;
+            play[k].sum = off; off = align_up(off + wc * (sum64 ? 8 : 4), 256);
+            play[k].cnt = off; off = align_up(off + wc * 4, 256);
+            play[k].mx = off; off = align_up(off + wc * 2, 256);
+            play[k].rank = off; off = align_up(off + wc * rank_bytes * sp->n_q, 256);
+        }
+    }
+    const size_t packed_end = off;
     // two result slots, used by alternate jobs: a caller may still be moving job i's tables (to the
     // host, to other GPUs) while job i+1 is being computed
     const size_t result_area = off - clear_bytes;
@@ -545,10 +570,20 @@ int kgs_stats_begin(kgs_handle h, const kgs_window_spec* sp) {
         K.o_mean = reinterpret_cast<double*>(base + slot_shift + lay[k].omean);
         K.o_pct = reinterpret_cast<double*>(base + slot_shift + lay[k].opct);
         K.o_max = reinterpret_cast<uint32_t*>(base + slot_shift + lay[k].om);
+        if (packed) {
+            K.p_sum = base + slot_shift + play[k].sum;
+            K.p_count = reinterpret_cast<uint32_t*>(base + slot_shift + play[k].cnt);
+            K.p_max = reinterpret_cast<uint16_t*>(base + slot_shift + play[k].mx);
+            K.p_rank = sp->n_q ? base + slot_shift + play[k].rank : nullptr;
+        }
     }
     h->result_off = clear_bytes + slot_shift;
     h->result_bytes = result_area;
     h->exchange_bytes = exchange_end - clear_bytes;
+    h->packed_on = packed;
+    h->packed_sum64 = sum64;
+    h->packed_off = packed_begin + slot_shift;
+    h->packed_bytes = packed_end - packed_begin;
     h->big_list = reinterpret_cast<uint32_t*>(base + big_off);
     h->big_cap = big_cap;
     h->wide_list = reinterpret_cast<uint32_t*>(base + wide_off);
@@ -680,6 +715,7 @@ int kgs_stats_finalize(kgs_handle h) {
         F.cell_begin = cells;
         F.cnt = K.cnt; F.sum = K.sum; F.mx = K.mx; F.head = K.head;
         F.o_count = K.o_count; F.o_sum = K.o_sum; F.o_max = K.o_max; F.o_mean = K.o_mean; F.o_pct = K.o_pct;
+        F.p_sum = K.p_sum; F.p_count = K.p_count; F.p_max = K.p_max; F.p_rank = K.p_rank;
         const uint64_t wc = (uint64_t)K.n_keys * sp.n_windows;
         if (cells + wc >= (1ull << 32)) return fail(h, KGS_ERR_ARG, "too many window cells");
         cells += (uint32_t)wc;
@@ -706,6 +742,7 @@ int kgs_stats_finalize(kgs_handle h) {
     P.wide_cap = h->wide_cap;
     P.u16 = sp.metric == KGS_METRIC_FB ? 1u : 0u;
     P.slide_chunk = h->slide_chunk;
+    P.packed_sum64 = h->packed_sum64 ? 1u : 0u;
     cudaStream_t st = h->compute;
     if (cells) {
         if (h->W > 1 && h->slide && sp.metric != KGS_METRIC_FB) {
@@ -800,6 +837,45 @@ int kgs_result_region(kgs_handle h, void** d_ptr, size_t* exchange_bytes, size_t
     *d_ptr = static_cast<char*>(h->arena.p) + h->result_off;
     *exchange_bytes = h->exchange_bytes;
     *total_bytes = h->result_bytes;
+    return KGS_OK;
+}
+
+int kgs_set_packed_exchange(kgs_handle h, int on) {
+    if (!h) return KGS_ERR_ARG;
+    h->packed_exchange = on != 0;
+    return KGS_OK;
+}
+
+int kgs_exchange_region(kgs_handle h, void** d_ptr, size_t* nbytes, int* packed) {
+    if (!h || !d_ptr || !nbytes) return KGS_ERR_ARG;
+    if (!h->job_final) return fail(h, KGS_ERR_STATE, "kgs_exchange_region: no finalized job");
+    if (h->packed_on) {
+        *d_ptr = static_cast<char*>(h->arena.p) + h->packed_off;
+        *nbytes = h->packed_bytes;
+    } else {
+        *d_ptr = static_cast<char*>(h->arena.p) + h->result_off;
+        *nbytes = h->exchange_bytes;
+    }
+    if (packed) *packed = h->packed_on ? (h->packed_sum64 ? 2 : 1) : 0;
+    return KGS_OK;
+}
+
+int kgs_packed_offset(kgs_handle h, int key_kind, int which, size_t* offset, size_t* nbytes) {
+    if (!h || !offset || !nbytes) return KGS_ERR_ARG;
+    if (!h->job_final || !h->packed_on) return fail(h, KGS_ERR_STATE, "kgs_packed_offset: no finalized job with packed exchange tables");
+    if (key_kind < 0 || key_kind > 2 || !(h->spec.key_mask & (1u << key_kind))) return fail(h, KGS_ERR_ARG, "key kind not part of this job");
+    const KindState& K = h->kind[key_kind];
+    const size_t wc = (size_t)K.n_keys * h->spec.n_windows;
+    const char* base = static_cast<char*>(h->arena.p) + h->packed_off;
+    const void* p;
+    switch (which) {
+        case 0: p = K.p_count; *nbytes = wc * 4; break;
+        case 1: p = K.p_sum; *nbytes = wc * (h->packed_sum64 ? 8 : 4); break;
+        case 2: p = K.p_max; *nbytes = wc * 2; break;
+        case 4: p = K.p_rank ? K.p_rank : K.p_max; *nbytes = K.p_rank ? wc * (h->spec.metric == KGS_METRIC_FB ? 4 : 2) * h->spec.n_q : 0; break;
+        default: return fail(h, KGS_ERR_ARG, "which must be 0 (count), 1 (sum), 2 (max) or 4 (selected values)");
+    }
+    *offset = (size_t)(static_cast<const char*>(p) - base);
     return KGS_OK;
 }
 

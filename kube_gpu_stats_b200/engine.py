@@ -238,6 +238,31 @@ class Engine:
         self._ck(self._lib.kgs_result_region(self._h, C.byref(p), C.byref(e), C.byref(t)))
         return p.value, e.value, t.value
 
+    def set_packed_exchange(self, on):
+        """From the next job on, finalize also writes the packed exchange tables (include/kgs.h)."""
+        self._ck(self._lib.kgs_set_packed_exchange(self._h, 1 if on else 0))
+
+    def exchange_region(self):
+        """(device address, bytes, packed flag) of what one collective has to move for this job."""
+        p, n, k = C.c_void_p(), C.c_size_t(), C.c_int()
+        self._ck(self._lib.kgs_exchange_region(self._h, C.byref(p), C.byref(n), C.byref(k)))
+        return p.value, n.value, k.value
+
+    def packed_layout(self, kinds):
+        """{kind: {table: (offset, nbytes)}} of the packed exchange tables, plus what decoding needs."""
+        sp = self._spec
+        out = {'n_windows': sp.n_windows, 'qs': [sp.q[i] for i in range(sp.n_q)], 'u16': sp.metric == _ffi.METRIC_FB,
+               'sum64': self.exchange_region()[2] == 2, 'kinds': {}}
+        for k in kinds:
+            t = {}
+            for name, which in (('count', 0), ('sum', 1), ('max', 2), ('rank', 4)):
+                off, nb = C.c_size_t(), C.c_size_t()
+                self._ck(self._lib.kgs_packed_offset(self._h, KIND_ID[k], which, C.byref(off), C.byref(nb)))
+                t[name] = (off.value, nb.value)
+            t['n_cells'] = self._n_keys[k] * sp.n_windows
+            out['kinds'][k] = t
+        return out
+
     # -- the reference's statistic ------------------------------------------------------
     def segmented_mean(self, values, offsets, mul=0.0, div=0.0):
         values = np.ascontiguousarray(values, dtype=np.float64)

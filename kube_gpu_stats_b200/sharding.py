@@ -89,7 +89,7 @@ class TableGather:
 
     def _buffers(self):
         import torch
-        ptr, nbytes, _ = self.eng.result_region()      # the exchange part only: 16 + 8*n_q bytes per cell
+        ptr, nbytes, _ = self.eng.exchange_region()    # packed tables when on, else 16 + 8*n_q bytes per cell
         v = self._views.get(ptr)
         if v is None or v[0].numel() != nbytes:
             dev = torch.device('cuda', self.eng.device)
@@ -134,6 +134,39 @@ class TableGather:
         if self._side is not None:
             torch.cuda.current_stream().wait_stream(self._side)
             self._side.synchronize()
+
+
+def decode_packed(buf, layout):
+    """One shard's packed exchange region (uint8 array) -> {kind: {count,sum,max,mean,pct}}.
+    mean and the percentiles are recomputed with the sender's own operation order (one fp64 divide;
+    rule R5: rank = q*(n-1), v[lo]*(1-w) + v[hi]*w), so they equal the sender's tables bit for bit."""
+    buf = np.ascontiguousarray(buf, dtype=np.uint8)
+    out = {}
+    for kind, t in layout['kinds'].items():
+        n = t['n_cells']
+
+        def arr(name, dt):
+            off, nb = t[name]
+            return buf[off:off + nb].view(dt)
+        count = arr('count', np.uint32).astype(np.uint64)
+        total = arr('sum', np.uint64 if layout['sum64'] else np.uint32).astype(np.uint64)
+        vmax = arr('max', np.uint16).astype(np.uint32)
+        cf = count.astype(np.float64)
+        mean = np.divide(total.astype(np.float64), cf, out=np.zeros(n), where=count > 0)
+        qs = layout['qs']
+        pct = np.full((len(qs), n), np.nan)
+        if qs:
+            ranks = arr('rank', np.uint32 if layout['u16'] else np.uint16).reshape(len(qs), n).astype(np.uint32)
+            shift, mask = (16, 0xFFFF) if layout['u16'] else (8, 0xFF)
+            nz = count > 0
+            for iq, q in enumerate(qs):
+                vlo = (ranks[iq] & mask).astype(np.float64)
+                vhi = (ranks[iq] >> shift).astype(np.float64)
+                rank = np.float64(q) * (cf - 1.0)
+                w = rank - np.floor(rank)
+                pct[iq, nz] = (vlo * (1.0 - w) + vhi * w)[nz]
+        out[kind] = {'count': count, 'sum': total, 'max': vmax, 'mean': mean, 'pct': pct}
+    return out
 
 
 # ---- host-memory variant of the exchange (any torch.distributed backend, e.g. gloo) -------------

@@ -183,6 +183,30 @@ def test_fetch_all_single_copy_equals_per_table_fetch(engine, cfg1):
             assert_stats_equal(engine.fetch(k), oracle(tr, k, 'mem', tr.t0, 60, 60, 60, QS), what='mem ' + k)
 
 
+@pytest.mark.parametrize('metric,step,width', [('sm', 60, 60), ('mem', 10, 50), ('fb', 300, 300)])
+def test_packed_exchange_tables_decode_to_the_full_tables(engine, cfg1, metric, step, width):
+    """What a peer GPU receives (10 + 2*n_q bytes per cell) must rebuild the sender's tables bit for bit."""
+    import torch
+    from kube_gpu_stats_b200 import sharding
+    tr = cfg1
+    kinds = ('pod', 'gpu', 'node')
+    engine.set_packed_exchange(True)
+    engine.set_run_log_capacity(2 * 3 * (tr.n + 8 * 4096))
+    engine.build_join(tr.keys, tr.pod_ids, tr.n_pods)
+    engine.ingest(tr.ts, tr.gpu_gid, tr.pid, tr.util)
+    spec = engine.make_spec(kinds=kinds, metric=metric, gpus_per_node=8, t0=tr.t0, step=step, width=width,
+                            n_windows=40, n_gpus=tr.n_gpus, n_nodes=tr.n_nodes, qs=QS, total_samples_hint=tr.n)
+    engine.window_stats_device(spec)
+    full = {k: engine.fetch(k) for k in kinds}
+    ptr, nbytes, packed = engine.exchange_region()
+    assert packed == (2 if metric == 'fb' else 1) and nbytes < engine.result_region()[1]   # fb sums may pass 2^32: u64
+    src = torch.as_tensor(sharding._DeviceBytes(ptr, nbytes), device='cuda:0')
+    got = sharding.decode_packed(src.cpu().numpy(), engine.packed_layout(kinds))
+    for k in kinds:
+        assert_stats_equal(got[k], full[k], what='packed %s %s' % (metric, k))
+        assert_stats_equal(full[k], oracle(tr, k, metric, tr.t0, step, width, 40, QS), what='oracle %s %s' % (metric, k))
+
+
 def test_state_and_argument_errors(engine, cfg1):
     from kube_gpu_stats_b200 import _ffi
     from kube_gpu_stats_b200.engine import KgsError
