@@ -630,6 +630,8 @@ int kgs_stats_accumulate(kgs_handle h) {
     if (B.n == 0) return KGS_OK;
     const kgs_window_spec& sp = h->spec;
     const bool pct = sp.n_q > 0;
+    if (h->accumulated + B.n >= (1ull << 32))
+        return fail(h, KGS_ERR_CAPACITY, "a job holds fewer than 2^32 samples per handle (cell counts are 32-bit); shard the trace");
     if (pct && h->vals_used + B.n + 16 > h->vals_cap)
         return fail(h, KGS_ERR_CAPACITY, "value log full: total_samples_hint was smaller than the samples accumulated");
     AccumParams P{};
