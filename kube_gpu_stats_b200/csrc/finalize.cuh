@@ -7,7 +7,7 @@
 // One THREAD owns one window cell and counts into a PRIVATE histogram in shared memory whose
 // layout keeps thread t on bank t%32 (conflict free, no atomics).  Three kernels:
 //   k_finalize_cells every cell: count/sum/max/mean; percentiles when the cell has <= 65 535
-//                    samples and max < 128 (u16 bins, 256 B per thread, 128 threads per CTA);
+//                    samples and max < 104 (u16 bins, 208 B per thread, 128 threads per CTA, 8 CTAs/SM);
 //                    other non-empty cells are appended to the wide list;
 //   k_finalize_wide  values up to 255, cells up to 65 535 samples (64 threads per CTA);
 //   k_finalize_big   anything larger, one warp per cell with u32 bins.
@@ -155,7 +155,7 @@ struct Layout16 {
         sts_u16(ab, vb);
     }
 };
-using CellLayout = Layout16<128, 128>;   // values 0..127: 256 B per thread, 32 KB per CTA of 128 threads
+using CellLayout = Layout16<128, 104>;   // values 0..103 (a utilisation is 0..100): 208 B per thread, 26 KB per CTA of 128 threads
 using WideLayout = Layout16<64, 256>;    // values 0..255: 512 B per thread, 32 KB per CTA of 64 threads
 
 // delta = 1 counts a value in, delta = 0xFFFF (-1 modulo 2^16, the bins are u16) takes it out again
@@ -301,9 +301,9 @@ __device__ __forceinline__ const FinKind& kind_of_cell(const FinParams& P, uint3
 }
 
 // Every window cell: count / sum / max / mean, and the percentiles of cells with up to 65 535
-// samples whose values stay below 128.  Cells are visited from the END of the index space
+// samples whose values stay below 104.  Cells are visited from the END of the index space
 // (node cells, the heaviest, are scheduled first).  Other non-empty cells go to the wide list.
-__global__ void __launch_bounds__(CellLayout::NT) k_finalize_cells(const __grid_constant__ FinParams P) {
+__global__ void __launch_bounds__(CellLayout::NT, 8) k_finalize_cells(const __grid_constant__ FinParams P) {
     using L = CellLayout;
     __shared__ uint32_t hist[L::WORDS * L::NT];
     const uint32_t tid = threadIdx.x;

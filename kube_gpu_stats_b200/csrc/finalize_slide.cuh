@@ -6,7 +6,7 @@
 // window j+1 it takes pane j out (delta 0xFFFF = -1 in the u16 bins) and counts pane j+W in, then
 // selects.  Only the first window of a chunk counts W panes.  Same exact selection (rule R5).
 //   * count / sum / max / mean of every window cell come from k_finalize_basic (no shared memory);
-//   * a chunk that meets a value >= 128 or a window above 65 535 samples hands its windows to the
+//   * a chunk that meets a value >= 104 or a window above 65 535 samples hands its windows to the
 //     wide list (k_finalize_wide / k_finalize_big count them the slow way).
 #pragma once
 #include "finalize.cuh"
@@ -63,7 +63,7 @@ __global__ void __launch_bounds__(CellLayout::NT) k_finalize_slide(const __grid_
     const uint32_t j1 = live ? min(P.n_windows, j0 + C) : 0;
     const uint32_t prow = key * P.n_panes;          // first pane cell of the key
     uint32_t count = 0, vub = 0;                    // samples in the window; upper bound of its values
-    bool bad = false;                               // met a value the 128-bin histogram cannot hold
+    bool bad = false;                               // met a value the 104-bin histogram cannot hold
     // first window of the chunk: count its W panes
     for (uint32_t d = 0; d < P.W; ++d) {
         uint32_t at = 0;
