@@ -274,8 +274,11 @@ __global__ void __launch_bounds__(kAccumWarps * 32) k_accum(const __grid_constan
             const uint32_t left = P.step - (x0 - pn0 * P.step);          // samples from t[0] to the end of pane pn0
             const uint32_t p_a = pn0 < P.n_panes ? pn0 : kInvalid;
             const uint32_t p_b = pn0 + 1 < P.n_panes ? pn0 + 1 : kInvalid;
+            // only the lane's first and last pane are used below (the per-sample panes matter to lanes with
+            // two or more boundaries, which a dense tile cannot have)
 #pragma unroll
-            for (int j = 0; j < 8; ++j) pane[j] = (uint32_t)j < left ? p_a : p_b;
+            for (int j = 0; j < 7; ++j) pane[j] = p_a;
+            pane[7] = left < 8 ? p_b : p_a;
             if (left < 8 && p_a != p_b) bm = 1u << left;
         } else {
             const uint32_t lim = full ? 8u : (P.n > i0 ? P.n - i0 : 0u);   // samples of this lane inside the batch
@@ -406,7 +409,7 @@ __global__ void __launch_bounds__(kAccumWarps * 32) k_accum(const __grid_constan
         // lanes with two or more boundaries: the pieces between the first and the last are retired
         // directly (rare in collector order; every lane in shuffled input, then 32 wide)
         const bool many = (bm & (bm - 1)) != 0;
-        const uint32_t many_mask = __ballot_sync(kAll, many);
+        const uint32_t many_mask = dense ? 0u : __ballot_sync(kAll, many);
         if (P.agg_on && __popc(many_mask) >= 16) agg = &table;
         if (many_mask) {
             uint32_t nr = 0;
