@@ -140,11 +140,13 @@ int kgs_stats_begin(kgs_handle h, const kgs_window_spec* spec);
 int kgs_stats_accumulate(kgs_handle h);
 int kgs_stats_finalize(kgs_handle h);
 int kgs_window_stats(kgs_handle h, const kgs_window_spec* spec);
-/* Capacity, in entries of 16 B, of the run log the next percentile job allocates (0 = automatic:
- * sized for runs of min(8, step/2) samples, ample for collector-ordered input at 1 Hz).  Three quarters
- * of the log are handed out as private slabs per warp, one quarter is a shared overflow pool; with a
- * capacity set here the slabs are sized for the worst case (every sample its own run), which needs
- * entries >= 2 * samples * key kinds (rounded up per 256-sample tile). */
+/* Run-log sizing.  0 (default) = automatic: the log (16 B entries) is sized for runs of
+ * min(8, step/2) samples, ample for collector-ordered input at 1 Hz; a quarter of it is a shared
+ * overflow pool, the rest is handed out as private slabs per warp and launch, and the log grows
+ * when a job brings more batches than total_samples_hint announced.  A non-zero value declares
+ * input whose order is unknown or far from collector order (a time-major live feed, a shuffled
+ * stream): it is the initial capacity, and every slab is sized for the worst case of one run per
+ * sample.  A job that still overflows the pool fails at fetch time with KGS_ERR_CAPACITY. */
 int kgs_set_run_log_capacity(kgs_handle h, uint64_t entries);
 /* Copy one key kind's result table to host arrays of n_keys * n_windows entries, cell index
  * key * n_windows + window (pct: n_q rows of that length).  Any pointer may be NULL. Blocking. */

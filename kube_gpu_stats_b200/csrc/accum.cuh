@@ -64,7 +64,7 @@ struct AccumParams {
     uint32_t desc_cap;
     uint32_t log_base;             // this launch's private run-log slab: warp w owns
     uint32_t log_per_warp;         //   [log_base + w*log_per_warp, +log_per_warp)
-    uint32_t pool_base;            // shared overflow pool [pool_base, desc_cap), cursor ctl[0]
+    uint32_t pool_end;             // shared overflow pool = entries [0, pool_end), cursor ctl[0]
     uint32_t* ctl;                 // ctl[0] pool cursor, ctl[1] overflow flag
     uint32_t agg_on;               // every cell index < 2^30: the per-CTA accumulator cache may be used
     uint32_t dense_ok;             // step >= 8 and no sampled windows: the dense-tile shortcut applies
@@ -167,8 +167,8 @@ __device__ __forceinline__ uint32_t reserve_log(const AccumParams& P, LogCursor&
     }
     uint32_t base = 0;
     if (lane_id() == 0) base = atomicAdd(P.ctl, count);
-    base = __shfl_sync(0xFFFFFFFFu, base, 0) + P.pool_base;
-    log_ok = (uint64_t)base + count <= P.desc_cap;
+    base = __shfl_sync(0xFFFFFFFFu, base, 0);
+    log_ok = (uint64_t)base + count <= P.pool_end;
     if (!log_ok && lane_id() == 0) P.ctl[1] = 1;
     return base;
 }

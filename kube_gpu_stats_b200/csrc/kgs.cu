@@ -130,6 +130,20 @@ int reserve(kgs_handle h, DevBuf& b, size_t bytes) {
     return KGS_OK;
 }
 
+// Grow a device buffer that holds live data: allocate, copy the first `keep` bytes, free the old one.
+// The compute stream is drained first (queued kernels hold pointers into the old allocation).
+int grow_copy(kgs_handle h, DevBuf& b, size_t bytes, size_t keep) {
+    if (bytes <= b.cap) return KGS_OK;
+    KGS_CUDA(h, cudaStreamSynchronize(h->compute));
+    DevBuf bigger;
+    int rc = reserve(h, bigger, bytes);
+    if (rc) return rc;
+    if (keep && b.p) KGS_CUDA(h, cudaMemcpy(bigger.p, b.p, keep, cudaMemcpyDeviceToDevice));
+    if (b.p) KGS_CUDA(h, cudaFree(b.p));
+    b = bigger;
+    return KGS_OK;
+}
+
 cudaEvent_t pooled_event(kgs_handle h) {
     if (!h->event_pool.empty()) {
         cudaEvent_t e = h->event_pool.back();
@@ -604,8 +618,8 @@ int kgs_stats_begin(kgs_handle h, const kgs_window_spec* sp) {
         if ((rc = reserve(h, h->desc, dcap * 16))) return rc;
         h->vals_cap = vals_cap;
         h->desc_cap = (uint32_t)dcap;
-        h->desc_pool_base = (uint32_t)(dcap - dcap / 4);   // last quarter: shared overflow pool
-        h->desc_priv_next = 0;
+        h->desc_pool_base = (uint32_t)(dcap / 4);          // entries [0, desc_pool_base): shared overflow pool
+        h->desc_priv_next = h->desc_pool_base;             // private slabs follow and grow upwards
     } else {
         h->vals_cap = 0;
         h->desc_cap = 0;
@@ -632,8 +646,15 @@ int kgs_stats_accumulate(kgs_handle h) {
     const bool pct = sp.n_q > 0;
     if (h->accumulated + B.n >= (1ull << 32))
         return fail(h, KGS_ERR_CAPACITY, "a job holds fewer than 2^32 samples per handle (cell counts are 32-bit); shard the trace");
-    if (pct && h->vals_used + B.n + 16 > h->vals_cap)
-        return fail(h, KGS_ERR_CAPACITY, "value log full: total_samples_hint was smaller than the samples accumulated");
+    if (pct && h->vals_used + B.n + 16 > h->vals_cap) {   // total_samples_hint was too small: enlarge the value log
+        const uint64_t vbytes = sp.metric == KGS_METRIC_FB ? 2 : 1;
+        uint64_t want = 2 * h->vals_cap;
+        if (want < h->vals_used + B.n + 65536) want = h->vals_used + B.n + 65536;
+        if (want >= (1ull << 32)) return fail(h, KGS_ERR_CAPACITY, "percentile jobs hold fewer than 2^32 samples per handle; shard the trace");
+        int rc2 = grow_copy(h, h->vals, want * vbytes, (size_t)h->vals_used * vbytes);
+        if (rc2) return rc2;
+        h->vals_cap = want;
+    }
     AccumParams P{};
     P.ts = B.ptr[0]; P.gid = B.ptr[1]; P.pid = B.ptr[2]; P.util = B.ptr[3];
     P.n = (uint32_t)B.n;
@@ -679,11 +700,21 @@ int kgs_stats_accumulate(kgs_handle h) {
         const uint64_t run_guess = sp.step / 2 < 2 ? 2 : (sp.step / 2 > 8 ? 8 : sp.step / 2);
         uint64_t per_warp = (uint64_t)P.tiles_per_warp * (kTileSamples / run_guess) * __builtin_popcount(sp.key_mask);
         if (h->run_cap_override) per_warp = (uint64_t)P.tiles_per_warp * kTileSamples * __builtin_popcount(sp.key_mask);   // every sample its own run
-        const uint64_t room = h->desc_pool_base - h->desc_priv_next;
-        if (per_warp * warps > room) per_warp = room / warps;
+        if ((uint64_t)h->desc_priv_next + per_warp * warps > h->desc_cap) {
+            // more (or smaller) batches than the sizing assumed: enlarge the log, entries keep their indices
+            uint64_t want = 2ull * h->desc_cap;
+            if (want < (uint64_t)h->desc_priv_next + per_warp * warps) want = (uint64_t)h->desc_priv_next + per_warp * warps;
+            if (want > 0xFFFFFFF0ull) want = 0xFFFFFFF0ull;
+            if ((uint64_t)h->desc_priv_next + per_warp * warps > want) per_warp = (want - h->desc_priv_next) / warps;
+            int rc2 = grow_copy(h, h->desc, want * 16, (size_t)h->desc_priv_next * 16);
+            if (rc2) return rc2;
+            h->desc_cap = (uint32_t)want;
+            P.desc = static_cast<uint4*>(h->desc.p);
+            P.desc_cap = h->desc_cap;
+        }
         P.log_base = h->desc_priv_next;
         P.log_per_warp = (uint32_t)per_warp;
-        P.pool_base = h->desc_pool_base;
+        P.pool_end = h->desc_pool_base;
         h->desc_priv_next += (uint32_t)(per_warp * warps);
     }
     launch(h, KGS_K_ACCUM, st, [&] {

@@ -207,6 +207,32 @@ def test_packed_exchange_tables_decode_to_the_full_tables(engine, cfg1, metric, 
         assert_stats_equal(full[k], oracle(tr, k, metric, tr.t0, step, width, 40, QS), what='oracle %s %s' % (metric, k))
 
 
+@pytest.mark.parametrize('order', ['collector', 'time_major'])
+def test_many_tiny_batches_grow_the_logs(engine, order):
+    """A live feed: hundreds of small batches and a total_samples_hint that is far too small.  The run
+    log and the value log have to grow (entries keep their indices) and the tables stay exact.
+    Time-major delivery (all GPUs of one second together) makes every sample its own run: such a
+    feed declares it with kgs_set_run_log_capacity, which sizes the per-warp slabs for the worst case."""
+    tr = synth.cluster_trace(2, 8, 1, 3000, n_tenancies=20, seed=11)
+    ts, gid, pid, util = tr.ts, tr.gpu_gid, tr.pid, tr.util
+    if order == 'time_major':
+        p = np.argsort(tr.ts, kind='stable')
+        ts, gid, pid, util = ts[p], gid[p], pid[p], util[p]
+        engine.set_run_log_capacity(4096)                        # any value: slabs for the worst case, the log grows
+    live = synth.Trace(ts, gid, pid, util, tr.keys, tr.pod_ids, tr.n_pods, tr.n_nodes, 8, tr.t0, 3000)
+    engine.build_join(tr.keys, tr.pod_ids, tr.n_pods)
+    spec = engine.make_spec(kinds=('pod', 'gpu', 'node'), metric='sm', gpus_per_node=8, t0=tr.t0, step=60,
+                            n_windows=50, n_gpus=tr.n_gpus, n_nodes=tr.n_nodes, qs=QS, total_samples_hint=1000)
+    engine.stats_begin(spec)
+    for a in range(0, live.n, 160):                              # 300 batches
+        b = min(live.n, a + 160)
+        engine.ingest(ts[a:b], gid[a:b], pid[a:b], util[a:b])
+        engine.stats_accumulate()
+    engine.stats_finalize()
+    for k in ('pod', 'gpu', 'node'):
+        assert_stats_equal(engine.fetch(k), oracle(live, k, 'sm', tr.t0, 60, 60, 50, QS), what='live feed ' + k)
+
+
 def test_state_and_argument_errors(engine, cfg1):
     from kube_gpu_stats_b200 import _ffi
     from kube_gpu_stats_b200.engine import KgsError
