@@ -88,6 +88,7 @@ struct kgs_ctx {
     uint64_t job_seq = 0;
     bool slide = true;             // W > 1 jobs keep a sliding histogram per chunk of windows (finalize_slide.cuh)
     uint32_t slide_chunk = 8;      // measured best on B200 (4: 3.0 ms, 8: 1.9, 16: 2.1, 64: 5.0 for the cfg5-shaped test)
+    int accum_waves = 2;           // CTAs per resident slot: > 1 keeps the tail short when another kernel (a collective) shares the SMs
     bool dense_path = true;
     bool accum_prefetch = false;   // register double-buffering of the next tile: 109 vs 78 registers
     int accum_ctas_per_sm = 4;     // resident CTAs of 8 warps per SM at 64 registers
@@ -234,6 +235,7 @@ int kgs_create(int device, kgs_handle* out) {
     }
     if (const char* e = getenv("KGS_SLIDE")) h->slide = atoi(e) != 0;
     if (const char* e = getenv("KGS_SLIDE_CHUNK")) { const int v = atoi(e); if (v >= 1 && v <= 4096) h->slide_chunk = (uint32_t)v; }
+    if (const char* e = getenv("KGS_ACCUM_WAVES")) { const int v = atoi(e); if (v >= 1 && v <= 16) h->accum_waves = v; }
     if (const char* e = getenv("KGS_DENSE")) h->dense_path = atoi(e) != 0;
     if (const char* e = getenv("KGS_ACCUM_PREFETCH")) h->accum_prefetch = atoi(e) != 0;
     if (const char* e = getenv("KGS_ACCUM_CTAS_PER_SM")) {   // tuning knob for experiments
@@ -689,7 +691,7 @@ int kgs_stats_accumulate(kgs_handle h) {
     KGS_CUDA(h, cudaStreamWaitEvent(st, B.ready, 0));
     // every warp owns a contiguous chunk of 256-sample tiles; ctas_per_sm resident CTAs of 8 warps
     const uint64_t n_tiles = (B.n + kTileSamples - 1) / kTileSamples;
-    const uint64_t max_warps = 148ull * h->accum_ctas_per_sm * kAccumWarps;
+    const uint64_t max_warps = 148ull * h->accum_ctas_per_sm * kAccumWarps * h->accum_waves;
     const uint64_t tpw = (n_tiles + max_warps - 1) / max_warps;
     P.tiles_per_warp = (uint32_t)(tpw < 2 ? 2 : tpw);
     const int grid = (int)((n_tiles + (uint64_t)P.tiles_per_warp * kAccumWarps - 1) / ((uint64_t)P.tiles_per_warp * kAccumWarps));
