@@ -219,8 +219,47 @@ __device__ __forceinline__ void load_oct(const AccumParams& P, uint32_t i0, bool
     }
 }
 
-template <bool PCT, bool PREFETCH>
+// ---- TMA staging (TMA = true) ----------------------------------------------------------------------
+// Each warp owns a ring of kStages tile buffers in shared memory (4 columns x 1 KB) and one mbarrier
+// per buffer.  Lane 0 arms the barrier with the 4 KB it expects and issues four 1-D bulk copies
+// (cp.async.bulk -> UBLKCP): the copy engine moves the next tiles while the warp works on the current
+// one, with no registers held for data in flight and no load instructions to issue.  The warp waits
+// on the barrier's phase bit, reads its 8 samples per column with two LDS.128, and re-arms the
+// buffer with the tile kStages ahead.  Warps never wait for each other.
+constexpr int kStages = 2;
+constexpr uint32_t kTileBytes = 4 * kTileSamples * 4;   // four u32 columns
+constexpr uint32_t kTmaSmemBytes = kAccumWarps * kStages * (kTileBytes + 8);
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}"
+                 : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar, uint64_t pol) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar), "l"(pol) : "memory");
+}
+__device__ __forceinline__ uint64_t policy_evict_first() {
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+__device__ __forceinline__ uint4 lds_v4(uint32_t a) {
+    uint4 r;
+    asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "r"(a) : "memory");
+    return r;
+}
+
+template <bool PCT, bool TMA>
 __global__ void __launch_bounds__(kAccumWarps * 32) k_accum(const __grid_constant__ AccumParams P) {
+    extern __shared__ __align__(128) unsigned char tma_smem[];   // TMA only: [warp][stage] tile buffers, then barriers
     __shared__ RunQueue queues[kAccumWarps];
     __shared__ AggTable table;
     constexpr uint32_t kAll = 0xFFFFFFFFu;
@@ -243,13 +282,53 @@ __global__ void __launch_bounds__(kAccumWarps * 32) k_accum(const __grid_constan
     uint32_t queued = 0;                               // warp-uniform
     LogCursor lc{P.log_base + warp * P.log_per_warp, P.log_per_warp};
 
-    Oct cur, nxt;
-    if (PREFETCH) load_oct(P, tile_begin * kTileSamples + 8 * lane, tile_begin < full_tiles, cur);
+    Oct cur;
+    uint32_t ring = 0, bars = 0;     // shared-space addresses of this warp's tile buffers and barriers
+    uint64_t pol_stream = 0;
+    auto tma_issue = [&](uint32_t stage, uint32_t tile) {   // lane 0 only: arm the barrier, start the four copies
+        const uint32_t dst = ring + stage * kTileBytes, bar = bars + stage * 8;
+        const size_t at = (size_t)tile * kTileSamples;
+        mbar_expect_tx(bar, kTileBytes);
+        bulk_g2s(dst, P.ts + at, kTileSamples * 4, bar, pol_stream);
+        bulk_g2s(dst + kTileSamples * 4, P.gid + at, kTileSamples * 4, bar, pol_stream);
+        bulk_g2s(dst + 2 * kTileSamples * 4, P.pid + at, kTileSamples * 4, bar, pol_stream);
+        bulk_g2s(dst + 3 * kTileSamples * 4, P.util + at, kTileSamples * 4, bar, pol_stream);
+    };
+    if (TMA) {
+        const uint32_t wib = threadIdx.x >> 5;
+        ring = (uint32_t)__cvta_generic_to_shared(tma_smem) + wib * kStages * kTileBytes;
+        bars = (uint32_t)__cvta_generic_to_shared(tma_smem) + kAccumWarps * kStages * kTileBytes + wib * kStages * 8;
+        if (lane == 0) {
+            pol_stream = policy_evict_first();
+#pragma unroll
+            for (int st = 0; st < kStages; ++st) mbar_init(bars + st * 8, 1);
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        }
+        __syncwarp();
+        if (lane == 0) {
+#pragma unroll
+            for (int st = 0; st < kStages; ++st)
+                if (tile_begin + st < tile_end && tile_begin + st < full_tiles) tma_issue(st, tile_begin + st);
+        }
+    }
     for (uint32_t tile = tile_begin; tile < tile_end; ++tile) {
         const uint32_t i0 = tile * kTileSamples + 8 * lane;
         const bool full = tile < full_tiles;
-        if (PREFETCH) {
-            if (tile + 1 < tile_end) load_oct(P, i0 + kTileSamples, tile + 1 < full_tiles, nxt);   // in flight during this tile
+        if (TMA && full) {
+            const uint32_t k = tile - tile_begin, stage = k % kStages, parity = (k / kStages) & 1u;
+            uint32_t spins = 0;
+            while (!mbar_try_wait(bars + stage * 8, parity)) {
+                if (++spins > (1u << 24)) { P.ctl[1] = 2; break; }   // never observed; a stuck copy must not hang the GPU
+            }
+            const uint32_t src = ring + stage * kTileBytes + lane * 32;
+            uint4 a = lds_v4(src), b = lds_v4(src + 16);
+            cur.t[0] = a.x; cur.t[1] = a.y; cur.t[2] = a.z; cur.t[3] = a.w; cur.t[4] = b.x; cur.t[5] = b.y; cur.t[6] = b.z; cur.t[7] = b.w;
+            a = lds_v4(src + kTileSamples * 4); b = lds_v4(src + kTileSamples * 4 + 16);
+            cur.g[0] = a.x; cur.g[1] = a.y; cur.g[2] = a.z; cur.g[3] = a.w; cur.g[4] = b.x; cur.g[5] = b.y; cur.g[6] = b.z; cur.g[7] = b.w;
+            a = lds_v4(src + 2 * kTileSamples * 4); b = lds_v4(src + 2 * kTileSamples * 4 + 16);
+            cur.p[0] = a.x; cur.p[1] = a.y; cur.p[2] = a.z; cur.p[3] = a.w; cur.p[4] = b.x; cur.p[5] = b.y; cur.p[6] = b.z; cur.p[7] = b.w;
+            a = lds_v4(src + 3 * kTileSamples * 4); b = lds_v4(src + 3 * kTileSamples * 4 + 16);
+            cur.u[0] = a.x; cur.u[1] = a.y; cur.u[2] = a.z; cur.u[3] = a.w; cur.u[4] = b.x; cur.u[5] = b.y; cur.u[6] = b.z; cur.u[7] = b.w;
         } else {
             load_oct(P, i0, full, cur);
         }
@@ -468,7 +547,11 @@ __global__ void __launch_bounds__(kAccumWarps * 32) k_accum(const __grid_constan
             queued = 1;
             __syncwarp();
         }
-        if (PREFETCH) cur = nxt;
+        if (TMA && full) {   // this tile's samples have all been consumed: refill its buffer with the tile kStages ahead
+            const uint32_t next = tile + kStages;
+            __syncwarp();
+            if (lane == 0 && next < tile_end && next < full_tiles) tma_issue((tile - tile_begin) % kStages, next);
+        }
     }
     flush_queue<PCT>(P, agg, lc, Q, queued, nk);
     if (P.agg_on) {   // write the CTA's accumulator cache out: one RED per occupied slot and statistic

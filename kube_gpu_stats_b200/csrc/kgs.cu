@@ -90,7 +90,7 @@ struct kgs_ctx {
     uint32_t slide_chunk = 8;      // measured best on B200 (4: 3.0 ms, 8: 1.9, 16: 2.1, 64: 5.0 for the cfg5-shaped test)
     int accum_waves = 2;           // CTAs per resident slot: > 1 keeps the tail short when another kernel (a collective) shares the SMs
     bool dense_path = true;
-    bool accum_prefetch = false;   // register double-buffering of the next tile: 109 vs 78 registers
+    bool accum_tma = false;        // stage tiles through shared memory with cp.async.bulk + mbarrier
     int accum_ctas_per_sm = 4;     // resident CTAs of 8 warps per SM at 64 registers
     // measurement
     uint64_t launches = 0;
@@ -237,7 +237,12 @@ int kgs_create(int device, kgs_handle* out) {
     if (const char* e = getenv("KGS_SLIDE_CHUNK")) { const int v = atoi(e); if (v >= 1 && v <= 4096) h->slide_chunk = (uint32_t)v; }
     if (const char* e = getenv("KGS_ACCUM_WAVES")) { const int v = atoi(e); if (v >= 1 && v <= 16) h->accum_waves = v; }
     if (const char* e = getenv("KGS_DENSE")) h->dense_path = atoi(e) != 0;
-    if (const char* e = getenv("KGS_ACCUM_PREFETCH")) h->accum_prefetch = atoi(e) != 0;
+    if (const char* e = getenv("KGS_ACCUM_TMA")) h->accum_tma = atoi(e) != 0;
+    if (h->accum_tma) {
+        h->accum_ctas_per_sm = 2;   // 64 KB of tile buffers + 42 KB static per CTA
+        cudaFuncSetAttribute(k_accum<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTmaSmemBytes);
+        cudaFuncSetAttribute(k_accum<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTmaSmemBytes);
+    }
     if (const char* e = getenv("KGS_ACCUM_CTAS_PER_SM")) {   // tuning knob for experiments
         const int v = atoi(e);
         if (v >= 1 && v <= 8) h->accum_ctas_per_sm = v;
@@ -720,9 +725,9 @@ int kgs_stats_accumulate(kgs_handle h) {
         h->desc_priv_next += (uint32_t)(per_warp * warps);
     }
     launch(h, KGS_K_ACCUM, st, [&] {
-        if (h->accum_prefetch) {
-            if (pct) k_accum<true, true><<<grid, 256, 0, st>>>(P);
-            else k_accum<false, true><<<grid, 256, 0, st>>>(P);
+        if (h->accum_tma) {
+            if (pct) k_accum<true, true><<<grid, 256, kTmaSmemBytes, st>>>(P);
+            else k_accum<false, true><<<grid, 256, kTmaSmemBytes, st>>>(P);
         } else {
             if (pct) k_accum<true, false><<<grid, 256, 0, st>>>(P);
             else k_accum<false, false><<<grid, 256, 0, st>>>(P);

@@ -249,3 +249,13 @@ def test_state_and_argument_errors(engine, cfg1):
     with pytest.raises(KgsError) as e:
         engine.window_stats(kinds=('gpu',), t0=cfg1.t0, step=60, n_windows=1, n_gpus=8, qs=(1.5,))
     assert e.value.code == _ffi.KGS_ERR_ARG
+
+
+def test_tma_staged_accumulate_gives_the_same_tables(built_lib, cfg1, monkeypatch):
+    """k_accum's optional TMA path (cp.async.bulk + mbarrier tile ring, KGS_ACCUM_TMA=1) against the oracle."""
+    from kube_gpu_stats_b200.engine import Engine
+    monkeypatch.setenv('KGS_ACCUM_TMA', '1')
+    tr = synth.config(2, scale=0.02)
+    with Engine(0) as eng:
+        check(eng, tr, ('pod', 'gpu', 'node'), 'sm', tr.t0, 60, 60, 60, QS)
+        check(eng, cfg1, ('pod', 'gpu', 'node'), 'mem', cfg1.t0 + 3, 7, 21, 90, (0.5,))
