@@ -259,3 +259,32 @@ def test_tma_staged_accumulate_gives_the_same_tables(built_lib, cfg1, monkeypatc
     with Engine(0) as eng:
         check(eng, tr, ('pod', 'gpu', 'node'), 'sm', tr.t0, 60, 60, 60, QS)
         check(eng, cfg1, ('pod', 'gpu', 'node'), 'mem', cfg1.t0 + 3, 7, 21, 90, (0.5,))
+
+
+def test_cfg2_full_size_properties_and_exact_slice(engine):
+    """BASELINE configs[1] at FULL size (1 000 nodes, 28.8 M samples, 10 000 pods): size-independent
+    properties on the whole result and an exact oracle comparison on the first 20 nodes."""
+    tr = synth.config(2)
+    kinds = ('pod', 'gpu', 'node')
+    got = run(engine, tr, kinds, 'sm', tr.t0, 60, 60, 60, (0.95,))
+    n_win = 60
+    for k in kinds:
+        assert int(got[k]['count'].sum()) == tr.n, k                    # every sample lands in exactly one cell per kind
+        nz = got[k]['count'] > 0
+        p95 = got[k]['pct'][0]
+        assert np.all(np.isnan(p95[~nz])) and np.all(p95[nz] <= got[k]['max'][nz]) and np.all(p95[nz] >= 0)
+        assert np.all(got[k]['mean'][nz] <= got[k]['max'][nz])
+    g = {f: np.asarray(got['gpu'][f]).reshape(tr.n_nodes, 8, n_win) for f in ('count', 'sum', 'max')}
+    np.testing.assert_array_equal(g['count'].sum(axis=1).reshape(-1), got['node']['count'])   # node = sum of its GPUs
+    np.testing.assert_array_equal(g['sum'].sum(axis=1).reshape(-1), got['node']['sum'])
+    np.testing.assert_array_equal(g['max'].max(axis=1).reshape(-1), got['node']['max'])
+    assert int(got['pod']['sum'].sum()) == int((tr.util & 0xFF).astype(np.uint64).sum())      # a checksum of checksums
+    # exact: the first 20 nodes own the first samples, GPUs and pods of the trace
+    nodes = 20
+    m = nodes * 8 * 3600
+    pods = int(np.searchsorted(tr.pod_node, nodes))
+    part = synth.Trace(tr.ts[:m], tr.gpu_gid[:m], tr.pid[:m], tr.util[:m], tr.keys, tr.pod_ids, pods, nodes, 8, tr.t0, 3600)
+    for k, nk in (('pod', pods), ('gpu', nodes * 8), ('node', nodes)):
+        want = oracle(part, k, 'sm', tr.t0, 60, 60, n_win, (0.95,))
+        head = {f: (np.asarray(v)[:, :nk * n_win] if f == 'pct' else np.asarray(v)[:nk * n_win]) for f, v in got[k].items()}
+        assert_stats_equal(head, want, what='full-size slice ' + k)
