@@ -55,6 +55,15 @@ def pack_util(sm, mem, fb):
         ((np.asarray(fb, np.uint32) & 0xFFFF) << 16)
 
 
+def series_major_order(ts, gpu_gid, pid):
+    """Permutation that puts a batch into series-major collector order: by GPU, then process, then
+    time (for one process per GPU this is the plain (gpu, time) order).  The kernels accept any
+    order and give the same tables; this order is the fast one, because consecutive samples then
+    share (gpu, pid, window) and fold into long runs - with several processes per GPU a plain
+    (gpu, time) order interleaves them and every sample becomes its own run."""
+    return np.lexsort((np.asarray(ts), np.asarray(pid), np.asarray(gpu_gid)))
+
+
 class SampleColumns:
     """Growing SoA batch (ts, gpu_gid, pid, util) over pinned memory of a fixed capacity."""
 
@@ -78,6 +87,12 @@ class SampleColumns:
 
     def views(self):
         return [c[:self.n] for c in self.cols]
+
+    def sort_series_major(self):
+        """Reorder the batch in place into (gpu, pid, time) order (see series_major_order)."""
+        order = series_major_order(*[c[:self.n] for c in self.cols[:3]])
+        for c in self.cols:
+            c[:self.n] = c[:self.n][order]
 
     def clear(self):
         self.n = 0

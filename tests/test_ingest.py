@@ -27,3 +27,11 @@ def test_pod_of_cgroup_layouts():
     assert ingest.pod_of_cgroup(cgroupfs) == '0a1b2c3d-1111-2222-3333-444455556666'
     assert ingest.pod_of_cgroup(systemd) == '0a1b2c3d-1111-2222-3333-444455556666'
     assert ingest.pod_of_cgroup("0::/user.slice/user-1000.slice/session-3.scope\\n") is None
+
+
+def test_series_major_order():
+    ts = np.array([5, 5, 5, 6, 6, 6, 5], dtype=np.uint32)
+    gid = np.array([1, 1, 0, 1, 1, 0, 0], dtype=np.uint32)
+    pid = np.array([9, 7, 3, 9, 7, 3, 2], dtype=np.uint32)
+    o = ingest.series_major_order(ts, gid, pid)
+    assert list(zip(gid[o], pid[o], ts[o])) == [(0, 2, 5), (0, 3, 5), (0, 3, 6), (1, 7, 5), (1, 7, 6), (1, 9, 5), (1, 9, 6)]

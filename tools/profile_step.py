@@ -14,12 +14,19 @@ ap.add_argument('--nodes', type=int, default=1000)
 ap.add_argument('--kinds', default='pod,gpu,node')
 ap.add_argument('--qs', default='0.95')
 ap.add_argument('--procs', type=int, default=1)
+ap.add_argument('--series-major', action='store_true', help='reorder to (gpu, pid, time) before ingest')
 args = ap.parse_args()
 tr = synth.cluster_trace(args.nodes, 8, args.procs, 3600, n_tenancies=args.nodes * 8 * args.procs * 5 // 4, seed=0)
+if args.series_major:
+    from kube_gpu_stats_b200 import ingest
+    o = ingest.series_major_order(tr.ts, tr.gpu_gid, tr.pid)
+    tr.ts, tr.gpu_gid, tr.pid, tr.util = tr.ts[o], tr.gpu_gid[o], tr.pid[o], tr.util[o]
 kinds = tuple(args.kinds.split(','))
 qs = tuple(float(q) for q in args.qs.split(',')) if args.qs else ()
 with Engine(0) as eng:
     eng.build_join(tr.keys, tr.pod_ids, tr.n_pods)
+    if args.procs > 1 and not args.series_major:
+        eng.set_run_log_capacity(8 * tr.n)
     eng.ingest(tr.ts, tr.gpu_gid, tr.pid, tr.util)
     spec = eng.make_spec(kinds=kinds, metric='sm', gpus_per_node=8, t0=tr.t0, step=60, n_windows=60,
                          n_gpus=tr.n_gpus, n_nodes=tr.n_nodes, qs=qs, total_samples_hint=tr.n)
