@@ -93,6 +93,15 @@ int kgs_ingest(kgs_handle h, const uint32_t* ts, const uint32_t* gpu_gid, const 
 int kgs_batch_reserve(kgs_handle h, uint64_t capacity);
 int kgs_batch_append(kgs_handle h, const uint32_t* ts, const uint32_t* gpu_gid, const uint32_t* pid,
                      const uint32_t* util, uint64_t n);
+/* Bring the resident batch into series-major collector order (by gpu_gid, then pid, each series in
+ * its input order) with a stable radix sort on the GPU; the sorted copy becomes the resident batch.
+ * The statistics are the same for any order - this is for speed: input that interleaves the series
+ * (a time-major live feed, several processes per GPU delivered second by second) makes every sample
+ * its own run.  No reference counterpart (ingestion, north_star subsystem 1).  Queued on the compute
+ * stream; needs a second copy of the batch in device memory. */
+int kgs_reorder_batch(kgs_handle h);
+/* Copy the resident batch's columns back to host arrays of n entries (any pointer may be NULL). Blocking. */
+int kgs_fetch_batch(kgs_handle h, uint32_t* ts, uint32_t* gpu_gid, uint32_t* pid, uint32_t* util);
 /* Same, for columns that already live in this device's memory, 32-byte aligned (no copy is made;
  * the caller keeps them alive and unchanged until the work that reads them has been synchronised). */
 int kgs_adopt_device_batch(kgs_handle h, const uint32_t* d_ts, const uint32_t* d_gpu_gid,
@@ -197,7 +206,7 @@ int kgs_launch_count(kgs_handle h, uint64_t* out);
  * on; kgs_kernel_time returns the accumulated device time and launch count of one kernel
  * (ids: KGS_K_*), kgs_reset_kernel_times clears them. */
 enum { KGS_K_BUILD = 0, KGS_K_BUILD_FIN = 1, KGS_K_PROBE = 2, KGS_K_ACCUM = 3, KGS_K_FINALIZE = 4,
-       KGS_K_FINALIZE_BIG = 5, KGS_K_SEGMEAN = 6, KGS_K_CLEAR = 7, KGS_K_FINALIZE_WIDE = 8, KGS_K_FINALIZE_BASIC = 9, KGS_N_KERNELS = 10 };
+       KGS_K_FINALIZE_BIG = 5, KGS_K_SEGMEAN = 6, KGS_K_CLEAR = 7, KGS_K_FINALIZE_WIDE = 8, KGS_K_FINALIZE_BASIC = 9, KGS_K_SORT = 10, KGS_N_KERNELS = 11 };
 int kgs_set_profiling(kgs_handle h, int on);
 int kgs_kernel_time(kgs_handle h, int kernel_id, double* total_ms, uint64_t* launches);
 int kgs_reset_kernel_times(kgs_handle h);

@@ -17,9 +17,9 @@ METRIC_SM, METRIC_MEM, METRIC_FB = 0, 1, 2
 POD_NONE = 0xFFFFFFFF
 MAX_Q = 8
 NOALLOC_MAX_PAIRS = 65536
-(K_BUILD, K_BUILD_FIN, K_PROBE, K_ACCUM, K_FINALIZE, K_FINALIZE_BIG, K_SEGMEAN, K_CLEAR, K_FINALIZE_WIDE, K_FINALIZE_BASIC) = range(10)
+(K_BUILD, K_BUILD_FIN, K_PROBE, K_ACCUM, K_FINALIZE, K_FINALIZE_BIG, K_SEGMEAN, K_CLEAR, K_FINALIZE_WIDE, K_FINALIZE_BASIC, K_SORT) = range(11)
 KERNEL_NAMES = ['join_build', 'join_resolve', 'join_probe', 'accum', 'finalize_cells', 'finalize_big',
-                'segmean', 'join_clear', 'finalize_wide', 'finalize_basic']
+                'segmean', 'join_clear', 'finalize_wide', 'finalize_basic', 'reorder']
 
 
 class WindowSpec(C.Structure):
@@ -55,6 +55,8 @@ def load(path=LIB_PATH):
         'kgs_ingest': [H, vp, vp, vp, vp, C.c_uint64],
         'kgs_batch_reserve': [H, C.c_uint64],
         'kgs_batch_append': [H, vp, vp, vp, vp, C.c_uint64],
+        'kgs_reorder_batch': [H],
+        'kgs_fetch_batch': [H, vp, vp, vp, vp],
         'kgs_adopt_device_batch': [H, vp, vp, vp, vp, C.c_uint64],
         'kgs_build_join': [H, vp, vp, C.c_uint64, C.c_uint32],
         'kgs_probe': [H, C.c_uint32, vp],

@@ -15,6 +15,7 @@
 #include "join.cuh"
 #include "noalloc.cuh"
 #include "segmean.cuh"
+#include "sort.cuh"
 
 using namespace kgs;
 
@@ -74,6 +75,7 @@ struct kgs_ctx {
     uint32_t W = 1, n_panes = 0;
     KindState kind[3];
     DevBuf arena, vals, desc, tmp, tmp2, tmp3, tmp4;
+    DevBuf sortbuf[4];
     size_t clear_bytes = 0;
     uint32_t* ctl = nullptr;       // [0] run cursor [1] run-log overflow [2] big-list length [3] spare
     uint32_t* big_list = nullptr;
@@ -272,6 +274,8 @@ int kgs_destroy(kgs_handle h) {
                       &h->tmp, &h->tmp2, &h->tmp3, &h->tmp4};
     for (DevBuf* b : bufs)
         if (b->p) cudaFree(b->p);
+    for (DevBuf& b : h->sortbuf)
+        if (b.p) cudaFree(b.p);
     cudaStreamDestroy(h->copy);
     cudaStreamDestroy(h->compute);
     delete h;
@@ -365,6 +369,86 @@ int kgs_batch_append(kgs_handle h, const uint32_t* ts, const uint32_t* gpu_gid, 
         if (n) KGS_CUDA(h, cudaMemcpyAsync(static_cast<uint32_t*>(B.col[c].p) + B.n, src[c], n * 4, cudaMemcpyHostToDevice, h->copy));
     B.n += n;
     KGS_CUDA(h, cudaEventRecord(B.ready, h->copy));
+    return KGS_OK;
+}
+
+int kgs_reorder_batch(kgs_handle h) {
+    if (!h) return KGS_ERR_ARG;
+    if (h->cur < 0) return fail(h, KGS_ERR_STATE, "kgs_reorder_batch: no resident batch");
+    KGS_CUDA(h, cudaSetDevice(h->device));
+    Batch& src = h->batch[h->cur];
+    const uint64_t n = src.n;
+    if (n < 2) return KGS_OK;
+    cudaStream_t st = h->compute;
+    KGS_CUDA(h, cudaStreamWaitEvent(st, src.ready, 0));
+    // how many key bits does this batch use?
+    int rc;
+    KGS_CUDA(h, cudaStreamSynchronize(st));   // tmp buffers may be reallocated
+    if ((rc = reserve(h, h->tmp, 64))) return rc;
+    KGS_CUDA(h, cudaMemsetAsync(h->tmp.p, 0, 8, st));
+    launch(h, KGS_K_SORT, st, [&] {
+        k_sort_maxima<<<grid_for(n, 256 * 16, 148 * 8), 256, 0, st>>>(src.ptr[1], src.ptr[2], (uint32_t)n, static_cast<uint32_t*>(h->tmp.p));
+    });
+    uint32_t mx[2] = {0, 0};
+    KGS_CUDA(h, cudaMemcpyAsync(mx, h->tmp.p, 8, cudaMemcpyDeviceToHost, st));
+    KGS_CUDA(h, cudaStreamSynchronize(st));
+    auto bits = [](uint32_t v) { uint32_t b = 1; while (b < 32 && (v >> b)) ++b; return b; };
+    const uint32_t pid_bits = bits(mx[1]), total_bits = bits(mx[0]) + pid_bits;
+    const uint32_t passes = (total_bits + 7) / 8;
+    // ping-pong between the other batch slot and a scratch set so that the last pass lands in the slot
+    Batch& dst = h->batch[(h->cur + 1) & 1];
+    KGS_CUDA(h, cudaStreamSynchronize(h->copy));
+    uint32_t* slot_cols[4];
+    uint32_t* scratch_cols[4];
+    for (int c = 0; c < 4; ++c) {
+        if ((rc = reserve(h, dst.col[c], n * 4 + 64))) return rc;
+        slot_cols[c] = static_cast<uint32_t*>(dst.col[c].p);
+        if (passes > 1 && (rc = reserve(h, h->sortbuf[c], n * 4 + 64))) return rc;
+        scratch_cols[c] = static_cast<uint32_t*>(h->sortbuf[c].p);
+    }
+    SortParams P{};
+    P.n = (uint32_t)n;
+    P.n_ctas = (uint32_t)((n + kSortBlock - 1) / kSortBlock);
+    P.pid_bits = pid_bits;
+    const uint32_t m = 256 * P.n_ctas, n_part = (m + kScanBlock - 1) / kScanBlock;
+    if ((rc = reserve(h, h->tmp2, (size_t)m * 4))) return rc;
+    if ((rc = reserve(h, h->tmp3, (size_t)n_part * 4 + 4))) return rc;
+    P.counts = static_cast<uint32_t*>(h->tmp2.p);
+    uint32_t* partial = static_cast<uint32_t*>(h->tmp3.p);
+    const uint32_t* cur_in[4] = {src.ptr[0], src.ptr[1], src.ptr[2], src.ptr[3]};
+    for (uint32_t pass = 0; pass < passes; ++pass) {
+        const bool to_slot = ((passes - 1 - pass) & 1u) == 0;   // the last pass writes the slot
+        for (int c = 0; c < 4; ++c) {
+            P.in[c] = cur_in[c];
+            P.out[c] = to_slot ? slot_cols[c] : scratch_cols[c];
+        }
+        P.shift = 8 * pass;
+        launch(h, KGS_K_SORT, st, [&] { k_sort_hist<<<P.n_ctas, kSortThreads, 0, st>>>(P); });
+        launch(h, KGS_K_SORT, st, [&] { k_scan_reduce<<<n_part, 256, 0, st>>>(P.counts, m, partial); });
+        launch(h, KGS_K_SORT, st, [&] { k_scan_top<<<1, 1024, 0, st>>>(partial, n_part); });
+        launch(h, KGS_K_SORT, st, [&] { k_scan_apply<<<n_part, 256, 0, st>>>(P.counts, m, partial); });
+        launch(h, KGS_K_SORT, st, [&] { k_sort_scatter<<<P.n_ctas, kSortThreads, 0, st>>>(P); });
+        for (int c = 0; c < 4; ++c) cur_in[c] = P.out[c];
+    }
+    KGS_CUDA(h, cudaGetLastError());
+    KGS_CUDA(h, cudaEventRecord(src.consumed, st));
+    for (int c = 0; c < 4; ++c) dst.ptr[c] = slot_cols[c];
+    dst.n = n;
+    KGS_CUDA(h, cudaEventRecord(dst.ready, st));
+    h->cur = (h->cur + 1) & 1;
+    return KGS_OK;
+}
+
+int kgs_fetch_batch(kgs_handle h, uint32_t* ts, uint32_t* gpu_gid, uint32_t* pid, uint32_t* util) {
+    if (!h) return KGS_ERR_ARG;
+    if (h->cur < 0) return fail(h, KGS_ERR_STATE, "kgs_fetch_batch: no resident batch");
+    KGS_CUDA(h, cudaSetDevice(h->device));
+    Batch& B = h->batch[h->cur];
+    uint32_t* dst[4] = {ts, gpu_gid, pid, util};
+    KGS_CUDA(h, cudaStreamWaitEvent(h->compute, B.ready, 0));
+    for (int c = 0; c < 4; ++c)
+        if (dst[c] && B.n) KGS_CUDA(h, cudaMemcpyAsync(dst[c], B.ptr[c], B.n * 4, cudaMemcpyDeviceToHost, h->compute));
+    KGS_CUDA(h, cudaStreamSynchronize(h->compute));
     return KGS_OK;
 }
 

@@ -100,6 +100,17 @@ class Engine:
         self._ck(self._lib.kgs_batch_append(self._h, *[c.ctypes.data for c in cols], n))
         self.n_resident += n
 
+    def reorder(self):
+        """Sort the resident batch into (gpu, pid, input order) on the GPU (see kgs_reorder_batch)."""
+        self._ck(self._lib.kgs_reorder_batch(self._h))
+        self._keep = []
+
+    def fetch_batch(self):
+        """The resident batch's four columns back on the host (testing / inspection)."""
+        cols = [np.empty(self.n_resident, dtype=np.uint32) for _ in range(4)]
+        self._ck(self._lib.kgs_fetch_batch(self._h, *[c.ctypes.data for c in cols]))
+        return cols
+
     def adopt_device_batch(self, d_ts, d_gid, d_pid, d_util, n):
         self._ck(self._lib.kgs_adopt_device_batch(self._h, int(d_ts), int(d_gid), int(d_pid), int(d_util), int(n)))
         self.n_resident = int(n)

@@ -1,0 +1,61 @@
+"""GPU: kgs_reorder_batch - the stable radix sort that brings a batch into (gpu, pid, input order)."""
+import numpy as np
+import pytest
+
+from conftest import assert_stats_equal
+from kube_gpu_stats_b200 import synth
+from oracle import window_stats as ws
+
+pytestmark = pytest.mark.gpu
+
+
+def expected_order(gid, pid):
+    """Stable sort by (gid, pid): what 'series-major, each series in its input order' means."""
+    return np.lexsort((np.arange(len(gid)), pid, gid))
+
+
+@pytest.mark.parametrize('n', [0, 1, 2, 33, 8191, 8192, 8193, 100003])
+def test_reorder_is_a_stable_sort_by_gpu_then_pid(engine, n):
+    rng = np.random.default_rng(n)
+    gid = rng.integers(0, 300, size=n).astype(np.uint32)
+    pid = rng.integers(1, 70000, size=n).astype(np.uint32)
+    if n > 10:
+        pid[rng.integers(0, n, size=n // 2)] = 4242                 # long runs of equal keys: stability matters
+    ts = np.arange(n, dtype=np.uint32)                               # input position, so the order is visible
+    util = rng.integers(0, 1 << 32, size=n, dtype=np.uint64).astype(np.uint32)
+    engine.ingest(ts, gid, pid, util)
+    engine.reorder()
+    got = engine.fetch_batch()
+    o = expected_order(gid, pid)
+    for g, w in zip(got, (ts[o], gid[o], pid[o], util[o])):
+        np.testing.assert_array_equal(g, w)
+
+
+def test_reorder_wide_keys(engine):
+    """gpu ids and pids that need more than 32 key bits together (five passes)."""
+    rng = np.random.default_rng(7)
+    n = 50000
+    gid = rng.integers(0, 1 << 17, size=n).astype(np.uint32)
+    pid = rng.integers(0, 1 << 22, size=n).astype(np.uint32)
+    ts = np.arange(n, dtype=np.uint32)
+    engine.ingest(ts, gid, pid, ts)
+    engine.reorder()
+    got = engine.fetch_batch()
+    o = expected_order(gid, pid)
+    np.testing.assert_array_equal(got[0], ts[o])
+    np.testing.assert_array_equal(got[1], gid[o])
+
+
+def test_interleaved_processes_same_tables_after_reorder(engine):
+    """8 processes per GPU delivered second by second: reorder, then the tables must be what the
+    oracle gives for the original order (the statistics do not depend on the order)."""
+    tr = synth.cluster_trace(4, 8, 8, 1800, n_tenancies=300, pids_per_pod=2, seed=5)
+    engine.build_join(tr.keys, tr.pod_ids, tr.n_pods)
+    engine.ingest(tr.ts, tr.gpu_gid, tr.pid, tr.util)
+    engine.reorder()
+    got = engine.window_stats(kinds=('pod', 'gpu', 'node'), metric='sm', gpus_per_node=8, t0=tr.t0, step=60,
+                              n_windows=30, n_gpus=tr.n_gpus, n_nodes=tr.n_nodes, qs=(0.5, 0.95))
+    for kind, kid, nk in (('pod', ws.KEY_POD, tr.n_pods), ('gpu', ws.KEY_GPU, tr.n_gpus), ('node', ws.KEY_NODE, tr.n_nodes)):
+        want = ws.window_stats_np(tr.ts, tr.gpu_gid, tr.pid, tr.util, tr.keys, tr.pod_ids, key_kind=kid, metric=0,
+                                  gpus_per_node=8, t0=tr.t0, step=60, width=60, n_windows=30, n_keys=nk, qs=(0.5, 0.95))
+        assert_stats_equal(got[kind], want, what='reordered ' + kind)
