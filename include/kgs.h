@@ -34,7 +34,8 @@ enum {
     KGS_ERR_CUDA = 2,      /* a CUDA runtime call failed; see kgs_last_error */
     KGS_ERR_STATE = 3,     /* call out of order (e.g. accumulate before begin, probe before build_join) */
     KGS_ERR_CAPACITY = 4,  /* a fixed-capacity scratch area overflowed (run log, static scratch) */
-    KGS_ERR_NOMEM = 5
+    KGS_ERR_NOMEM = 5,
+    KGS_ERR_PARSE = 6      /* kgs_matrix_parse: the text is not a well-formed answer, or float() would raise */
 };
 
 /* key kinds of the windowed statistics (north_star: per-pod / per-GPU / per-node) */
@@ -201,12 +202,35 @@ int kgs_segmented_mean_f64(kgs_handle h, const double* values, const uint64_t* o
 
 /* ---- measurement ---------------------------------------------------------------------- */
 /* Kernel launches issued by this handle since creation (bench.py's gpu_launches). */
+/* ---- value decode of a Prometheus answer on the GPU ---------------------------------------------
+ * Replaces the reference's `requests.get(...).json()` + per-sample `float(val[1])` loops
+ * (gpu_util_stats.py:25, :47-48, :73-74) for the bulk of an answer: `text` is the response body of
+ * /query_range (KGS_RESULT_MATRIX: {"data":{"result":[{"metric":{..},"values":[[ts,"v"],..]},..]}})
+ * or /query (KGS_RESULT_VECTOR: "value":[ts,"v"]).  The kernels find every series and every
+ * [ts,"v"] pair (strings, escapes and nesting handled on the GPU) and convert both numbers to fp64
+ * exactly as Python's float() does (correctly rounded, same grammar).  The result stays in device
+ * memory as a CSR: values[offsets[s] .. offsets[s+1]) belong to series s, in text order.
+ * `text` is a host pointer (pinned memory makes the copy asynchronous and faster), nbytes < 4 GiB.
+ * Errors: KGS_ERR_PARSE if the text ends inside a string / with open brackets, or a sample is not
+ * `[number, "text"]` with text that float() accepts (kgs_last_error names the byte).  Blocking. */
+enum { KGS_RESULT_MATRIX = 0, KGS_RESULT_VECTOR = 1 };
+int kgs_matrix_parse(kgs_handle h, const char* text, uint64_t nbytes, int result_type, uint64_t* n_series,
+                     uint64_t* n_samples);
+/* Copy the decoded answer to host arrays (any pointer may be NULL): ts and values have n_samples
+ * entries, offsets n_series + 1, spans 4 per series: byte index of the series' '{', of the '[' and
+ * ']' of its values array (UINT64_MAX when it has none) and of its '}' - what the caller needs to
+ * decode the small label part (`metric`) of each series itself.  Blocking. */
+int kgs_matrix_fetch(kgs_handle h, double* ts, double* values, uint64_t* offsets, uint64_t* spans);
+/* kgs_segmented_mean_f64 over the decoded answer where it lies (no copy of the values): out has
+ * n_series entries.  mul / div as in kgs_segmented_mean_f64.  Blocking. */
+int kgs_matrix_mean(kgs_handle h, double mul, double div, double* out);
+
 int kgs_launch_count(kgs_handle h, uint64_t* out);
 /* With profiling on, every kernel launch is bracketed by CUDA events on the stream it runs
  * on; kgs_kernel_time returns the accumulated device time and launch count of one kernel
  * (ids: KGS_K_*), kgs_reset_kernel_times clears them. */
 enum { KGS_K_BUILD = 0, KGS_K_BUILD_FIN = 1, KGS_K_PROBE = 2, KGS_K_ACCUM = 3, KGS_K_FINALIZE = 4,
-       KGS_K_FINALIZE_BIG = 5, KGS_K_SEGMEAN = 6, KGS_K_CLEAR = 7, KGS_K_FINALIZE_WIDE = 8, KGS_K_FINALIZE_BASIC = 9, KGS_K_SORT = 10, KGS_N_KERNELS = 11 };
+       KGS_K_FINALIZE_BIG = 5, KGS_K_SEGMEAN = 6, KGS_K_CLEAR = 7, KGS_K_FINALIZE_WIDE = 8, KGS_K_FINALIZE_BASIC = 9, KGS_K_SORT = 10, KGS_K_PARSE = 11, KGS_N_KERNELS = 12 };
 int kgs_set_profiling(kgs_handle h, int on);
 int kgs_kernel_time(kgs_handle h, int kernel_id, double* total_ms, uint64_t* launches);
 int kgs_reset_kernel_times(kgs_handle h);

@@ -11,15 +11,16 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, 'libkgs.so')
 HEADER_PATH = os.path.join(HERE, '..', 'include', 'kgs.h')
 
-KGS_OK, KGS_ERR_ARG, KGS_ERR_CUDA, KGS_ERR_STATE, KGS_ERR_CAPACITY, KGS_ERR_NOMEM = range(6)
+KGS_OK, KGS_ERR_ARG, KGS_ERR_CUDA, KGS_ERR_STATE, KGS_ERR_CAPACITY, KGS_ERR_NOMEM, KGS_ERR_PARSE = range(7)
+RESULT_MATRIX, RESULT_VECTOR = 0, 1
 KEY_POD, KEY_GPU, KEY_NODE = 0, 1, 2
 METRIC_SM, METRIC_MEM, METRIC_FB = 0, 1, 2
 POD_NONE = 0xFFFFFFFF
 MAX_Q = 8
 NOALLOC_MAX_PAIRS = 65536
-(K_BUILD, K_BUILD_FIN, K_PROBE, K_ACCUM, K_FINALIZE, K_FINALIZE_BIG, K_SEGMEAN, K_CLEAR, K_FINALIZE_WIDE, K_FINALIZE_BASIC, K_SORT) = range(11)
+(K_BUILD, K_BUILD_FIN, K_PROBE, K_ACCUM, K_FINALIZE, K_FINALIZE_BIG, K_SEGMEAN, K_CLEAR, K_FINALIZE_WIDE, K_FINALIZE_BASIC, K_SORT, K_PARSE) = range(12)
 KERNEL_NAMES = ['join_build', 'join_resolve', 'join_probe', 'accum', 'finalize_cells', 'finalize_big',
-                'segmean', 'join_clear', 'finalize_wide', 'finalize_basic', 'reorder']
+                'segmean', 'join_clear', 'finalize_wide', 'finalize_basic', 'reorder', 'parse']
 
 
 class WindowSpec(C.Structure):
@@ -75,6 +76,9 @@ def load(path=LIB_PATH):
         'kgs_result_offset': [H, C.c_int, C.c_int, C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)],
         'kgs_fetch_region': [H, vp, C.c_size_t],
         'kgs_segmented_mean_f64': [H, vp, vp, C.c_uint64, C.c_double, C.c_double, vp],
+        'kgs_matrix_parse': [H, vp, C.c_uint64, C.c_int, u64p, u64p],
+        'kgs_matrix_fetch': [H, vp, vp, vp, vp],
+        'kgs_matrix_mean': [H, C.c_double, C.c_double, vp],
         'kgs_launch_count': [H, u64p],
         'kgs_set_profiling': [H, C.c_int],
         'kgs_kernel_time': [H, C.c_int, f64p, u64p],

@@ -16,6 +16,7 @@
 #include "noalloc.cuh"
 #include "segmean.cuh"
 #include "sort.cuh"
+#include "promjson.cuh"
 
 using namespace kgs;
 
@@ -76,6 +77,11 @@ struct kgs_ctx {
     KindState kind[3];
     DevBuf arena, vals, desc, tmp, tmp2, tmp3, tmp4;
     DevBuf sortbuf[4];
+    // decoded Prometheus answer (promjson.cuh)
+    DevBuf mx_text, mx_cta_trans, mx_cta_counts, mx_chunk_state, mx_chunk_counts, mx_pos, mx_ts, mx_val, mx_off, mx_spans,
+        mx_long, mx_out, mx_ctl;
+    uint64_t mx_n_series = 0, mx_n_samples = 0, mx_n_long = 0;
+    bool mx_valid = false;
     size_t clear_bytes = 0;
     uint32_t* ctl = nullptr;       // [0] run cursor [1] run-log overflow [2] big-list length [3] spare
     uint32_t* big_list = nullptr;
@@ -271,7 +277,9 @@ int kgs_destroy(kgs_handle h) {
         cudaEventDestroy(h->mark[b]);
     }
     DevBuf* bufs[] = {&h->slots, &h->build_keys, &h->build_pods, &h->arena, &h->vals, &h->desc,
-                      &h->tmp, &h->tmp2, &h->tmp3, &h->tmp4};
+                      &h->tmp, &h->tmp2, &h->tmp3, &h->tmp4, &h->mx_text, &h->mx_cta_trans, &h->mx_cta_counts,
+                      &h->mx_chunk_state, &h->mx_chunk_counts, &h->mx_pos, &h->mx_ts, &h->mx_val, &h->mx_off,
+                      &h->mx_spans, &h->mx_long, &h->mx_out, &h->mx_ctl};
     for (DevBuf* b : bufs)
         if (b->p) cudaFree(b->p);
     for (DevBuf& b : h->sortbuf)
@@ -1064,6 +1072,131 @@ int kgs_segmented_mean_f64(kgs_handle h, const double* values, const uint64_t* o
     }
     KGS_CUDA(h, cudaGetLastError());
     KGS_CUDA(h, cudaMemcpyAsync(out, dout, n_series * 8, cudaMemcpyDeviceToHost, st));
+    KGS_CUDA(h, cudaStreamSynchronize(st));
+    return KGS_OK;
+}
+
+int kgs_matrix_parse(kgs_handle h, const char* text, uint64_t nbytes, int result_type, uint64_t* n_series,
+                     uint64_t* n_samples) {
+    if (!h) return KGS_ERR_ARG;
+    h->mx_valid = false;
+    if (!text && nbytes) return fail(h, KGS_ERR_ARG, "kgs_matrix_parse: null text");
+    if (result_type != KGS_RESULT_MATRIX && result_type != KGS_RESULT_VECTOR)
+        return fail(h, KGS_ERR_ARG, "kgs_matrix_parse: result_type must be KGS_RESULT_MATRIX or KGS_RESULT_VECTOR");
+    if (nbytes >= (1ull << 32) - 2 * kMxTile)
+        return fail(h, KGS_ERR_ARG, "kgs_matrix_parse: an answer of 4 GiB or more has to be split by the caller");
+    KGS_CUDA(h, cudaSetDevice(h->device));
+    cudaStream_t st = h->compute;
+    KGS_CUDA(h, cudaStreamSynchronize(st));   // buffers may be reallocated
+    const uint32_t n_ctas = (uint32_t)std::max<uint64_t>(1, (nbytes + kMxTile - 1) / kMxTile);
+    const size_t padded = (size_t)n_ctas * kMxTile + kMxChunk;
+    const size_t chunks = (size_t)n_ctas * kMxThreads;
+    int rc;
+    if ((rc = reserve(h, h->mx_text, padded))) return rc;
+    if ((rc = reserve(h, h->mx_cta_trans, n_ctas * sizeof(MxTrans)))) return rc;
+    if ((rc = reserve(h, h->mx_cta_counts, n_ctas * sizeof(uint2)))) return rc;
+    if ((rc = reserve(h, h->mx_chunk_state, chunks * 4))) return rc;
+    if ((rc = reserve(h, h->mx_chunk_counts, chunks * 8))) return rc;
+    if ((rc = reserve(h, h->mx_ctl, 64))) return rc;
+    char* dtext = static_cast<char*>(h->mx_text.p);
+    unsigned long long* ctl = static_cast<unsigned long long*>(h->mx_ctl.p);
+    KGS_CUDA(h, cudaMemsetAsync(dtext + nbytes, 0, padded - nbytes, st));
+    if (nbytes) KGS_CUDA(h, cudaMemcpyAsync(dtext, text, nbytes, cudaMemcpyHostToDevice, st));
+    KGS_CUDA(h, cudaMemsetAsync(ctl, 0, 64, st));
+    KGS_CUDA(h, cudaMemsetAsync(ctl + 2, 0xFF, 8, st));
+    MxParams P{};
+    P.text = dtext;
+    P.n = nbytes;
+    P.n_ctas = n_ctas;
+    P.pair_depth = result_type == KGS_RESULT_MATRIX ? 5u : 4u;
+    P.cta_trans = static_cast<MxTrans*>(h->mx_cta_trans.p);
+    P.cta_counts = static_cast<uint2*>(h->mx_cta_counts.p);
+    P.chunk_state = static_cast<uint32_t*>(h->mx_chunk_state.p);
+    P.chunk_counts = static_cast<uint2*>(h->mx_chunk_counts.p);
+    P.ctl = ctl;
+    launch(h, KGS_K_PARSE, st, [&] { k_mx_classify<<<n_ctas, kMxThreads, 0, st>>>(P); });
+    launch(h, KGS_K_PARSE, st, [&] { k_mx_top<<<1, kMxThreads, 0, st>>>(P); });
+    launch(h, KGS_K_PARSE, st, [&] { k_mx_count<<<n_ctas, kMxThreads, 0, st>>>(P); });
+    launch(h, KGS_K_PARSE, st, [&] { k_mx_top2<<<1, kMxThreads, 0, st>>>(P); });
+    KGS_CUDA(h, cudaGetLastError());
+    unsigned long long head[8];
+    KGS_CUDA(h, cudaMemcpyAsync(head, ctl, 64, cudaMemcpyDeviceToHost, st));
+    KGS_CUDA(h, cudaStreamSynchronize(st));
+    if (head[4] != 0)
+        return fail(h, KGS_ERR_PARSE, "kgs_matrix_parse: the text ends inside a string or with unbalanced brackets");
+    const uint64_t ns = head[0], nser = head[1];
+    if (ns >= (1ull << 32) || nser >= (1ull << 31)) return fail(h, KGS_ERR_ARG, "kgs_matrix_parse: too many samples or series");
+    if ((rc = reserve(h, h->mx_pos, ns * 4 + 4))) return rc;
+    if ((rc = reserve(h, h->mx_ts, ns * 8 + 8))) return rc;
+    if ((rc = reserve(h, h->mx_val, ns * 8 + 8))) return rc;
+    if ((rc = reserve(h, h->mx_off, (nser + 1) * 8))) return rc;
+    if ((rc = reserve(h, h->mx_spans, nser * 32 + 32))) return rc;
+    if ((rc = reserve(h, h->mx_long, nser * 4 + 4))) return rc;
+    P.sample_pos = static_cast<uint32_t*>(h->mx_pos.p);
+    P.ts = static_cast<double*>(h->mx_ts.p);
+    P.val = static_cast<double*>(h->mx_val.p);
+    P.offsets = static_cast<unsigned long long*>(h->mx_off.p);
+    P.spans = static_cast<unsigned long long*>(h->mx_spans.p);
+    KGS_CUDA(h, cudaMemsetAsync(P.spans, 0xFF, nser * 32 + 32, st));
+    launch(h, KGS_K_PARSE, st, [&] { k_mx_emit<<<n_ctas, kMxThreads, 0, st>>>(P); });
+    if (ns) launch(h, KGS_K_PARSE, st, [&] { k_mx_parse<<<(unsigned)((ns + 127) / 128), 128, 0, st>>>(P); });
+    if (nser)
+        launch(h, KGS_K_PARSE, st, [&] {
+            k_mx_long_series<<<(unsigned)((nser + 255) / 256), 256, 0, st>>>(P.offsets, (uint32_t)nser, kSeqMax,
+                                                                              static_cast<uint32_t*>(h->mx_long.p), ctl);
+        });
+    KGS_CUDA(h, cudaGetLastError());
+    KGS_CUDA(h, cudaMemcpyAsync(head, ctl, 64, cudaMemcpyDeviceToHost, st));
+    KGS_CUDA(h, cudaStreamSynchronize(st));
+    if (head[2] != ~0ull)
+        return fail(h, KGS_ERR_PARSE, "kgs_matrix_parse: malformed sample (float() would raise) at byte " + std::to_string(head[2]));
+    h->mx_n_samples = ns;
+    h->mx_n_series = nser;
+    h->mx_n_long = head[3];
+    h->mx_valid = true;
+    if (n_series) *n_series = nser;
+    if (n_samples) *n_samples = ns;
+    return KGS_OK;
+}
+
+int kgs_matrix_fetch(kgs_handle h, double* ts, double* values, uint64_t* offsets, uint64_t* spans) {
+    if (!h) return KGS_ERR_ARG;
+    if (!h->mx_valid) return fail(h, KGS_ERR_STATE, "kgs_matrix_fetch: no decoded answer (kgs_matrix_parse first)");
+    KGS_CUDA(h, cudaSetDevice(h->device));
+    cudaStream_t st = h->compute;
+    const uint64_t ns = h->mx_n_samples, nser = h->mx_n_series;
+    if (ts && ns) KGS_CUDA(h, cudaMemcpyAsync(ts, h->mx_ts.p, ns * 8, cudaMemcpyDeviceToHost, st));
+    if (values && ns) KGS_CUDA(h, cudaMemcpyAsync(values, h->mx_val.p, ns * 8, cudaMemcpyDeviceToHost, st));
+    if (offsets) KGS_CUDA(h, cudaMemcpyAsync(offsets, h->mx_off.p, (nser + 1) * 8, cudaMemcpyDeviceToHost, st));
+    if (spans && nser) KGS_CUDA(h, cudaMemcpyAsync(spans, h->mx_spans.p, nser * 32, cudaMemcpyDeviceToHost, st));
+    KGS_CUDA(h, cudaStreamSynchronize(st));
+    return KGS_OK;
+}
+
+int kgs_matrix_mean(kgs_handle h, double mul, double div, double* out) {
+    if (!h) return KGS_ERR_ARG;
+    if (!h->mx_valid) return fail(h, KGS_ERR_STATE, "kgs_matrix_mean: no decoded answer (kgs_matrix_parse first)");
+    const uint64_t nser = h->mx_n_series;
+    if (nser == 0) return KGS_OK;
+    if (!out) return fail(h, KGS_ERR_ARG, "kgs_matrix_mean: null out");
+    KGS_CUDA(h, cudaSetDevice(h->device));
+    cudaStream_t st = h->compute;
+    int rc;
+    if ((rc = reserve(h, h->mx_out, nser * 8))) return rc;
+    const double* dv = static_cast<const double*>(h->mx_val.p);
+    const unsigned long long* doff = static_cast<const unsigned long long*>(h->mx_off.p);
+    double* dout = static_cast<double*>(h->mx_out.p);
+    launch(h, KGS_K_SEGMEAN, st, [&] {
+        k_segmean_short<<<(unsigned)((nser + 127) / 128), 128, 0, st>>>(dv, doff, (uint32_t)nser, mul, div, dout);
+    });
+    if (h->mx_n_long) {
+        const uint32_t nl = (uint32_t)h->mx_n_long;
+        launch(h, KGS_K_SEGMEAN, st, [&] {
+            k_segmean_long<<<(nl * 32 + 127) / 128, 128, 0, st>>>(dv, doff, static_cast<const uint32_t*>(h->mx_long.p), nl, mul, div, dout);
+        });
+    }
+    KGS_CUDA(h, cudaGetLastError());
+    KGS_CUDA(h, cudaMemcpyAsync(out, dout, nser * 8, cudaMemcpyDeviceToHost, st));
     KGS_CUDA(h, cudaStreamSynchronize(st));
     return KGS_OK;
 }

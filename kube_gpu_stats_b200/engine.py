@@ -38,6 +38,7 @@ class Engine:
         self._spec = None
         self._n_keys = {}
         self.n_resident = 0
+        self._matrix = (0, 0)
 
     # -- plumbing ---------------------------------------------------------------------
     def _ck(self, rc):
@@ -283,6 +284,45 @@ class Engine:
         if ns > 0:
             self._ck(self._lib.kgs_segmented_mean_f64(self._h, values.ctypes.data, offsets.ctypes.data, ns,
                                                       float(mul), float(div), out.ctypes.data))
+        return out
+
+    # -- value decode of a Prometheus answer (gpu_util_stats.py:25,:47-48,:73-74) ---------
+    def matrix_parse(self, text, result_type='matrix'):
+        """Decode the body of a /query_range (``matrix``) or /query (``vector``) answer on the GPU.
+        ``text``: bytes-like, or (address, nbytes) of a pinned buffer.  Returns (n_series, n_samples);
+        the CSR stays in device memory for matrix_mean / matrix_fetch.  Raises ValueError where
+        the reference's ``float()`` / ``.json()`` would."""
+        if isinstance(text, tuple):
+            addr, nbytes = text
+            keep = None
+        else:
+            keep = np.frombuffer(text, dtype=np.uint8)
+            addr, nbytes = keep.ctypes.data if len(keep) else 0, len(keep)
+        kind = {'matrix': _ffi.RESULT_MATRIX, 'vector': _ffi.RESULT_VECTOR}[result_type]
+        ns, nv = C.c_uint64(), C.c_uint64()
+        self._matrix = (0, 0)
+        rc = self._lib.kgs_matrix_parse(self._h, addr, nbytes, kind, C.byref(ns), C.byref(nv))
+        if rc == _ffi.KGS_ERR_PARSE:
+            raise ValueError(self._lib.kgs_last_error(self._h).decode())
+        self._ck(rc)
+        self._matrix = (ns.value, nv.value)
+        return self._matrix
+
+    def matrix_fetch(self, ts=True, values=True, spans=True):
+        """(ts, values, offsets, spans) of the decoded answer as numpy arrays (None where not asked)."""
+        n_series, n_samples = self._matrix
+        a_ts = np.empty(n_samples, dtype=np.float64) if ts else None
+        a_val = np.empty(n_samples, dtype=np.float64) if values else None
+        a_off = np.empty(n_series + 1, dtype=np.uint64)
+        a_sp = np.empty((n_series, 4), dtype=np.uint64) if spans else None
+        ptr = lambda a: a.ctypes.data if a is not None and a.size else None
+        self._ck(self._lib.kgs_matrix_fetch(self._h, ptr(a_ts), ptr(a_val), a_off.ctypes.data, ptr(a_sp)))
+        return a_ts, a_val, a_off, a_sp
+
+    def matrix_mean(self, mul=0.0, div=0.0):
+        """Per-series statistic of the reference over the decoded answer (see segmented_mean)."""
+        out = np.empty(self._matrix[0], dtype=np.float64)
+        self._ck(self._lib.kgs_matrix_mean(self._h, float(mul), float(div), out.ctypes.data if len(out) else None))
         return out
 
     # -- measurement --------------------------------------------------------------------

@@ -4,7 +4,11 @@ Same module globals, function names, arguments, return shapes and stdout as the 
 (cited as GUS:line).  What changed underneath:
 
 * the per-sample ``float()`` + ``sum()/len()`` loops (GUS:43-52, GUS:68-80) run on the GPU:
-  series values are decoded once into an fp64 CSR and reduced by ``kgs_segmented_mean_f64``;
+  ``query_prom`` hands the BYTES of the answer to ``kgs_matrix_parse`` (every ``[ts, "v"]`` pair
+  found and converted to fp64 on the GPU, bit-identical to ``float()``) and returns a
+  ``MatrixAnswer``: a dict with the same shape as ``.json()`` whose sample values live in device
+  memory; ``stats_*`` reduce them there (``kgs_matrix_mean``).  A plain dict (a caller's own
+  decoded JSON) still works: its values go through ``series_to_csr`` + ``kgs_segmented_mean_f64``;
 * the (server, pod) join (GUS:82-92) goes through libkgs' open-addressing hash table
   (``kgs_build_join`` / ``kgs_probe``) with dictionary-encoded server and pod ids - last
   series of a key wins, exactly like the reference's dict assignment (GUS:78);
@@ -54,6 +58,18 @@ def _http_get(url, params, timeout, use_proxies):
     return requests.get(url, params=params, timeout=timeout, proxies=use_proxies).json()
 
 
+def _http_get_raw(url, params, timeout, use_proxies):
+    """Body of the answer as bytes (or whatever a custom transport returns)."""
+    if _transport is not None:
+        return _transport(url, params, timeout, use_proxies)
+    replay = os.environ.get('KGS_REPLAY_DIR')
+    if replay:
+        with open(os.path.join(replay, replay_name(url, params)), 'rb') as f:
+            return f.read()
+    import requests
+    return requests.get(url, params=params, timeout=timeout, proxies=use_proxies).content
+
+
 def engine():
     global _engine
     if _engine is None:
@@ -70,12 +86,89 @@ def query_prom(query, start_time, end_time, step_sec):
         'end': int(mktime(end_time.timetuple())),
         'step': step_sec,
     }
-    return _http_get(prom_base_url + '/query_range', payload, 5, proxies)
+    body = _http_get_raw(prom_base_url + '/query_range', payload, 5, proxies)
+    if isinstance(body, (bytes, bytearray, memoryview)):
+        return MatrixAnswer(body)
+    return body
 
 
 def query_prom_instant(query):
     """GUS:29-34 (no proxies, unlike query_prom)."""
     return _http_get(prom_base_url + '/query', {'query': query}, 5, None)
+
+
+class _Series(dict):
+    """One entry of ``data.result``: ``metric`` decoded on the host; ``['values']`` is produced on
+    demand from the answer's text (the bulk of it is only ever read by the GPU)."""
+
+    def __init__(self, fields, owner, index):
+        super().__init__(fields)
+        self._owner, self._index = owner, index
+
+    def __missing__(self, key):
+        if key != 'values':
+            raise KeyError(key)
+        return self._owner.values_of(self._index)
+
+
+class MatrixAnswer(dict):
+    """A /query_range answer decoded by ``kgs_matrix_parse`` (GUS:25 ``.json()`` + GUS:47-48,
+    GUS:73-74 ``float(val[1])``).  Looks like the reference's decoded JSON; the per-sample numbers
+    stay on the GPU as a CSR in series order."""
+    _generation = 0
+
+    def __init__(self, body):
+        self.raw = bytes(body)
+        self._parse()
+        _, _, _, spans = engine().matrix_fetch(ts=False, values=False)
+        self.spans = spans
+        none = np.uint64(0xFFFFFFFFFFFFFFFF)
+        pieces, at = [], 0
+        for so, vo, vc, sc in spans.tolist():          # cut the inside of every values array out
+            if vo != none and vc != none:
+                pieces.append(self.raw[at:vo + 1])
+                at = vc
+        pieces.append(self.raw[at:])
+        super().__init__(json.loads(b''.join(pieces)))
+        result = self.get('data', {}).get('result', []) if isinstance(self.get('data'), dict) else []
+        if len(result) != len(spans):
+            raise ValueError('answer is not a Prometheus matrix: %d series objects, %d entries in data.result'
+                             % (len(spans), len(result)))
+        for i, fields in enumerate(result):
+            had = 'values' in fields
+            fields.pop('values', None)
+            result[i] = _Series(fields, self, i) if had else fields
+
+    def _parse(self):
+        self.n_series, self.n_samples = engine().matrix_parse(self.raw, 'matrix')
+        MatrixAnswer._generation += 1
+        self._mine = MatrixAnswer._generation
+
+    def _resident(self):
+        if self._mine != MatrixAnswer._generation:     # another answer was decoded since
+            self._parse()
+        return engine()
+
+    def values_of(self, index):
+        so, vo, vc, sc = (int(x) for x in self.spans[index])
+        return json.loads(self.raw[vo:vc + 1])
+
+    def series_means(self, mul=0.0, div=0.0):
+        return self._resident().matrix_mean(mul, div)
+
+    def series_lengths(self):
+        _, _, offsets, _ = self._resident().matrix_fetch(ts=False, values=False, spans=False)
+        return np.diff(offsets.astype(np.int64))
+
+
+def _series_stat(json_result, results, mul=0.0, div=0.0):
+    """(statistic per series, samples per series) - on the decoded answer where it lies, else via
+    the host-side decode of a caller-supplied dict."""
+    if isinstance(json_result, MatrixAnswer):
+        return json_result.series_means(mul, div), json_result.series_lengths()
+    values, offsets = series_to_csr(results)
+    stat = engine().segmented_mean(values, offsets, mul=mul, div=div) if results else np.zeros(0)
+    return stat, np.diff(offsets.astype(np.int64))
 
 
 def series_to_csr(results):
@@ -100,18 +193,19 @@ def _encode(names, table):
 def stats_server_results(json_result, time_range_sec, step_sec):
     """GUS:36-60.  Keyed by hostname only: the LAST series of a server replaces earlier ones
     (GUS:49); value = sum * step_sec / time_range_sec (GUS:51); one row per inventory server."""
+    stat = _series_stat(json_result, json_result['data']['result'], mul=step_sec, div=time_range_sec) \
+        if isinstance(json_result, MatrixAnswer) else None
     server_cards = get_gpu_servers()
     results = json_result['data']['result']
     last = {}
     for i, res in enumerate(results):
         last[res['metric']['kubernetes_io_hostname']] = i
-    values, offsets = series_to_csr(results)
-    val = engine().segmented_mean(values, offsets, mul=step_sec, div=time_range_sec) if results else []
+    val, lens = stat if stat is not None else _series_stat(json_result, results, mul=step_sec, div=time_range_sec)
     lines = []
     for server in sorted(server_cards.keys()):
         total, used, card = server_cards[server]
         v = float(val[last[server]]) if server in last else 0
-        if server in last and offsets[last[server] + 1] == offsets[last[server]]:
+        if server in last and lens[last[server]] == 0:
             v = 0                                  # Py2: sum([]) * step / range is the int 0
         lines.append([server, card, v, used, total])
     return lines
@@ -119,13 +213,15 @@ def stats_server_results(json_result, time_range_sec, step_sec):
 
 def stats_pod_results(json_result, start_time, end_time):
     """GUS:62-94.  Returns ``[[server, pod, card_num, util], ...]``."""
+    # GUS:68-80: mean per series on the GPU.  A MatrixAnswer is reduced before the two inventory
+    # queries below decode their own (small) answers over it in device memory.
+    means = json_result.series_means() if isinstance(json_result, MatrixAnswer) else None
     server_cards = get_gpu_servers()
     server_pods = get_pod_by_servers(start_time, end_time)
     results = json_result['data']['result']
     eng = engine()
-    # GUS:68-80: mean per series on the GPU
-    values, offsets = series_to_csr(results)
-    means = eng.segmented_mean(values, offsets)
+    if means is None:
+        means, _ = _series_stat(json_result, results)
     # GUS:78 keeps the last series of a (server, pod): build the join table series-key -> index
     sid, pid = {}, {}
     s_ids = _encode([r['metric']['kubernetes_io_hostname'] for r in results], sid)
