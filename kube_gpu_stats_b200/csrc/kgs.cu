@@ -81,6 +81,8 @@ struct kgs_ctx {
     DevBuf mx_text, mx_cta_trans, mx_cta_counts, mx_chunk_state, mx_chunk_counts, mx_pos, mx_ts, mx_val, mx_off, mx_spans,
         mx_long, mx_out, mx_ctl;
     uint64_t mx_n_series = 0, mx_n_samples = 0, mx_n_long = 0;
+    std::vector<cudaEvent_t> mx_arrived;   // one event per piece of text on the copy stream
+    uint32_t mx_piece_bytes = 32u << 20;
     bool mx_valid = false;
     size_t clear_bytes = 0;
     uint32_t* ctl = nullptr;       // [0] run cursor [1] run-log overflow [2] big-list length [3] spare
@@ -245,6 +247,7 @@ int kgs_create(int device, kgs_handle* out) {
     if (const char* e = getenv("KGS_SLIDE_CHUNK")) { const int v = atoi(e); if (v >= 1 && v <= 4096) h->slide_chunk = (uint32_t)v; }
     if (const char* e = getenv("KGS_ACCUM_WAVES")) { const int v = atoi(e); if (v >= 1 && v <= 16) h->accum_waves = v; }
     if (const char* e = getenv("KGS_DENSE")) h->dense_path = atoi(e) != 0;
+    if (const char* e = getenv("KGS_PARSE_PIECE_KB")) { const int v = atoi(e); if (v >= 16 && v <= (1 << 21)) h->mx_piece_bytes = (uint32_t)v << 10; }
     if (const char* e = getenv("KGS_ACCUM_TMA")) h->accum_tma = atoi(e) != 0;
     if (h->accum_tma) {
         h->accum_ctas_per_sm = 2;   // 64 KB of tile buffers + 42 KB static per CTA
@@ -284,6 +287,7 @@ int kgs_destroy(kgs_handle h) {
         if (b->p) cudaFree(b->p);
     for (DevBuf& b : h->sortbuf)
         if (b.p) cudaFree(b.p);
+    for (auto e : h->mx_arrived) cudaEventDestroy(e);
     cudaStreamDestroy(h->copy);
     cudaStreamDestroy(h->compute);
     delete h;
@@ -1088,9 +1092,13 @@ int kgs_matrix_parse(kgs_handle h, const char* text, uint64_t nbytes, int result
     KGS_CUDA(h, cudaSetDevice(h->device));
     cudaStream_t st = h->compute;
     KGS_CUDA(h, cudaStreamSynchronize(st));   // buffers may be reallocated
+    KGS_CUDA(h, cudaStreamSynchronize(h->copy));
     const uint32_t n_ctas = (uint32_t)std::max<uint64_t>(1, (nbytes + kMxTile - 1) / kMxTile);
     const size_t padded = (size_t)n_ctas * kMxTile + kMxChunk;
     const size_t chunks = (size_t)n_ctas * kMxThreads;
+    // The text arrives in pieces on the copy stream; a piece is decoded while the next ones are in flight.
+    const uint32_t piece_ctas = std::max<uint32_t>(1, h->mx_piece_bytes / kMxTile);
+    const uint32_t n_pieces = (n_ctas + piece_ctas - 1) / piece_ctas;
     int rc;
     if ((rc = reserve(h, h->mx_text, padded))) return rc;
     if ((rc = reserve(h, h->mx_cta_trans, n_ctas * sizeof(MxTrans)))) return rc;
@@ -1098,10 +1106,13 @@ int kgs_matrix_parse(kgs_handle h, const char* text, uint64_t nbytes, int result
     if ((rc = reserve(h, h->mx_chunk_state, chunks * 4))) return rc;
     if ((rc = reserve(h, h->mx_chunk_counts, chunks * 8))) return rc;
     if ((rc = reserve(h, h->mx_ctl, 64))) return rc;
+    while (h->mx_arrived.size() < n_pieces) {
+        cudaEvent_t e = nullptr;
+        KGS_CUDA(h, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        h->mx_arrived.push_back(e);
+    }
     char* dtext = static_cast<char*>(h->mx_text.p);
     unsigned long long* ctl = static_cast<unsigned long long*>(h->mx_ctl.p);
-    KGS_CUDA(h, cudaMemsetAsync(dtext + nbytes, 0, padded - nbytes, st));
-    if (nbytes) KGS_CUDA(h, cudaMemcpyAsync(dtext, text, nbytes, cudaMemcpyHostToDevice, st));
     KGS_CUDA(h, cudaMemsetAsync(ctl, 0, 64, st));
     KGS_CUDA(h, cudaMemsetAsync(ctl + 2, 0xFF, 8, st));
     MxParams P{};
@@ -1109,53 +1120,99 @@ int kgs_matrix_parse(kgs_handle h, const char* text, uint64_t nbytes, int result
     P.n = nbytes;
     P.n_ctas = n_ctas;
     P.pair_depth = result_type == KGS_RESULT_MATRIX ? 5u : 4u;
+    P.carry = reinterpret_cast<MxTrans*>(ctl + 6);
     P.cta_trans = static_cast<MxTrans*>(h->mx_cta_trans.p);
     P.cta_counts = static_cast<uint2*>(h->mx_cta_counts.p);
     P.chunk_state = static_cast<uint32_t*>(h->mx_chunk_state.p);
     P.chunk_counts = static_cast<uint2*>(h->mx_chunk_counts.p);
     P.ctl = ctl;
-    launch(h, KGS_K_PARSE, st, [&] { k_mx_classify<<<n_ctas, kMxThreads, 0, st>>>(P); });
-    launch(h, KGS_K_PARSE, st, [&] { k_mx_top<<<1, kMxThreads, 0, st>>>(P); });
-    launch(h, KGS_K_PARSE, st, [&] { k_mx_count<<<n_ctas, kMxThreads, 0, st>>>(P); });
-    launch(h, KGS_K_PARSE, st, [&] { k_mx_top2<<<1, kMxThreads, 0, st>>>(P); });
-    KGS_CUDA(h, cudaGetLastError());
+    auto send_piece = [&](uint32_t i) -> int {
+        const size_t off = (size_t)i * piece_ctas * kMxTile;
+        const size_t len = off < nbytes ? std::min<size_t>(nbytes - off, (size_t)piece_ctas * kMxTile) : 0;
+        if (len) KGS_CUDA(h, cudaMemcpyAsync(dtext + off, text + off, len, cudaMemcpyHostToDevice, h->copy));
+        if (i + 1 == n_pieces) KGS_CUDA(h, cudaMemsetAsync(dtext + nbytes, 0, padded - nbytes, h->copy));
+        KGS_CUDA(h, cudaEventRecord(h->mx_arrived[i], h->copy));
+        return KGS_OK;
+    };
+    // grow-keeping-contents; `fill` bytes are written behind the kept part (the span table starts as all ones)
+    auto ensure = [&](DevBuf& b, size_t need, size_t keep, size_t want, int fill, bool first) -> int {
+        const size_t before = b.cap;
+        if (need > b.cap) {
+            int r = grow_copy(h, b, std::max(need, want), keep);
+            if (r) return r;
+        }
+        if (fill >= 0 && (first || b.cap != before))
+            KGS_CUDA(h, cudaMemsetAsync(static_cast<char*>(b.p) + keep, fill, b.cap - keep, st));
+        return KGS_OK;
+    };
     unsigned long long head[8];
-    KGS_CUDA(h, cudaMemcpyAsync(head, ctl, 64, cudaMemcpyDeviceToHost, st));
-    KGS_CUDA(h, cudaStreamSynchronize(st));
-    if (head[4] != 0)
-        return fail(h, KGS_ERR_PARSE, "kgs_matrix_parse: the text ends inside a string or with unbalanced brackets");
-    const uint64_t ns = head[0], nser = head[1];
-    if (ns >= (1ull << 32) || nser >= (1ull << 31)) return fail(h, KGS_ERR_ARG, "kgs_matrix_parse: too many samples or series");
-    if ((rc = reserve(h, h->mx_pos, ns * 4 + 4))) return rc;
-    if ((rc = reserve(h, h->mx_ts, ns * 8 + 8))) return rc;
-    if ((rc = reserve(h, h->mx_val, ns * 8 + 8))) return rc;
-    if ((rc = reserve(h, h->mx_off, (nser + 1) * 8))) return rc;
-    if ((rc = reserve(h, h->mx_spans, nser * 32 + 32))) return rc;
-    if ((rc = reserve(h, h->mx_long, nser * 4 + 4))) return rc;
-    P.sample_pos = static_cast<uint32_t*>(h->mx_pos.p);
-    P.ts = static_cast<double*>(h->mx_ts.p);
-    P.val = static_cast<double*>(h->mx_val.p);
-    P.offsets = static_cast<unsigned long long*>(h->mx_off.p);
-    P.spans = static_cast<unsigned long long*>(h->mx_spans.p);
-    KGS_CUDA(h, cudaMemsetAsync(P.spans, 0xFF, nser * 32 + 32, st));
-    launch(h, KGS_K_PARSE, st, [&] { k_mx_emit<<<n_ctas, kMxThreads, 0, st>>>(P); });
-    if (ns) launch(h, KGS_K_PARSE, st, [&] { k_mx_parse<<<(unsigned)((ns + 127) / 128), 128, 0, st>>>(P); });
-    if (nser)
+    uint64_t k_done = 0, s_done = 0;
+    uint32_t sent = 0;
+    for (uint32_t i = 0; i < n_pieces; ++i) {
+        while (sent < n_pieces && sent <= i + 2)
+            if ((rc = send_piece(sent++))) return rc;
+        KGS_CUDA(h, cudaStreamWaitEvent(st, h->mx_arrived[i], 0));
+        P.cta_first = i * piece_ctas;
+        P.cta_count = std::min(piece_ctas, n_ctas - P.cta_first);
+        P.last_piece = i + 1 == n_pieces;
+        const unsigned grid = P.cta_count;
+        launch(h, KGS_K_PARSE, st, [&] { k_mx_classify<<<grid, kMxThreads, 0, st>>>(P); });
+        launch(h, KGS_K_PARSE, st, [&] { k_mx_top<<<1, kMxThreads, 0, st>>>(P); });
+        launch(h, KGS_K_PARSE, st, [&] { k_mx_count<<<grid, kMxThreads, 0, st>>>(P); });
+        launch(h, KGS_K_PARSE, st, [&] { k_mx_top2<<<1, kMxThreads, 0, st>>>(P); });
+        KGS_CUDA(h, cudaGetLastError());
+        KGS_CUDA(h, cudaMemcpyAsync(head, ctl, 64, cudaMemcpyDeviceToHost, st));
+        KGS_CUDA(h, cudaStreamSynchronize(st));
+        const uint64_t ns = head[0], nser = head[1];
+        if (P.last_piece && head[4] != 0) {
+            cudaStreamSynchronize(h->copy);
+            return fail(h, KGS_ERR_PARSE, "kgs_matrix_parse: the text ends inside a string or with unbalanced brackets");
+        }
+        if (ns >= (1ull << 32) || nser >= (1ull << 31)) {
+            cudaStreamSynchronize(h->copy);
+            return fail(h, KGS_ERR_ARG, "kgs_matrix_parse: too many samples or series");
+        }
+        // sizes of the whole answer, projected from the text seen so far
+        const double seen = (double)std::min<uint64_t>(nbytes, (uint64_t)(P.cta_first + P.cta_count) * kMxTile);
+        const double scale = P.last_piece || seen <= 0 ? 1.0 : 1.1 * (double)nbytes / seen;
+        const size_t want_k = (size_t)((double)ns * scale) + 4096, want_s = (size_t)((double)nser * scale) + 256;
+        const bool first = i == 0;
+        if ((rc = ensure(h->mx_pos, ns * 4 + 4, k_done * 4, want_k * 4, -1, first))) return rc;
+        if ((rc = ensure(h->mx_ts, ns * 8 + 8, k_done * 8, want_k * 8, -1, first))) return rc;
+        if ((rc = ensure(h->mx_val, ns * 8 + 8, k_done * 8, want_k * 8, -1, first))) return rc;
+        if ((rc = ensure(h->mx_off, (nser + 1) * 8, s_done * 8, (want_s + 1) * 8, -1, first))) return rc;
+        if ((rc = ensure(h->mx_spans, nser * 32 + 32, s_done * 32, want_s * 32, 0xFF, first))) return rc;
+        P.sample_pos = static_cast<uint32_t*>(h->mx_pos.p);
+        P.ts = static_cast<double*>(h->mx_ts.p);
+        P.val = static_cast<double*>(h->mx_val.p);
+        P.offsets = static_cast<unsigned long long*>(h->mx_off.p);
+        P.spans = static_cast<unsigned long long*>(h->mx_spans.p);
+        P.k_first = (uint32_t)k_done;
+        P.k_end = (uint32_t)ns;
+        launch(h, KGS_K_PARSE, st, [&] { k_mx_emit<<<grid, kMxThreads, 0, st>>>(P); });
+        if (ns > k_done)
+            launch(h, KGS_K_PARSE, st, [&] { k_mx_parse<<<(unsigned)((ns - k_done + 127) / 128), 128, 0, st>>>(P); });
+        KGS_CUDA(h, cudaGetLastError());
+        k_done = ns;
+        s_done = nser;
+    }
+    if ((rc = reserve(h, h->mx_long, s_done * 4 + 4))) return rc;
+    if (s_done)
         launch(h, KGS_K_PARSE, st, [&] {
-            k_mx_long_series<<<(unsigned)((nser + 255) / 256), 256, 0, st>>>(P.offsets, (uint32_t)nser, kSeqMax,
-                                                                              static_cast<uint32_t*>(h->mx_long.p), ctl);
+            k_mx_long_series<<<(unsigned)((s_done + 255) / 256), 256, 0, st>>>(P.offsets, (uint32_t)s_done, kSeqMax,
+                                                                                static_cast<uint32_t*>(h->mx_long.p), ctl);
         });
     KGS_CUDA(h, cudaGetLastError());
     KGS_CUDA(h, cudaMemcpyAsync(head, ctl, 64, cudaMemcpyDeviceToHost, st));
     KGS_CUDA(h, cudaStreamSynchronize(st));
     if (head[2] != ~0ull)
         return fail(h, KGS_ERR_PARSE, "kgs_matrix_parse: malformed sample (float() would raise) at byte " + std::to_string(head[2]));
-    h->mx_n_samples = ns;
-    h->mx_n_series = nser;
+    h->mx_n_samples = k_done;
+    h->mx_n_series = s_done;
     h->mx_n_long = head[3];
     h->mx_valid = true;
-    if (n_series) *n_series = nser;
-    if (n_samples) *n_samples = ns;
+    if (n_series) *n_series = s_done;
+    if (n_samples) *n_samples = k_done;
     return KGS_OK;
 }
 

@@ -78,7 +78,11 @@ struct MxParams {
     const char* text;          // padded with zero bytes to a whole number of tiles plus one chunk
     unsigned long long n;      // bytes of text
     uint32_t n_ctas;
+    uint32_t cta_first, cta_count;   // the piece of the text this launch works on (pieces arrive one by one)
+    uint32_t last_piece;
+    uint32_t k_first, k_end;   // samples of the piece (k_mx_parse)
     uint32_t pair_depth;       // 5: matrix, 4: vector
+    MxTrans* carry;            // transition of all text before the piece
     MxTrans* cta_trans;        // [n_ctas]
     uint2* cta_counts;         // [n_ctas] (samples, series)
     uint32_t* chunk_state;     // [chunks] depth << 1 | in_string at the chunk's first byte
@@ -148,30 +152,39 @@ __device__ __forceinline__ MxTrans mx_chunk_trans(const uint4 (&t)[4], bool esc)
 
 __global__ void __launch_bounds__(kMxThreads) k_mx_classify(const __grid_constant__ MxParams P) {
     __shared__ MxTrans warp_tot[kMxThreads / 32];
-    const unsigned long long base = ((unsigned long long)blockIdx.x * kMxThreads + threadIdx.x) * kMxChunk;
+    const uint32_t cta = P.cta_first + blockIdx.x;
+    const unsigned long long base = ((unsigned long long)cta * kMxThreads + threadIdx.x) * kMxChunk;
     uint4 t[4];
     mx_load(P, base, t);
     const MxTrans mine = mx_chunk_trans(t, mx_escaped_at(P.text, base));
     MxTrans total;
     mx_block_scan(mine, warp_tot, total);
-    if (threadIdx.x == 0) P.cta_trans[blockIdx.x] = total;
+    if (threadIdx.x == 0) P.cta_trans[cta] = total;
 }
 
-// Exclusive scan of the CTA transitions, one CTA; records the state at the end of the text.
+// Exclusive scan of the piece's CTA transitions behind the carry of the text before it, one CTA;
+// records the state at the end of the text seen so far.
 __global__ void __launch_bounds__(kMxThreads) k_mx_top(const __grid_constant__ MxParams P) {
     __shared__ MxTrans warp_tot[kMxThreads / 32];
-    const uint32_t per = (P.n_ctas + kMxThreads - 1) / kMxThreads;
-    const uint32_t a = min(P.n_ctas, threadIdx.x * per), b = min(P.n_ctas, a + per);
+    const uint32_t end = P.cta_first + P.cta_count;
+    const uint32_t per = (P.cta_count + kMxThreads - 1) / kMxThreads;
+    const uint32_t a = min(end, P.cta_first + threadIdx.x * per), b = min(end, a + per);
     MxTrans seg{0, 0, 0};
     for (uint32_t i = a; i < b; ++i) seg = mx_then(seg, P.cta_trans[i]);
+    const MxTrans carry = *P.carry;
     MxTrans total;
-    MxTrans run = mx_block_scan(seg, warp_tot, total);
+    MxTrans run = mx_then(carry, mx_block_scan(seg, warp_tot, total));
     for (uint32_t i = a; i < b; ++i) {
         const MxTrans x = P.cta_trans[i];
         P.cta_trans[i] = run;
         run = mx_then(run, x);
     }
-    if (threadIdx.x == 0) P.ctl[4] = ((unsigned long long)(uint32_t)total.d0 << 1) | total.flip;   // 0 for balanced text
+    __syncthreads();   // every thread has read the carry
+    if (threadIdx.x == 0) {
+        total = mx_then(carry, total);
+        *P.carry = total;
+        P.ctl[4] = ((unsigned long long)(uint32_t)total.d0 << 1) | total.flip;   // 0 for balanced text
+    }
 }
 
 struct MxCursor {   // lexical state while walking a chunk
@@ -208,13 +221,14 @@ __device__ __forceinline__ void mx_events(const uint4 (&t)[4], bool esc, MxCurso
 __global__ void __launch_bounds__(kMxThreads) k_mx_count(const __grid_constant__ MxParams P) {
     __shared__ MxTrans warp_tot[kMxThreads / 32];
     __shared__ uint32_t wsum[2][kMxThreads / 32];
-    const uint32_t chunk = blockIdx.x * kMxThreads + threadIdx.x;
+    const uint32_t cta = P.cta_first + blockIdx.x;
+    const uint32_t chunk = cta * kMxThreads + threadIdx.x;
     const unsigned long long base = (unsigned long long)chunk * kMxChunk;
     uint4 t[4];
     mx_load(P, base, t);
     const bool esc = mx_escaped_at(P.text, base);
     MxTrans total;
-    const MxTrans before = mx_then(P.cta_trans[blockIdx.x], mx_block_scan(mx_chunk_trans(t, esc), warp_tot, total));
+    const MxTrans before = mx_then(P.cta_trans[cta], mx_block_scan(mx_chunk_trans(t, esc), warp_tot, total));
     const MxCursor cur{before.flip, before.d0};          // the text starts outside a string at depth 0
     uint32_t n_samples = 0, n_series = 0;
     mx_events(t, esc, cur, (int32_t)P.pair_depth, [&](uint32_t) { ++n_samples; }, [&](uint32_t) { ++n_series; },
@@ -233,14 +247,16 @@ __global__ void __launch_bounds__(kMxThreads) k_mx_count(const __grid_constant__
             a += wsum[0][k];
             b += wsum[1][k];
         }
-        P.cta_counts[blockIdx.x] = make_uint2(a, b);
+        P.cta_counts[cta] = make_uint2(a, b);
     }
 }
 
 __global__ void __launch_bounds__(kMxThreads) k_mx_top2(const __grid_constant__ MxParams P) {
     __shared__ unsigned long long wtot[2][kMxThreads / 32];
-    const uint32_t per = (P.n_ctas + kMxThreads - 1) / kMxThreads;
-    const uint32_t a = min(P.n_ctas, threadIdx.x * per), b = min(P.n_ctas, a + per);
+    const uint32_t end = P.cta_first + P.cta_count;
+    const uint32_t per = (P.cta_count + kMxThreads - 1) / kMxThreads;
+    const uint32_t a = min(end, P.cta_first + threadIdx.x * per), b = min(end, a + per);
+    const unsigned long long c0 = P.ctl[0], c1 = P.ctl[1];   // samples and series before this piece
     unsigned long long s0 = 0, s1 = 0;
     for (uint32_t i = a; i < b; ++i) {
         const uint2 c = P.cta_counts[i];
@@ -271,7 +287,7 @@ __global__ void __launch_bounds__(kMxThreads) k_mx_top2(const __grid_constant__ 
         t0 += wtot[0][k];
         t1 += wtot[1][k];
     }
-    unsigned long long r0 = p0 + i0 - s0, r1 = p1 + i1 - s1;
+    unsigned long long r0 = c0 + p0 + i0 - s0, r1 = c1 + p1 + i1 - s1;
     // sample indices are 32-bit in the per-CTA table: the host refuses answers past 2^32 - 1 samples
     for (uint32_t i = a; i < b; ++i) {
         const uint2 c = P.cta_counts[i];
@@ -279,15 +295,17 @@ __global__ void __launch_bounds__(kMxThreads) k_mx_top2(const __grid_constant__ 
         r0 += c.x;
         r1 += c.y;
     }
+    __syncthreads();   // every thread has read the running totals
     if (threadIdx.x == 0) {
-        P.ctl[0] = t0;
-        P.ctl[1] = t1;
+        P.ctl[0] = c0 + t0;
+        P.ctl[1] = c1 + t1;
     }
 }
 
 __global__ void __launch_bounds__(kMxThreads) k_mx_emit(const __grid_constant__ MxParams P) {
     __shared__ uint32_t wtot[2][kMxThreads / 32];
-    const uint32_t chunk = blockIdx.x * kMxThreads + threadIdx.x;
+    const uint32_t cta_id = P.cta_first + blockIdx.x;
+    const uint32_t chunk = cta_id * kMxThreads + threadIdx.x;
     const unsigned long long base = (unsigned long long)chunk * kMxChunk;
     const uint2 mine = P.chunk_counts[chunk];
     uint32_t i0 = mine.x, i1 = mine.y;
@@ -305,13 +323,13 @@ __global__ void __launch_bounds__(kMxThreads) k_mx_emit(const __grid_constant__ 
         wtot[1][w] = i1;
     }
     __syncthreads();
-    const uint2 cta = P.cta_counts[blockIdx.x];
+    const uint2 cta = P.cta_counts[cta_id];
     uint32_t k = cta.x + i0 - mine.x, s = cta.y + i1 - mine.y;
     for (uint32_t q = 0; q < w; ++q) {
         k += wtot[0][q];
         s += wtot[1][q];
     }
-    if (chunk == 0) P.offsets[P.ctl[1]] = P.ctl[0];      // closing entry of the CSR
+    if (P.last_piece && blockIdx.x == 0 && threadIdx.x == 0) P.offsets[P.ctl[1]] = P.ctl[0];   // closing entry of the CSR
     if ((mine.x | mine.y) == 0) {
         // nothing opens here, but a values array or a series may close here
         const uint32_t st = P.chunk_state[chunk];
@@ -338,8 +356,8 @@ __device__ __forceinline__ bool mx_blank(char c) { return c == ' ' || c == '\t' 
 
 // One thread per sample: '[' blanks number blanks ',' blanks ("text" | number) blanks ']'.
 __global__ void __launch_bounds__(128) k_mx_parse(const __grid_constant__ MxParams P) {
-    const unsigned long long k = (unsigned long long)blockIdx.x * 128 + threadIdx.x;
-    if (k >= P.ctl[0]) return;
+    const unsigned long long k = (unsigned long long)P.k_first + (unsigned long long)blockIdx.x * 128 + threadIdx.x;
+    if (k >= P.k_end) return;
     const char* s = P.text;
     const unsigned long long open = P.sample_pos[k], n = P.n;
     unsigned long long i = open + 1;

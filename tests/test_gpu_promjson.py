@@ -121,11 +121,22 @@ def test_vector_answer(engine):
     assert check(engine, text, vector=True) == (300, 300)
 
 
-def test_large_answer_crosses_every_boundary(engine):
-    """~2.5 M samples / 50 MB of text: thousands of CTAs, series of ragged length, labels full of escapes."""
+@pytest.mark.parametrize('piece_kb', [None, 16, 112, 4096])
+def test_large_answer_crosses_every_boundary(built_lib, monkeypatch, piece_kb):
+    """~2.5 M samples / 50 MB of text: thousands of CTAs, series of ragged length, labels full of escapes.
+    The text is decoded in pieces while later pieces are still being copied (default 32 MB); small
+    pieces put piece borders everywhere and make the result buffers grow while they fill."""
+    from kube_gpu_stats_b200.engine import Engine
+    if piece_kb:
+        monkeypatch.setenv('KGS_PARSE_PIECE_KB', str(piece_kb))
+    with Engine(0) as engine:
+        _large_answer(engine, 3000 if piece_kb != 16 else 400)
+
+
+def _large_answer(engine, n_series_made):
     rng = np.random.default_rng(12)
     parts, want_val, lens = [], [], []
-    for s in range(3000):
+    for s in range(n_series_made):
         n = int(rng.integers(0, 1700))
         v = np.round(rng.random(n) * 100, int(rng.integers(0, 6)))
         strs = [repr(float(x)) if i % 3 else ('%g' % x) for i, x in enumerate(v)]
@@ -136,12 +147,12 @@ def test_large_answer_crosses_every_boundary(engine):
         parts.append('{"metric":%s,"values":[%s]}' % (lab, vals))
     text = ('{"status":"success","data":{"resultType":"matrix","result":[' + ','.join(parts) + ']}}').encode()
     n_series, n_samples = engine.matrix_parse(text)
-    assert n_series == 3000 and n_samples == sum(lens)
+    assert n_series == n_series_made and n_samples == sum(lens)
     ts, val, off, spans = engine.matrix_fetch()
     np.testing.assert_array_equal(np.diff(off.astype(np.int64)), lens)
     np.testing.assert_array_equal(bits(val), bits(np.concatenate(want_val)))
     assert ts[0] == 1700000000.0 and np.all(np.diff(ts)[np.diff(ts) != 1.0] <= 0)
-    for s in (0, 1, 1499, 2999):
+    for s in (0, 1, n_series_made // 2, n_series_made - 1):
         so, vo, vc, sc = (int(x) for x in spans[s])
         assert json.loads(text[so:sc + 1])['metric']['pod_name'].startswith('pod-%d-' % s)
     # means of the decoded answer where it lies == means of the same CSR sent from the host

@@ -1,0 +1,97 @@
+#!/usr/bin/env python
+"""Value decode of a 1 Hz replay answer: the reference's
+``.json()`` + ``float(val[1])`` + ``sum()/len()`` on one host core against kgs_matrix_parse +
+kgs_matrix_mean from a pinned host buffer (H2D copy inside the timed region).
+
+The answer text is Prometheus-shaped: ``series`` series of ``points`` [ts,"v"] pairs each
+(configs[0]: 64 x 3600; configs[1]-scale: 8000 x 3600 = 28.8 M samples, ~0.6 GB of text).
+Prints one JSON object."""
+import argparse
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from kube_gpu_stats_b200.engine import Engine  # noqa: E402
+
+
+def answer_text(series, points, distinct=64, seed=0):
+    """Bytes of a /query_range answer; `distinct` different series bodies are cycled."""
+    rng = np.random.default_rng(seed)
+    bodies = []
+    for s in range(min(distinct, series)):
+        v = np.clip(np.round(50 + np.cumsum(rng.normal(0, 2, points)), 1), 0, 100)
+        bodies.append(','.join('[%d,"%s"]' % (1700000000 + i, repr(float(x)).rstrip('0').rstrip('.') or '0')
+                               for i, x in enumerate(v)))
+    parts = []
+    for s in range(series):
+        parts.append('{"metric":{"kubernetes_io_hostname":"node-%d","nvidia_gpu_type":"B200","pod_name":"pod-%d"},"values":[%s]}'
+                     % (s // 8, s, bodies[s % len(bodies)]))
+    return ('{"status":"success","data":{"resultType":"matrix","result":[' + ','.join(parts) + ']}}').encode()
+
+
+def reference_decode(text):
+    """gpu_util_stats.py:25 + :68-80 on the host: decode, float() every value, mean per series."""
+    res = json.loads(text)['data']['result']
+    out = []
+    for r in res:
+        vals = []
+        for v in r['values']:
+            vals.append(float(v[1]))
+        out.append(sum(vals) / len(vals) if vals else 0.0)
+    return out
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--series', type=int, default=8000)
+    ap.add_argument('--points', type=int, default=3600)
+    ap.add_argument('--cpu-series', type=int, default=256, help='series in the bounded CPU sample')
+    ap.add_argument('--reps', type=int, default=5)
+    a = ap.parse_args()
+    text = answer_text(a.series, a.points)
+    n_samples = a.series * a.points
+    with Engine(0) as eng:
+        pin = eng.pinned(len(text), dtype=np.uint8)
+        pin[:] = np.frombuffer(text, dtype=np.uint8)
+        where = (pin.ctypes.data, len(text))
+        for _ in range(2):
+            eng.matrix_parse(where)
+            means = eng.matrix_mean()
+        eng.set_profiling(True)
+        eng.reset_kernel_times()
+        t0 = time.perf_counter()
+        for _ in range(a.reps):
+            ns, nv = eng.matrix_parse(where)
+            means = eng.matrix_mean()
+        wall = (time.perf_counter() - t0) / a.reps
+        kt = eng.kernel_times()
+        eng.set_profiling(False)
+        assert (ns, nv) == (a.series, n_samples)
+        kernels_ms = (kt['parse'][0] + kt['segmean'][0]) / a.reps
+        # pageable bytes object instead of the pinned buffer (what requests hands over)
+        t0 = time.perf_counter()
+        eng.matrix_parse(text)
+        eng.matrix_mean()
+        wall_pageable = time.perf_counter() - t0
+    small = answer_text(a.cpu_series, a.points)
+    t0 = time.perf_counter()
+    ref = reference_decode(small)
+    cpu = time.perf_counter() - t0
+    got = means[:a.cpu_series]
+    same = bool(np.allclose(got, ref, rtol=1e-12, atol=0))
+    print(json.dumps({
+        'workload': '%d series x %d points, %.1f MB of answer text' % (a.series, a.points, len(text) / 1e6),
+        'gpu_ms_per_answer': round(wall * 1e3, 3), 'gpu_kernels_ms': round(kernels_ms, 3),
+        'gpu_samples_per_s': round(n_samples / wall), 'gpu_text_GBps': round(len(text) / wall / 1e9, 2),
+        'gpu_ms_from_pageable_bytes': round(wall_pageable * 1e3, 3),
+        'cpu_reference_samples_per_s': round(a.cpu_series * a.points / cpu),
+        'cpu_sample': '%d series x %d points (%.1f s on 1 core)' % (a.cpu_series, a.points, cpu),
+        'speedup': round(n_samples / wall / (a.cpu_series * a.points / cpu), 1), 'means_agree': same}))
+
+
+if __name__ == '__main__':
+    main()
