@@ -315,6 +315,11 @@ def run_b200(args):
             crossover = {'gpu_faster_from_samples': xn,
                          'points': [{'samples': n_, 'gpu_e2e_ms': g_ * 1e3, 'cpu_ms': c_ * 1e3 if c_ else None} for n_, g_, c_ in xrows],
                          'note': 'GPU = table build + pinned H2D + join + 3 tables with p95 + D2H; CPU = pure-Python oracle, 1 core'}
+        decode = None
+        if not args.no_cpu_baseline and world == 1:
+            # the reference's own input: text of a Prometheus answer, decoded on the GPU (row a1)
+            import decode_bench
+            decode = decode_bench.measure(series=8 * n_nodes, points=3600, cpu_series=256, reps=3)
         if not args.no_cpu_baseline:
             rate = cpu_rate_probe(tr)
             nodes = int(max(1, min(n_nodes, rate * 15.0 / (8 * 3600))))
@@ -342,6 +347,7 @@ def run_b200(args):
                          'accum_share_of_step_kernels': (acc_ms / prof_steps) / step_kernel_ms if step_kernel_ms else None},
             'cpu_baseline': cpu,
             'crossover': crossover,
+            'decode': decode,
         }
         # keep the result honest: the last e2e step's tables must not be empty
         assert int(res['node']['count'].sum()) == n, 'e2e tables do not cover the batch'

@@ -243,6 +243,8 @@ int kgs_create(int device, kgs_handle* out) {
         if ((e = cudaEventCreateWithFlags(&h->batch[b].consumed, cudaEventDisableTiming)) != cudaSuccess) return bail(e, "cudaEventCreate");
         if ((e = cudaEventCreate(&h->mark[b])) != cudaSuccess) return bail(e, "cudaEventCreate");
     }
+    if ((e = cudaFuncSetAttribute(k_sort_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSortSmemBytes)) != cudaSuccess)
+        return bail(e, "cudaFuncSetAttribute(k_sort_scatter)");
     if (const char* e = getenv("KGS_SLIDE")) h->slide = atoi(e) != 0;
     if (const char* e = getenv("KGS_SLIDE_CHUNK")) { const int v = atoi(e); if (v >= 1 && v <= 4096) h->slide_chunk = (uint32_t)v; }
     if (const char* e = getenv("KGS_ACCUM_WAVES")) { const int v = atoi(e); if (v >= 1 && v <= 16) h->accum_waves = v; }
@@ -439,7 +441,7 @@ int kgs_reorder_batch(kgs_handle h) {
         launch(h, KGS_K_SORT, st, [&] { k_scan_reduce<<<n_part, 256, 0, st>>>(P.counts, m, partial); });
         launch(h, KGS_K_SORT, st, [&] { k_scan_top<<<1, 1024, 0, st>>>(partial, n_part); });
         launch(h, KGS_K_SORT, st, [&] { k_scan_apply<<<n_part, 256, 0, st>>>(P.counts, m, partial); });
-        launch(h, KGS_K_SORT, st, [&] { k_sort_scatter<<<P.n_ctas, kSortThreads, 0, st>>>(P); });
+        launch(h, KGS_K_SORT, st, [&] { k_sort_scatter<<<P.n_ctas, kSortThreads, kSortSmemBytes, st>>>(P); });
         for (int c = 0; c < 4; ++c) cur_in[c] = P.out[c];
     }
     KGS_CUDA(h, cudaGetLastError());

@@ -133,32 +133,64 @@ __global__ void __launch_bounds__(256) k_scan_apply(uint32_t* a, uint32_t n, con
 }
 
 // ---- stable scatter ---------------------------------------------------------------------------------
+// The CTA first sorts its 8192 elements by digit in shared memory (stable: warps in order, rounds in
+// order, lanes in order inside a match group), then writes them out bucket by bucket, so that the
+// ~32 elements a CTA has for one digit leave as one contiguous 128-byte piece per column instead of
+// 32 separate 4-byte stores (the input of a time-major feed has 32 different digits per warp load).
+struct SortSmem {
+    uint32_t slot[kSortWarps][256];   // per warp and digit: count, then next position inside the CTA's sorted order
+    uint32_t gdelta[256];             // global index of the digit's first element of this CTA minus its local start
+    uint32_t wsum[kSortWarps];
+    uint32_t dst[kSortBlock];         // global destination of the element at each sorted position
+    uint32_t val[kSortBlock];         // one column in sorted order
+};
+constexpr size_t kSortSmemBytes = sizeof(SortSmem);
+
 __global__ void __launch_bounds__(kSortThreads) k_sort_scatter(const __grid_constant__ SortParams P) {
-    __shared__ uint32_t slot[kSortWarps][256];   // per warp and digit: count, then next output index
-    const uint32_t lane = lane_id(), w = threadIdx.x >> 5;
-    for (int k = 0; k < kSortWarps; ++k) slot[k][threadIdx.x] = 0;
+    extern __shared__ __align__(16) unsigned char sort_smem_raw[];
+    SortSmem& S = *reinterpret_cast<SortSmem*>(sort_smem_raw);
+    const uint32_t lane = lane_id(), w = threadIdx.x >> 5, t = threadIdx.x;
+    for (int k = 0; k < kSortWarps; ++k) S.slot[k][t] = 0;
     __syncthreads();
-    const uint32_t wbegin = blockIdx.x * kSortBlock + w * kSortWarpSpan;
+    const uint32_t cbegin = blockIdx.x * kSortBlock;
+    const uint32_t n_cta = min(kSortBlock, P.n - cbegin);
+    const uint32_t wbegin = cbegin + w * kSortWarpSpan;
     // A: digit counts of each warp's span
     for (uint32_t r = 0; r < (uint32_t)kSortRounds; ++r) {
         const uint32_t i = wbegin + r * 32 + lane;
         const uint32_t d = i < P.n ? sort_digit(P, i) : 256u + lane;   // out-of-range lanes match nobody
         const uint32_t m = __match_any_sync(0xFFFFFFFFu, d);
-        if (d < 256u && lane == (uint32_t)(__ffs(m) - 1)) slot[w][d] += __popc(m);
+        if (d < 256u && lane == (uint32_t)(__ffs(m) - 1)) S.slot[w][d] += __popc(m);
     }
     __syncthreads();
-    // B: digit t of this CTA starts at counts[t][cta]; the warps follow one another
+    // B: thread t owns digit t: where its elements start inside the CTA's sorted order (exclusive scan
+    // over the digits), the warps following one another inside a digit, and the global base
     {
-        uint32_t run = P.counts[threadIdx.x * P.n_ctas + blockIdx.x];
+        uint32_t cnt = 0;
+        for (int k = 0; k < kSortWarps; ++k) cnt += S.slot[k][t];
+        uint32_t incl = cnt;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, incl, d);
+            if (lane >= (uint32_t)d) incl += o;
+        }
+        if (lane == 31) S.wsum[w] = incl;
+        __syncthreads();
+        uint32_t lstart = incl - cnt;
+        for (uint32_t k = 0; k < w; ++k) lstart += S.wsum[k];
+        S.gdelta[t] = P.counts[t * P.n_ctas + blockIdx.x] - lstart;
+        uint32_t run = lstart;
         for (int k = 0; k < kSortWarps; ++k) {
-            const uint32_t c = slot[k][threadIdx.x];
-            slot[k][threadIdx.x] = run;
+            const uint32_t c = S.slot[k][t];
+            S.slot[k][t] = run;
             run += c;
         }
     }
     __syncthreads();
-    // C: move the elements; inside a match group the lane order is the input order
-    for (uint32_t r = 0; r < (uint32_t)kSortRounds; ++r) {
+    // C: position of every element in the sorted order (kept in registers), destination per position
+    uint32_t lp[kSortRounds];
+#pragma unroll
+    for (int r = 0; r < kSortRounds; ++r) {
         const uint32_t i = wbegin + r * 32 + lane;
         const bool in = i < P.n;
         const uint32_t d = in ? sort_digit(P, i) : 256u + lane;
@@ -166,16 +198,24 @@ __global__ void __launch_bounds__(kSortThreads) k_sort_scatter(const __grid_cons
         const uint32_t leader = __ffs(m) - 1;
         uint32_t base = 0;
         if (in && lane == leader) {
-            base = slot[w][d];
-            slot[w][d] = base + __popc(m);
+            base = S.slot[w][d];
+            S.slot[w][d] = base + __popc(m);
         }
         base = __shfl_sync(0xFFFFFFFFu, base, leader);
-        if (in) {
-            const uint32_t dst = base + __popc(m & ((1u << lane) - 1u));
-#pragma unroll
-            for (int c = 0; c < 4; ++c) P.out[c][dst] = P.in[c][i];
-        }
+        lp[r] = base + __popc(m & ((1u << lane) - 1u));
+        if (in) S.dst[lp[r]] = S.gdelta[d] + lp[r];
         __syncwarp();
+    }
+    // D: one column at a time through shared memory, written out in sorted order
+    for (int c = 0; c < 4; ++c) {
+        __syncthreads();   // dst complete (c == 0) / the previous column has left val
+#pragma unroll
+        for (int r = 0; r < kSortRounds; ++r) {
+            const uint32_t i = wbegin + r * 32 + lane;
+            if (i < P.n) S.val[lp[r]] = P.in[c][i];
+        }
+        __syncthreads();
+        for (uint32_t k = t; k < n_cta; k += kSortThreads) P.out[c][S.dst[k]] = S.val[k];
     }
 }
 
