@@ -205,7 +205,28 @@ def run_b200(args):
     eng.sync()
 
     stream = torch.cuda.ExternalStream(eng.stream('compute'), device=torch.device('cuda', local))
-    gather = sharding.TableGather(eng, KINDS, world) if world > 1 else None
+    gather, exchange = None, None
+    if world > 1:
+        # tables travel as copy-engine pushes into peer-mapped symmetric memory (no SMs taken from the next
+        # job's kernels); the NCCL all_gather stays as the transport when symmetric memory cannot be set up
+        try:
+            if os.environ.get('KGS_EXCHANGE', 'peer') != 'peer':
+                raise RuntimeError('KGS_EXCHANGE asks for NCCL')
+            gather = sharding.PeerTableGather(eng, KINDS, world)
+            with torch.cuda.stream(stream):
+                eng.window_stats_device(spec)
+                gather.all_gather()              # rendezvous now: every rank takes the same branch
+            eng.sync()
+            exchange = 'copy-engine pushes of the packed 12 B/cell tables into every peer over NVLink (symmetric memory) + signal barrier, overlapped with the next step'
+        except Exception as exc:                 # noqa: BLE001
+            sys.stderr.write('rank %d: peer exchange not available (%s); using the NCCL all_gather\n' % (rank, exc))
+            ok = torch.tensor([0], device='cuda')
+        else:
+            ok = torch.tensor([1], device='cuda')
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        if int(ok) == 0:
+            gather = sharding.TableGather(eng, KINDS, world)
+            exchange = 'NCCL all_gather of the packed 12 B/cell exchange tables, overlapped with the next step'
 
     def step():
         # N > 1: the all_gather of step i's tables runs on a side stream while step i+1 computes
@@ -333,7 +354,7 @@ def run_b200(args):
             'vs_baseline': None, 'dtype': 'u8 in / u64 + f64 out', 'data': 'synthetic',
             'config': {'workload': workload_name(n_nodes), 'samples_per_gpu': n, 'bytes_per_sample': 16,
                        'l2': 'input per step is %.0f MB, larger than the 126 MB L2 (no flush needed)' % (n * 16 / 1e6),
-                       'parallelism': 'node-sharded x%d' % world, 'collective': 'NCCL all_gather of the packed 12 B/cell exchange tables, overlapped with the next step' if world > 1 else None},
+                       'parallelism': 'node-sharded x%d' % world, 'collective': exchange},
             'clocks': clocks,
             'e2e': {'value': total_samples * e2e_steps / e2e_s, 'unit': UNIT, 'h2d_bytes_per_step': h2d_bytes,
                     'd2h_bytes_per_step': d2h_bytes, 'steps': e2e_steps, 'ms_per_step': 1e3 * e2e_s / e2e_steps,

@@ -136,6 +136,80 @@ class TableGather:
             self._side.synchronize()
 
 
+class PeerTableGather(TableGather):
+    """The same exchange without a collective kernel: every rank PUSHES its packed tables straight
+    into every other rank's gathered buffer over NVLink with the copy engines (peer-mapped symmetric
+    memory from ``torch.distributed._symmetric_memory``; one ``cudaMemcpyAsync`` per peer), followed
+    by one signal-pad barrier.  No SM is taken from the statistics kernels of the next job, which is
+    what an NCCL all_gather running beside them costs (bench.py, N = 2..8).
+
+    Gathered buffers are double-buffered like the result regions: the push of job k+2 into a peer's
+    slot happens after the barrier of job k+1, which that peer enters only after everything it had
+    queued before (including readers of job k's slot)."""
+
+    def __init__(self, engine, kinds, world, group=None):
+        super().__init__(engine, kinds, world)
+        import torch.distributed as dist
+        self.group = group if group is not None else dist.group.WORLD
+        self.rank = dist.get_rank(self.group)
+        self._sym = None          # (nbytes, local symmetric tensor, handle, per-parity per-rank views)
+        self._parity = 0
+        self._done = {}
+
+    def _symmetric(self, nbytes):
+        import torch
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm
+        if self._sym is not None and self._sym[0] == nbytes:
+            return self._sym
+        dev = torch.device('cuda', self.eng.device)
+        biggest = torch.tensor([nbytes], dtype=torch.int64, device=dev)
+        dist.all_reduce(biggest, op=dist.ReduceOp.MAX, group=self.group)
+        if int(biggest) != nbytes:
+            raise ValueError('PeerTableGather needs equally sized exchange regions on every rank '
+                             '(%d bytes here, %d elsewhere)' % (nbytes, int(biggest)))
+        slot = (nbytes + 255) // 256 * 256
+        local = symm.empty(2 * self.world * slot, dtype=torch.uint8, device=dev)
+        hdl = symm.rendezvous(local, self.group)
+        views = [[hdl.get_buffer(r, (nbytes,), torch.uint8, (par * self.world + self.rank) * slot)
+                  for r in range(self.world)] for par in range(2)]
+        mine = [local[par * self.world * slot:(par + 1) * self.world * slot].view(self.world, slot)[:, :nbytes] for par in range(2)]
+        self._sym = (nbytes, local, hdl, views, mine)
+        return self._sym
+
+    def _push(self):
+        import torch
+        ptr, nbytes, _ = self.eng.exchange_region()
+        dev = torch.device('cuda', self.eng.device)
+        src = self._views.get(ptr)
+        if src is None or src[0].numel() != nbytes:
+            src = (torch.as_tensor(_DeviceBytes(ptr, nbytes), device=dev), None, torch.cuda.Event())
+            self._views[ptr] = src
+        self._last = ptr
+        _, _, hdl, views, mine = self._symmetric(nbytes)
+        par = self._parity
+        self._parity ^= 1
+        for k in range(self.world):                      # start with the neighbour: spread the links
+            r = (self.rank + 1 + k) % self.world
+            views[par][r].copy_(src[0], non_blocking=True)
+        hdl.barrier(channel=par, timeout_ms=20000)
+        return mine[par], src[2]
+
+    def all_gather(self):
+        dst, _ = self._push()
+        return dst
+
+    def all_gather_async(self, compute_stream):
+        import torch
+        if self._side is None:
+            self._side = torch.cuda.Stream(device=torch.device('cuda', self.eng.device))
+        self._side.wait_stream(compute_stream)
+        with torch.cuda.stream(self._side):
+            dst, done = self._push()
+            done.record(self._side)
+        return dst
+
+
 def decode_packed(buf, layout):
     """One shard's packed exchange region (uint8 array) -> {kind: {count,sum,max,mean,pct}}.
     mean and the percentiles are recomputed with the sender's own operation order (one fp64 divide;
