@@ -154,7 +154,6 @@ class PeerTableGather(TableGather):
         self.rank = dist.get_rank(self.group)
         self._sym = None          # (nbytes, local symmetric tensor, handle, per-parity per-rank views)
         self._parity = 0
-        self._done = {}
 
     def _symmetric(self, nbytes):
         import torch
@@ -189,6 +188,8 @@ class PeerTableGather(TableGather):
         _, _, hdl, views, mine = self._symmetric(nbytes)
         par = self._parity
         self._parity ^= 1
+        # one stream: spreading the copies over several streams was measured slower at 8 GPUs (0.35 vs
+        # 0.264 ms per step) - the extra stream/event calls cost more host time than the copies overlap
         for k in range(self.world):                      # start with the neighbour: spread the links
             r = (self.rank + 1 + k) % self.world
             views[par][r].copy_(src[0], non_blocking=True)
