@@ -9,8 +9,8 @@
 //   k_finalize_cells every cell: count/sum/max/mean; percentiles when the cell has <= 65 535
 //                    samples and max < 104 (u16 bins, 208 B per thread, 128 threads per CTA, 8 CTAs/SM);
 //                    other non-empty cells are appended to the wide list;
-//   k_finalize_wide  values up to 255, cells up to 65 535 samples (64 threads per CTA);
-//   k_finalize_big   anything larger, one warp per cell with u32 bins.
+//   k_finalize_rare  one launch for the two rare lists: values up to 255 with up to 65 535 samples per
+//                    cell (64 threads per CTA, u16 bins), and anything larger (a warp per cell, u32 bins).
 #pragma once
 #include "common.cuh"
 
@@ -51,9 +51,10 @@ struct FinParams {
     double q[8];
     const uint8_t* vals;
     const uint4* desc;
-    uint32_t* wide_list;                 // pairs (kind slot, cell) left to k_finalize_wide
-    uint32_t* big_list;                  // pairs left to k_finalize_big
+    uint32_t* wide_list;                 // pairs (kind slot, cell) left to k_finalize_rare (wide part)
+    uint32_t* big_list;                  // pairs left to k_finalize_rare (big part)
     uint32_t* ctl;                       // ctl[2] = big_list length, ctl[3] = wide_list length
+    uint32_t rare_wide_ctas;             // k_finalize_rare: CTAs working on the wide list (the rest: big list)
     uint32_t wide_cap, big_cap;
     uint32_t packed_sum64;               // packed sums are u64 (a cell's sum may not fit 32 bits)
     uint32_t slide_chunk;                // windows per thread of k_finalize_slide
@@ -300,6 +301,35 @@ __device__ __forceinline__ const FinKind& kind_of_cell(const FinParams& P, uint3
     return P.kind[ks];
 }
 
+// Cells the private u16 histograms cannot take go on one of two lists (one atomic per warp and
+// list): above 65 535 samples -> big list (u32 bins, a warp per cell); otherwise (a value >= 104,
+// or a 16-bit metric) -> wide list.  The two lists are worked off by ONE launch (k_finalize_rare).
+__device__ __forceinline__ void defer_cell(const FinParams& P, bool later, unsigned long long count, uint32_t ks, uint32_t c) {
+    constexpr uint32_t kAll = 0xFFFFFFFFu;
+    const bool big = later && !P.u16 && count > kSmallMax;
+    const bool wide = later && !big;
+    const uint32_t wide_mask = __ballot_sync(kAll, wide), big_mask = __ballot_sync(kAll, big);
+    const uint32_t below = (1u << lane_id()) - 1u;
+    if (wide_mask) {
+        uint32_t at = 0;
+        if (lane_id() == 0) at = atomicAdd(P.ctl + 3, (uint32_t)__popc(wide_mask));
+        at = __shfl_sync(kAll, at, 0) + __popc(wide_mask & below);
+        if (wide && at < P.wide_cap) {
+            P.wide_list[2 * at] = ks;
+            P.wide_list[2 * at + 1] = c;
+        }
+    }
+    if (big_mask) {
+        uint32_t at = 0;
+        if (lane_id() == 0) at = atomicAdd(P.ctl + 2, (uint32_t)__popc(big_mask));
+        at = __shfl_sync(kAll, at, 0) + __popc(big_mask & below);
+        if (big && at < P.big_cap) {
+            P.big_list[2 * at] = ks;
+            P.big_list[2 * at + 1] = c;
+        }
+    }
+}
+
 // Every window cell: count / sum / max / mean, and the percentiles of cells with up to 65 535
 // samples whose values stay below 104.  Cells are visited from the END of the index space
 // (node cells, the heaviest, are scheduled first).  Other non-empty cells go to the wide list.
@@ -338,19 +368,7 @@ __global__ void __launch_bounds__(CellLayout::NT, 8) k_finalize_cells(const __gr
     const FinKind& K = P.kind[ks];
     const bool fast = live && count > 0 && count <= kSmallMax && vmax < (uint32_t)L::BINS && !P.u16;
     const bool later = live && count > 0 && !fast;
-    const uint32_t later_mask = __ballot_sync(0xFFFFFFFFu, later);   // one atomic per warp
-    if (later_mask) {
-        uint32_t base = 0;
-        if (lane_id() == 0) base = atomicAdd(P.ctl + 3, (uint32_t)__popc(later_mask));
-        base = __shfl_sync(0xFFFFFFFFu, base, 0);
-        if (later) {
-            const uint32_t at = base + __popc(later_mask & ((1u << lane_id()) - 1u));
-            if (at < P.wide_cap) {
-                P.wide_list[2 * at] = ks;
-                P.wide_list[2 * at + 1] = c;
-            }
-        }
-    }
+    defer_cell(P, later, count, ks, c);
     // Twin cells.  With one process per GPU a (gpu, window) cell and its (pod, window) cell usually
     // consist of the very same single run, and k_accum wrote that run's descriptors side by side
     // (pod at index i, gpu at i + 1).  The pod cell's thread then selects once and stores the
@@ -379,33 +397,25 @@ __global__ void __launch_bounds__(CellLayout::NT, 8) k_finalize_cells(const __gr
     if (work) select_store<L>(base, P, K, c, (uint32_t)count, vmax, twin_cell);
 }
 
-// The wide list: values up to 255 (u16 bins, 256 values); cells above 65 535 samples move on to
-// the big list.
-__global__ void __launch_bounds__(WideLayout::NT) k_finalize_wide(const __grid_constant__ FinParams P) {
+// The wide list: values up to 255 (u16 bins, 256 values), at most 65 535 samples per cell.
+// CTAs [0, P.rare_wide_ctas) of k_finalize_rare.
+__device__ __forceinline__ void finalize_wide_part(const FinParams& P, uint32_t cta, uint32_t n_ctas) {
     using L = WideLayout;
     __shared__ uint32_t hist[L::WORDS * L::NT];
     const uint32_t tid = threadIdx.x;
     const uint32_t n_wide = P.ctl[1] ? 0u : min(P.ctl[3], P.wide_cap);
-    if (blockIdx.x * L::NT >= n_wide) return;
+    if (cta * L::NT >= n_wide) return;
     const uint32_t base = (uint32_t)__cvta_generic_to_shared(hist) + tid * 4;
     for (uint32_t a = base; a < base + L::WORDS * L::ROW; a += L::ROW) sts_u32(a, 0);
-    for (uint32_t it0 = blockIdx.x * L::NT; it0 < n_wide; it0 += gridDim.x * L::NT) {   // CTA-uniform trips
+    for (uint32_t it0 = cta * L::NT; it0 < n_wide; it0 += n_ctas * L::NT) {   // CTA-uniform trips
         const uint32_t it = it0 + tid;
-        bool valid = it < n_wide;
+        const bool valid = it < n_wide;
         uint32_t ks = 0, c = 0, vmax = 0, pc0 = 0;
         unsigned long long count = 0;
         if (valid) {
             ks = P.wide_list[2 * it];
             c = P.wide_list[2 * it + 1];
             count = P.kind[ks].o_count[c];
-            if (count > kSmallMax) {
-                const uint32_t at = atomicAdd(P.ctl + 2, 1u);
-                if (at < P.big_cap) {
-                    P.big_list[2 * at] = ks;
-                    P.big_list[2 * at + 1] = c;
-                }
-                valid = false;
-            }
         }
         const FinKind& K = P.kind[ks];
         if (valid) {
@@ -421,14 +431,15 @@ __global__ void __launch_bounds__(WideLayout::NT) k_finalize_wide(const __grid_c
 }
 
 // Cells above kSmallMax samples: one warp per cell, u32 bins in shared memory.  Every lane reads
-// the same descriptor, the whole warp counts each run's bytes.
-__global__ void __launch_bounds__(128) k_finalize_big(const __grid_constant__ FinParams P) {
-    __shared__ uint32_t hist_all[4][256];
+// the same descriptor, the whole warp counts each run's bytes.  The CTAs behind the wide part.
+__device__ __forceinline__ void finalize_big_part(const FinParams& P, uint32_t cta, uint32_t n_ctas) {
+    constexpr uint32_t kWarps = WideLayout::NT / 32;
+    __shared__ uint32_t hist_all[kWarps][256];
     const uint32_t lane = lane_id(), wib = threadIdx.x >> 5;
     uint32_t* hist = hist_all[wib];
     const uint32_t n_big = P.ctl[1] ? 0u : min(P.ctl[2], P.big_cap);
-    const uint32_t warps = gridDim.x * 4;
-    for (uint32_t it = blockIdx.x * 4 + wib; it < n_big; it += warps) {
+    const uint32_t warps = n_ctas * kWarps;
+    for (uint32_t it = cta * kWarps + wib; it < n_big; it += warps) {
         const FinKind& K = P.kind[P.big_list[2 * it]];
         const uint32_t c = P.big_list[2 * it + 1];
         const uint32_t key = c / P.n_windows, j = c - key * P.n_windows;
@@ -463,6 +474,12 @@ __global__ void __launch_bounds__(128) k_finalize_big(const __grid_constant__ Fi
         }
         __syncwarp();
     }
+}
+
+// Both rare lists in one launch (each is almost always empty; two launches cost 6 % of a step).
+__global__ void __launch_bounds__(WideLayout::NT) k_finalize_rare(const __grid_constant__ FinParams P) {
+    if (blockIdx.x < P.rare_wide_ctas) finalize_wide_part(P, blockIdx.x, P.rare_wide_ctas);
+    else finalize_big_part(P, blockIdx.x - P.rare_wide_ctas, gridDim.x - P.rare_wide_ctas);
 }
 
 // 16-bit metrics (fb_mib): a two-digit radix select, one warp per cell.  Pass 1 counts the HIGH

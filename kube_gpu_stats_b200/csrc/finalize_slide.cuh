@@ -7,7 +7,7 @@
 // selects.  Only the first window of a chunk counts W panes.  Same exact selection (rule R5).
 //   * count / sum / max / mean of every window cell come from k_finalize_basic (no shared memory);
 //   * a chunk that meets a value >= 104 or a window above 65 535 samples hands its windows to the
-//     wide list (k_finalize_wide / k_finalize_big count them the slow way).
+//     wide or big list (k_finalize_rare counts them the slow way).
 #pragma once
 #include "finalize.cuh"
 
@@ -97,16 +97,7 @@ __global__ void __launch_bounds__(CellLayout::NT) k_finalize_slide(const __grid_
         }
         const uint32_t c = key * P.n_windows + j;
         const bool later = on && count > 0 && (bad || count > kSmallMax);
-        const uint32_t later_mask = __ballot_sync(kAll, later);
-        if (later_mask) {                           // the slow kernels count these windows pane by pane
-            uint32_t at = 0;
-            if (lane_id() == 0) at = atomicAdd(P.ctl + 3, (uint32_t)__popc(later_mask));
-            at = __shfl_sync(kAll, at, 0) + __popc(later_mask & ((1u << lane_id()) - 1u));
-            if (later && at < P.wide_cap) {
-                P.wide_list[2 * at] = ks;
-                P.wide_list[2 * at + 1] = c;
-            }
-        }
+        defer_cell(P, later, count, ks, c);         // the slow kernel counts these windows pane by pane
         if (on && count > 0 && !later) {
             for (uint32_t iq = 0; iq < P.n_q; ++iq) {
                 uint32_t ilo, ihi, vlo, vhi;

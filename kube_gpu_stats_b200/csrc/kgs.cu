@@ -900,12 +900,11 @@ int kgs_stats_finalize(kgs_handle h) {
         }
         if (sp.n_q && sp.metric == KGS_METRIC_FB) {   // 16-bit values: two-digit radix select, warp per cell
             launch(h, KGS_K_FINALIZE_WIDE, st, [&] { k_finalize_u16<<<148 * 8, 128, 0, st>>>(P); });
-        } else if (sp.n_q) {   // cells with values >= 128 (and, through the big list, above 65 535 samples)
+        } else if (sp.n_q) {   // one launch for the cells with values >= 104 and those above 65 535 samples
             const int wide_grid = grid_for(cells, WideLayout::NT, 148 * 6);
-            launch(h, KGS_K_FINALIZE_WIDE, st, [&] { k_finalize_wide<<<wide_grid, WideLayout::NT, 0, st>>>(P); });
-        }
-        if (sp.n_q && sp.metric != KGS_METRIC_FB && h->accumulated * h->W > kSmallMax) {
-            launch(h, KGS_K_FINALIZE_BIG, st, [&] { k_finalize_big<<<148, 128, 0, st>>>(P); });
+            const int big_grid = h->accumulated * h->W > kSmallMax ? 148 * 2 : 0;
+            P.rare_wide_ctas = (uint32_t)wide_grid;
+            launch(h, KGS_K_FINALIZE_WIDE, st, [&] { k_finalize_rare<<<wide_grid + big_grid, WideLayout::NT, 0, st>>>(P); });
         }
     }
     KGS_CUDA(h, cudaGetLastError());
