@@ -21,6 +21,7 @@
 #pragma once
 #include "common.cuh"
 #include "strtod.cuh"
+#include "promjson_bits.cuh"
 
 namespace kgs {
 
@@ -105,49 +106,23 @@ __device__ __forceinline__ bool mx_escaped_at(const char* text, unsigned long lo
     return run & 1u;
 }
 
-// Calls f(index in chunk, byte) for every byte of the chunk that is neither a backslash nor escaped.
-template <class F>
-__device__ __forceinline__ void mx_walk(const uint4 (&t)[4], bool esc, F&& f) {
-#pragma unroll
-    for (int v = 0; v < 4; ++v) {
-        const uint32_t w[4] = {t[v].x, t[v].y, t[v].z, t[v].w};
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-#pragma unroll
-            for (int b = 0; b < 4; ++b) {
-                const uint32_t c = (w[j] >> (8 * b)) & 0xFFu;
-                if (esc) {
-                    esc = false;
-                } else if (c == '\\') {
-                    esc = true;
-                } else {
-                    f((uint32_t)(v * 16 + j * 4 + b), c);
-                }
-            }
-        }
-    }
-}
-
 __device__ __forceinline__ void mx_load(const MxParams& P, unsigned long long base, uint4 (&t)[4]) {
     const uint4* p = reinterpret_cast<const uint4*>(P.text + base);
 #pragma unroll
     for (int v = 0; v < 4; ++v) t[v] = __ldg(p + v);
 }
 
-__device__ __forceinline__ MxTrans mx_chunk_trans(const uint4 (&t)[4], bool esc) {
-    uint32_t par = 0;
-    int32_t d[2] = {0, 0};
-    mx_walk(t, esc, [&](uint32_t, uint32_t c) {
-        if (c == '"') {
-            par ^= 1u;
-        } else {
-            const uint32_t k = c | 0x20u;                 // '[' | 0x20 == '{', ']' | 0x20 == '}'
-            const int32_t step = (k == '{') ? 1 : ((k == '}') ? -1 : 0);
-            d[0] += par ? 0 : step;
-            d[1] += par ? step : 0;
-        }
-    });
-    return MxTrans{par, d[0], d[1]};
+// The chunk as masks (promjson_bits.cuh): 16 words -> where the quotes, escapes and brackets are.
+__device__ __forceinline__ MxLex mx_lex_chunk(const uint4 (&t)[4], bool first_escaped) {
+    const uint32_t w[16] = {t[0].x, t[0].y, t[0].z, t[0].w, t[1].x, t[1].y, t[1].z, t[1].w,
+                            t[2].x, t[2].y, t[2].z, t[2].w, t[3].x, t[3].y, t[3].z, t[3].w};
+    return mx_lex(mx_masks(w), first_escaped);
+}
+
+__device__ __forceinline__ MxTrans mx_chunk_trans(const MxLex& x) {
+    int d0, d1;
+    mx_depth_change(x, d0, d1);
+    return MxTrans{x.flip, d0, d1};
 }
 
 __global__ void __launch_bounds__(kMxThreads) k_mx_classify(const __grid_constant__ MxParams P) {
@@ -156,7 +131,7 @@ __global__ void __launch_bounds__(kMxThreads) k_mx_classify(const __grid_constan
     const unsigned long long base = ((unsigned long long)cta * kMxThreads + threadIdx.x) * kMxChunk;
     uint4 t[4];
     mx_load(P, base, t);
-    const MxTrans mine = mx_chunk_trans(t, mx_escaped_at(P.text, base));
+    const MxTrans mine = mx_chunk_trans(mx_lex_chunk(t, mx_escaped_at(P.text, base)));
     MxTrans total;
     mx_block_scan(mine, warp_tot, total);
     if (threadIdx.x == 0) P.cta_trans[cta] = total;
@@ -187,37 +162,6 @@ __global__ void __launch_bounds__(kMxThreads) k_mx_top(const __grid_constant__ M
     }
 }
 
-struct MxCursor {   // lexical state while walking a chunk
-    uint32_t in_string;
-    int32_t depth;
-};
-
-template <class Sample, class SeriesOpen, class ValuesOpen, class ValuesClose, class SeriesClose>
-__device__ __forceinline__ void mx_events(const uint4 (&t)[4], bool esc, MxCursor cur, int32_t pair_depth, Sample&& on_sample,
-                                          SeriesOpen&& on_series, ValuesOpen&& on_vopen, ValuesClose&& on_vclose,
-                                          SeriesClose&& on_sclose) {
-    mx_walk(t, esc, [&](uint32_t i, uint32_t c) {
-        if (c == '"') {
-            cur.in_string ^= 1u;
-        } else if (!cur.in_string) {
-            if (c == '[') {
-                if (cur.depth == pair_depth) on_sample(i);
-                else if (cur.depth == 4) on_vopen(i);
-                ++cur.depth;
-            } else if (c == '{') {
-                if (cur.depth == 3) on_series(i);
-                ++cur.depth;
-            } else if (c == ']') {
-                --cur.depth;
-                if (cur.depth == 4 && pair_depth == 5) on_vclose(i);
-            } else if (c == '}') {
-                --cur.depth;
-                if (cur.depth == 3) on_sclose(i);
-            }
-        }
-    });
-}
-
 __global__ void __launch_bounds__(kMxThreads) k_mx_count(const __grid_constant__ MxParams P) {
     __shared__ MxTrans warp_tot[kMxThreads / 32];
     __shared__ uint32_t wsum[2][kMxThreads / 32];
@@ -226,14 +170,17 @@ __global__ void __launch_bounds__(kMxThreads) k_mx_count(const __grid_constant__
     const unsigned long long base = (unsigned long long)chunk * kMxChunk;
     uint4 t[4];
     mx_load(P, base, t);
-    const bool esc = mx_escaped_at(P.text, base);
+    const MxLex lex = mx_lex_chunk(t, mx_escaped_at(P.text, base));
     MxTrans total;
-    const MxTrans before = mx_then(P.cta_trans[cta], mx_block_scan(mx_chunk_trans(t, esc), warp_tot, total));
-    const MxCursor cur{before.flip, before.d0};          // the text starts outside a string at depth 0
+    const MxTrans before = mx_then(P.cta_trans[cta], mx_block_scan(mx_chunk_trans(lex), warp_tot, total));
+    const uint32_t in_string = before.flip;              // the text starts outside a string at depth 0
+    const int32_t depth = before.d0;
     uint32_t n_samples = 0, n_series = 0;
-    mx_events(t, esc, cur, (int32_t)P.pair_depth, [&](uint32_t) { ++n_samples; }, [&](uint32_t) { ++n_series; },
-              [](uint32_t) {}, [](uint32_t) {}, [](uint32_t) {});
-    P.chunk_state[chunk] = ((uint32_t)cur.depth << 1) | cur.in_string;
+    mx_brackets(lex, in_string, depth, (int)P.pair_depth, [&](int kind, uint32_t) {
+        n_samples += kind == 0;
+        n_series += kind == 1;
+    });
+    P.chunk_state[chunk] = ((uint32_t)depth << 1) | in_string;
     P.chunk_counts[chunk] = make_uint2(n_samples, n_series);
     const uint32_t s0 = __reduce_add_sync(0xFFFFFFFFu, n_samples), s1 = __reduce_add_sync(0xFFFFFFFFu, n_series);
     if (lane_id() == 0) {
@@ -338,18 +285,18 @@ __global__ void __launch_bounds__(kMxThreads) k_mx_emit(const __grid_constant__ 
     uint4 t[4];
     mx_load(P, base, t);
     const uint32_t st = P.chunk_state[chunk];
-    const MxCursor cur{st & 1u, (int32_t)(st >> 1)};
-    mx_events(
-        t, mx_escaped_at(P.text, base), cur, (int32_t)P.pair_depth,
-        [&](uint32_t i) { P.sample_pos[k++] = (uint32_t)(base + i); },
-        [&](uint32_t i) {
+    const MxLex lex = mx_lex_chunk(t, mx_escaped_at(P.text, base));
+    mx_brackets(lex, st & 1u, (int)(st >> 1), (int)P.pair_depth, [&](int kind, uint32_t i) {
+        if (kind == 0) {
+            P.sample_pos[k++] = (uint32_t)(base + i);
+        } else if (kind == 1) {
             P.offsets[s] = k;
             P.spans[4ull * s] = base + i;
             ++s;
-        },
-        [&](uint32_t i) { if (s) P.spans[4ull * (s - 1) + 1] = base + i; },
-        [&](uint32_t i) { if (s) P.spans[4ull * (s - 1) + 2] = base + i; },
-        [&](uint32_t i) { if (s) P.spans[4ull * (s - 1) + 3] = base + i; });
+        } else if (s) {                                  // 2: '[' of values, 3: its ']', 4: '}' of the series
+            P.spans[4ull * (s - 1) + (uint32_t)(kind - 1)] = base + i;
+        }
+    });
 }
 
 __device__ __forceinline__ bool mx_blank(char c) { return c == ' ' || c == '\t' || c == '\n' || c == '\r'; }
