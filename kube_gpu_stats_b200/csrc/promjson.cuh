@@ -307,9 +307,23 @@ __global__ void __launch_bounds__(128) k_mx_parse(const __grid_constant__ MxPara
     if (k >= P.k_end) return;
     const char* s = P.text;
     const unsigned long long open = P.sample_pos[k], n = P.n;
+    double ts = 0.0, v = 0.0;
+    {   // the everyday form [digits[.digits],"digits[.digits]"] with short numbers: no grammar, one division each
+        // (the text is padded with zero bytes, so the digit loops stop inside the buffer)
+        const char* p = s + open + 1;
+        const uint32_t a = parse_short_decimal(p, &ts);
+        if (a && p[a] == ',' && p[a + 1] == '"') {
+            const char* q = p + a + 2;
+            const uint32_t b = parse_short_decimal(q, &v);
+            if (b && q[b] == '"' && q[b + 1] == ']') {
+                P.ts[k] = ts;
+                P.val[k] = v;
+                return;
+            }
+        }
+    }
     unsigned long long i = open + 1;
     bool ok = true;
-    double ts = 0.0, v = 0.0;
     while (i < n && mx_blank(s[i])) ++i;
     unsigned long long a = i;
     while (i < n && s[i] != ',' && s[i] != ']' && !mx_blank(s[i])) ++i;

@@ -108,6 +108,51 @@ KGS_HD inline unsigned long long eisel_lemire(unsigned long long w, long long q)
     return ((unsigned long long)power2 << 52) | mant;
 }
 
+// ---- the common case first -------------------------------------------------------------------------
+// "-?digits[.digits]" with at most 15 digits in all (what a utilisation or an epoch timestamp looks
+// like): the digits are an integer below 2^53 and 10^k is exact, so ONE correctly rounded division
+// gives the correctly rounded value (Clinger's fast path) - a few dozen instructions instead of the
+// full grammar + Eisel-Lemire.  Returns the number of characters consumed (the caller checks what
+// follows), 0 if the text at s does not have this form; s must be readable up to a non-digit byte.
+KGS_HD inline uint32_t parse_short_decimal(const char* s, double* out) {
+    uint32_t i = 0, nd = 0, nf = 0;
+    const bool neg = s[0] == '-';
+    if (neg) i = 1;
+    unsigned long long w = 0;
+    uint32_t c;
+    while ((c = (uint32_t)(unsigned char)s[i] - (uint32_t)'0') <= 9u && nd <= 15u) {
+        w = w * 10 + c;
+        ++i;
+        ++nd;
+    }
+    if (s[i] == '.') {
+        ++i;
+        while ((c = (uint32_t)(unsigned char)s[i] - (uint32_t)'0') <= 9u && nd + nf <= 15u) {
+            w = w * 10 + c;
+            ++i;
+            ++nf;
+        }
+    }
+    if (nd + nf == 0 || nd + nf > 15u) return 0;
+    double v = (double)(long long)w;
+    if (nf) {
+        double p = 1.0;
+        switch (nf) {   // exact powers of ten
+            case 1: p = 1e1; break;   case 2: p = 1e2; break;   case 3: p = 1e3; break;   case 4: p = 1e4; break;
+            case 5: p = 1e5; break;   case 6: p = 1e6; break;   case 7: p = 1e7; break;   case 8: p = 1e8; break;
+            case 9: p = 1e9; break;   case 10: p = 1e10; break; case 11: p = 1e11; break; case 12: p = 1e12; break;
+            case 13: p = 1e13; break; case 14: p = 1e14; break; default: p = 1e15; break;
+        }
+#ifdef __CUDA_ARCH__
+        v = __ddiv_rn(v, p);
+#else
+        v = v / p;
+#endif
+    }
+    *out = neg ? -v : v;
+    return i;
+}
+
 // ---- exact tie-break for tokens with more than 19 significant digits --------------------------------
 struct BigNat {
     static constexpr int kLimbs = 136;   // 4352 bits: 769 digits, or 2^54 * 5^1100, with room to shift

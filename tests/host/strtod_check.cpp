@@ -14,7 +14,12 @@ int main() {
         const bool ok = kgs::parse_float(line.data(), (uint32_t)line.size(), &v);
         unsigned long long bits;
         std::memcpy(&bits, &v, 8);
-        std::printf("%d %016llx\n", ok ? 1 : 0, ok ? bits : 0ull);
+        // the short-decimal fast path on the same token (zero-terminated by std::string)
+        double f = 0;
+        const uint32_t used = kgs::parse_short_decimal(line.c_str(), &f);
+        unsigned long long fbits;
+        std::memcpy(&fbits, &f, 8);
+        std::printf("%d %016llx %u %016llx\n", ok ? 1 : 0, ok ? bits : 0ull, used, used ? fbits : 0ull);
     }
     return 0;
 }

@@ -85,6 +85,7 @@ def test_strings_that_look_like_structure(engine):
 
 def test_value_grammar_is_floats(engine):
     toks = ['NaN', '+Inf', '-Inf', 'inf', 'nan', 'Infinity', '1e5', '1E-5', '.5', '5.', '1_000', ' 7 ', '+3', '-0', '0.1', '0.30000000000000004',
+            '999999999999999', '9999999999999999', '-.5', '00012.50', '0.000000000000001', '123456789.123456', '1234567890.123456', '2.675', '-0.0',
             '4.9406564584124654e-324', '2.4703282292062328e-324', '1.7976931348623157e308', '1.7976931348623159e308', '1e400',
             '9007199254740993', '9007199254740992.5', '9007199254740993.0000000000000000000000001', '123456789012345678901234567890',
             '1000000000000000000000', '0.000001', '1' + '0' * 400, '0.' + '0' * 400 + '1']
@@ -95,7 +96,9 @@ def test_value_grammar_is_floats(engine):
             toks.append(repr(x))
     for _ in range(5000):
         toks.append('0.' + ''.join(rng.choice('0123456789') for _ in range(rng.randint(17, 30))) + 'e%d' % rng.randint(-330, 310))
-    series = [({'i': str(k)}, [[1700000000 + j, t] for j, t in enumerate(toks[k::7])]) for k in range(7)]
+    for _ in range(20000):     # short decimals: the one-division path of k_mx_parse
+        toks.append('%d.%s' % (rng.randint(0, 10 ** rng.randint(0, 9)), ''.join(rng.choice('0123456789') for _ in range(rng.randint(0, 6)))))
+    series = [({'i': str(k)}, [[1700000000 + j if j % 3 else 1700000000.0 + j / 8, t] for j, t in enumerate(toks[k::7])]) for k in range(7)]
     check(engine, matrix(series, separators=(',', ':')))
 
 

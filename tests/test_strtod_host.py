@@ -21,9 +21,11 @@ def checker(tmp_path_factory):
     def run(tokens):
         out = subprocess.run([str(exe)], input='\n'.join(tokens) + '\n', capture_output=True, text=True, check=True)
         res = []
+        run.fast = []
         for line in out.stdout.splitlines():
-            ok, bits = line.split()
+            ok, bits, used, fbits = line.split()
             res.append((int(ok), int(bits, 16)))
+            run.fast.append((int(used), int(fbits, 16)))
         return res
     return run
 
@@ -113,3 +115,32 @@ def test_random_tokens(checker):
     got = checker(toks)
     bad = [(t, g, expected(t)) for t, g in zip(toks, got) if not same(g, expected(t))]
     assert not bad, bad[:5]
+
+
+def test_short_decimal_fast_path(checker):
+    """parse_short_decimal: when it accepts a token completely it must give float()'s bits; it must
+    accept the everyday forms (that is the point of it) and refuse what it cannot do exactly."""
+    rng = random.Random(21)
+    toks = ['0', '7', '100', '57.5', '-0', '-0.0', '5.', '.5', '-.5', '00012.50', '1700000000', '1700000000.123',
+            '999999999999999', '9999999999999999', '0.000000000000001', '123456789.123456', '1234567890.123456',
+            '.', '-', '-.', '', '1e5', '12a', '1_0', 'nan', '0.1', '0.3', '99.99999999999', '4.35', '2.675', '1.005']
+    for _ in range(60000):
+        a = rng.randint(0, 15)
+        b = rng.randint(0, 15 - a)
+        t = ''.join(rng.choice('0123456789') for _ in range(a))
+        if b or rng.random() < .2:
+            t += '.' + ''.join(rng.choice('0123456789') for _ in range(b))
+        toks.append(('-' if rng.random() < .2 else '') + t)
+    toks = [t for t in toks if '\n' not in t]
+    checker(toks)
+    accepted = 0
+    for tok, (used, fbits) in zip(toks, checker.fast):
+        if used == len(tok) and used:
+            accepted += 1
+            assert (1, fbits) == expected(tok), (tok, hex(fbits), expected(tok))
+        else:
+            digits = sum(ch.isdigit() for ch in tok)
+            simple = digits and digits <= 15 and all(ch in '-.0123456789' for ch in tok) and tok.count('.') <= 1 \
+                and '-' not in tok[1:]
+            assert not simple, ('fast path refused a short decimal', tok, used)
+    assert accepted > 50000
