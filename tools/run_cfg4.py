@@ -73,7 +73,13 @@ else:
     kinds, qs = ('pod', 'gpu', 'node'), (0.95,)
     spec = eng.make_spec(kinds=kinds, metric='sm', gpus_per_node=8, t0=base.t0, step=60, n_windows=args.seconds // 60,
                          n_gpus=n_gpus, n_nodes=n_nodes, qs=qs, total_samples_hint=n)
-gather = sharding.TableGather(eng, kinds, world) if world > 1 else None
+ap_exchange = os.environ.get('KGS_EXCHANGE', 'peer')
+gather = None
+if world > 1:
+    eng.set_packed_exchange(True)
+    gather = sharding.PeerTableGather(eng, kinds, world) if ap_exchange == 'peer' else sharding.TableGather(eng, kinds, world)
+    if rank == 0:
+        print('exchange: %s' % type(gather).__name__, flush=True)
 stream = torch.cuda.ExternalStream(eng.stream('compute'), device=torch.device('cuda', local))
 with torch.cuda.stream(stream):
     eng.window_stats_device(spec)                 # warm-up (allocates the arena)
