@@ -1146,6 +1146,11 @@ int kgs_matrix_parse(kgs_handle h, const char* text, uint64_t nbytes, int result
             KGS_CUDA(h, cudaMemsetAsync(static_cast<char*>(b.p) + keep, fill, b.cap - keep, st));
         return KGS_OK;
     };
+    // whatever way this function is left, no copy may still be reading the caller's buffer
+    struct DrainCopies {
+        cudaStream_t s;
+        ~DrainCopies() { cudaStreamSynchronize(s); }
+    } drain{h->copy};
     unsigned long long head[8];
     uint64_t k_done = 0, s_done = 0;
     uint32_t sent = 0;
@@ -1165,14 +1170,10 @@ int kgs_matrix_parse(kgs_handle h, const char* text, uint64_t nbytes, int result
         KGS_CUDA(h, cudaMemcpyAsync(head, ctl, 64, cudaMemcpyDeviceToHost, st));
         KGS_CUDA(h, cudaStreamSynchronize(st));
         const uint64_t ns = head[0], nser = head[1];
-        if (P.last_piece && head[4] != 0) {
-            cudaStreamSynchronize(h->copy);
+        if (P.last_piece && head[4] != 0)
             return fail(h, KGS_ERR_PARSE, "kgs_matrix_parse: the text ends inside a string or with unbalanced brackets");
-        }
-        if (ns >= (1ull << 32) || nser >= (1ull << 31)) {
-            cudaStreamSynchronize(h->copy);
+        if (ns >= (1ull << 32) || nser >= (1ull << 31))
             return fail(h, KGS_ERR_ARG, "kgs_matrix_parse: too many samples or series");
-        }
         // sizes of the whole answer, projected from the text seen so far
         const double seen = (double)std::min<uint64_t>(nbytes, (uint64_t)(P.cta_first + P.cta_count) * kMxTile);
         const double scale = P.last_piece || seen <= 0 ? 1.0 : 1.1 * (double)nbytes / seen;
