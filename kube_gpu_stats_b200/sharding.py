@@ -289,3 +289,28 @@ def all_gather_tables(table):
     got = [torch.zeros(longest, dtype=torch.uint8) for _ in range(world)]
     dist.all_gather(got, padded)
     return [unpack_tables(g[:int(s)].numpy()) for g, s in zip(got, sizes)]
+
+
+def cluster_totals(per_type, group=None, device=None):
+    """The one cross-shard REDUCTION of the reference: who_use_gpu.py:18-20 sums GPU counts over all
+    pods, in total and per GPU type.  Each rank passes the totals of its own shard of pods
+    ({gpu type: count}); every rank gets back (grand total, {gpu type: count}) of the whole cluster,
+    types in first-seen order across ranks (rank 0's order first).  One all_gather of the type names
+    (strings) and one all_reduce(SUM) of a small int64 vector - NCCL when `device` is a CUDA device,
+    any backend otherwise."""
+    import torch
+    import torch.distributed as dist
+    world = dist.get_world_size(group)
+    names = [None] * world
+    dist.all_gather_object(names, list(per_type.keys()), group=group)
+    order = []
+    for rank_names in names:
+        for t in rank_names:
+            if t not in order:
+                order.append(t)
+    vec = torch.tensor([int(per_type.get(t, 0)) for t in order], dtype=torch.int64, device=device)
+    if len(order):
+        dist.all_reduce(vec, op=dist.ReduceOp.SUM, group=group)
+    totals = dict(zip(order, (int(v) for v in vec.tolist())))
+    return sum(totals.values()), totals
+

@@ -47,6 +47,11 @@ def _worker(rank, world, port, out_dir):
     for kind, kid, nk in (('pod', ws.KEY_POD, n_pods), ('gpu', ws.KEY_GPU, n_nodes * 8), ('node', ws.KEY_NODE, n_nodes)):
         local = ws.window_stats_np(ts, gid, pid, util, keys, pods, key_kind=kid, t0=tr.t0, n_keys=nk, **KW)
         merged[kind] = sharding.merge_tables(sharding.all_gather_tables(local), KW['n_windows'])
+    # the reference's one global reduction (who_use_gpu.py:18-20): GPU totals per type over all pods
+    mine = [{'P40': 6, 'V100': 2}, {'V100': 5, 'B200': 8, 'P40': 1}][rank]
+    total, per_type = sharding.cluster_totals(mine)
+    assert total == 22 and list(per_type.items()) == [('P40', 7), ('V100', 7), ('B200', 8)]
+    assert sharding.cluster_totals({}) == (0, {})
     if rank == 0:
         np.savez(os.path.join(out_dir, 'merged.npz'), **{'%s_%s' % (k, f): v for k, t in merged.items() for f, v in t.items()})
     dist.barrier()
