@@ -32,11 +32,30 @@ __global__ void __launch_bounds__(256) k_finalize_basic(const __grid_constant__ 
     store_basics(P, K, c, count, total, vmax);
 }
 
+// Four consecutive u32 of an array held in registers; reloaded (one 16-byte load) when the index
+// leaves them.  A lane's panes lie 4*chunk bytes from its neighbour's, so a scalar load per step costs
+// a 32-byte sector from L2 for 4 useful bytes (the L1 left beside the histograms cannot keep them):
+// this turns four such loads into one.  Arrays are 256-byte aligned and padded inside the arena.
+struct Quad {
+    uint4 v;
+    uint32_t base;
+    __device__ __forceinline__ uint32_t at(const uint32_t* a, uint32_t e) {
+        const uint32_t b = e & ~3u;
+        if (b != base) {
+            v = __ldg(reinterpret_cast<const uint4*>(a + b));
+            base = b;
+        }
+        const uint32_t k = e & 3u;
+        return k == 0 ? v.x : (k == 1 ? v.y : (k == 2 ? v.z : v.w));
+    }
+};
+
 // One thread per (key kind, key, chunk of P.slide_chunk windows); a warp's lanes are consecutive
-// chunks of (mostly) the same key, so they step through their windows in lockstep.
+// chunks of (mostly) the same key, so they step through their windows in lockstep.  Count and max of
+// every window come from k_finalize_basic (run before this kernel); of the panes only the list heads
+// are read here.
 __global__ void __launch_bounds__(CellLayout::NT) k_finalize_slide(const __grid_constant__ FinParams P) {
     using L = CellLayout;
-    constexpr uint32_t kAll = 0xFFFFFFFFu;
     __shared__ uint32_t hist[L::WORDS * L::NT];
     if (P.ctl[1]) return;   // overflowed run log: the host reports the error
     const uint32_t tid = threadIdx.x;
@@ -62,40 +81,40 @@ __global__ void __launch_bounds__(CellLayout::NT) k_finalize_slide(const __grid_
     const uint32_t j0 = live ? (idx - key * chunks_per_key) * C : 0;
     const uint32_t j1 = live ? min(P.n_windows, j0 + C) : 0;
     const uint32_t prow = key * P.n_panes;          // first pane cell of the key
-    uint32_t count = 0, vub = 0;                    // samples in the window; upper bound of its values
-    bool bad = false;                               // met a value the 104-bin histogram cannot hold
-    // first window of the chunk: count its W panes
-    for (uint32_t d = 0; d < P.W; ++d) {
-        uint32_t at = 0;
-        if (live && j0 < j1) {
-            const uint32_t pc = prow + j0 + d;
-            const uint32_t m = K.mx[pc];
-            count += K.cnt[pc];
-            vub = max(vub, m);
-            bad |= m >= (uint32_t)L::BINS;
-            if (!bad) at = K.head[pc];
+    const uint32_t crow = key * P.n_windows;        // first window cell of the key
+    Quad q_in{make_uint4(0, 0, 0, 0), 0xFFFFFFFFu}, q_out = q_in, q_cnt = q_in, q_max = q_in;
+    // A window whose largest value does not fit the 104-bin histogram goes to the wide list, and so do
+    // the windows after it in this chunk (the histogram stops being maintained).
+    bool bad = false;
+    {   // first window of the chunk: count its W panes
+        const bool on = live && j0 < j1;
+        if (on) bad = q_max.at(K.o_max, crow + j0) >= (uint32_t)L::BINS;
+        for (uint32_t d = 0; d < P.W; ++d) {
+            uint32_t at = 0;
+            if (on && !bad) at = q_in.at(K.head, prow + j0 + d);
+            add_list_sync<L>(base, P, at);
         }
-        add_list_sync<L>(base, P, at);
     }
     for (uint32_t s = 0; s < C; ++s) {              // warp-uniform trip count
         const uint32_t j = j0 + s;
         const bool on = live && j < j1;
+        const uint32_t c = crow + j;
+        uint32_t count = 0, vmax = 0;
+        if (on) {
+            count = q_cnt.at(K.o_count, c);
+            vmax = q_max.at(K.o_max, c);
+        }
         if (s > 0) {                                // slide: pane j-1 leaves, pane j+W-1 enters
             uint32_t out = 0, in = 0;
             if (on) {
-                const uint32_t po = prow + j - 1, pi = prow + j + P.W - 1;
-                const uint32_t m = K.mx[pi];
-                count += K.cnt[pi] - K.cnt[po];
-                vub = max(vub, m);
                 const bool was_bad = bad;
-                bad |= m >= (uint32_t)L::BINS;
-                if (!was_bad) out = K.head[po];     // un-count only what was counted
-                if (!bad) in = K.head[pi];
+                bad |= vmax >= (uint32_t)L::BINS;
+                if (!was_bad) out = q_out.at(K.head, prow + j - 1);     // un-count only what was counted
+                if (!bad) in = q_in.at(K.head, prow + j + P.W - 1);
             }
             add_list_sync<L>(base, P, out, 0xFFFFu);
             add_list_sync<L>(base, P, in);
         }
-        const uint32_t c = key * P.n_windows + j;
         const bool later = on && count > 0 && (bad || count > kSmallMax);
         defer_cell(P, later, count, ks, c);         // the slow kernel counts these windows pane by pane
         if (on && count > 0 && !later) {
@@ -103,7 +122,7 @@ __global__ void __launch_bounds__(CellLayout::NT) k_finalize_slide(const __grid_
                 uint32_t ilo, ihi, vlo, vhi;
                 double wt;
                 pct_ranks(P.q[iq], count, ilo, ihi, wt);
-                select2<L>(base, count, vub, ilo, ihi, vlo, vhi);
+                select2<L>(base, count, vmax, ilo, ihi, vlo, vhi);
                 store_pct(P, K, c, iq, vlo, vhi, wt);
             }
         }
