@@ -111,6 +111,21 @@ class _Series(dict):
         return self._owner.values_of(self._index)
 
 
+def answer_skeleton(raw, spans):
+    """The answer's text with the inside of every ``values`` array cut out: what is left (status,
+    resultType, the label objects, ``"values":[]``) is small and is decoded on the host.
+    ``spans[s]`` = byte index of series s' ``{``, of the ``[`` and ``]`` of its values array
+    (2**64-1 when it has none) and of its ``}``, as ``kgs_matrix_fetch`` reports them."""
+    none = 0xFFFFFFFFFFFFFFFF
+    pieces, at = [], 0
+    for so, vo, vc, sc in np.asarray(spans, dtype=np.uint64).reshape(-1, 4).tolist():
+        if vo != none and vc != none:
+            pieces.append(raw[at:vo + 1])
+            at = vc
+    pieces.append(raw[at:])
+    return b''.join(pieces)
+
+
 class MatrixAnswer(dict):
     """A /query_range answer decoded by ``kgs_matrix_parse`` (GUS:25 ``.json()`` + GUS:47-48,
     GUS:73-74 ``float(val[1])``).  Looks like the reference's decoded JSON; the per-sample numbers
@@ -122,14 +137,7 @@ class MatrixAnswer(dict):
         self._parse()
         _, _, _, spans = engine().matrix_fetch(ts=False, values=False)
         self.spans = spans
-        none = np.uint64(0xFFFFFFFFFFFFFFFF)
-        pieces, at = [], 0
-        for so, vo, vc, sc in spans.tolist():          # cut the inside of every values array out
-            if vo != none and vc != none:
-                pieces.append(self.raw[at:vo + 1])
-                at = vc
-        pieces.append(self.raw[at:])
-        super().__init__(json.loads(b''.join(pieces)))
+        super().__init__(json.loads(answer_skeleton(self.raw, spans)))
         result = self.get('data', {}).get('result', []) if isinstance(self.get('data'), dict) else []
         if len(result) != len(spans):
             raise ValueError('answer is not a Prometheus matrix: %d series objects, %d entries in data.result'

@@ -112,3 +112,45 @@ def test_replay_dir_round_trip(tmp_path, monkeypatch):
     monkeypatch.setenv('KGS_REPLAY_DIR', str(tmp_path))
     gus.set_transport(None)
     assert {k: list(v) for k, v in gus.get_gpu_servers().items()} == g['expect']['get_gpu_servers']['value']
+
+
+def test_answer_skeleton_keeps_everything_but_the_samples():
+    """Host half of MatrixAnswer: the text minus the inside of every values array decodes to the
+    answer with empty ``values`` lists (the byte spans come from the GPU; here from a plain scan)."""
+    import json
+    import numpy as np
+    from kube_gpu_stats_b200 import gpu_util_stats as gus
+    answer = {'status': 'success', 'data': {'resultType': 'matrix', 'result': [
+        {'metric': {'pod_name': 'a]"[', 'kubernetes_io_hostname': 'n1'}, 'values': [[1, '2'], [3, '4.5']]},
+        {'metric': {'pod_name': 'b'}, 'values': []},
+        {'metric': {'pod_name': 'c'}},
+        {'values': [[5, '6']], 'metric': {}}]}}
+    for dump in ({}, {'separators': (',', ':')}, {'indent': 1}):
+        raw = json.dumps(answer, **dump).encode()
+        spans, at = [], raw.index(b'"result"')
+        for res in answer['data']['result']:
+            body = json.dumps(res, **dump)
+            if dump.get('indent'):
+                body = body.replace('\n', '\n' + ' ' * 3)      # nested three levels deep
+            so = raw.index(body.encode(), at)
+            sc = so + len(body.encode()) - 1
+            none = 2 ** 64 - 1
+            if 'values' in res:
+                vo = raw.index(b'"values"', so) + raw[raw.index(b'"values"', so):].index(b'[')
+                depth, vc = 0, vo
+                while True:
+                    depth += {ord('['): 1, ord(']'): -1}.get(raw[vc], 0)
+                    if depth == 0:
+                        break
+                    vc += 1
+            else:
+                vo = vc = none
+            spans.append((so, vo, vc, sc))
+            at = sc
+        got = json.loads(gus.answer_skeleton(raw, np.array(spans, dtype=np.uint64)))
+        want = json.loads(raw)
+        for res in want['data']['result']:
+            if 'values' in res:
+                res['values'] = []
+        assert got == want
+
