@@ -1192,6 +1192,8 @@ int kgs_matrix_parse(kgs_handle h, const char* text, uint64_t nbytes, int result
         P.k_first = (uint32_t)k_done;
         P.k_end = (uint32_t)ns;
         launch(h, KGS_K_PARSE, st, [&] { k_mx_emit<<<grid, kMxThreads, 0, st>>>(P); });
+        // a pair that starts in the last bytes of this piece is read on into the next one
+        if (!P.last_piece) KGS_CUDA(h, cudaStreamWaitEvent(st, h->mx_arrived[i + 1], 0));
         if (ns > k_done)
             launch(h, KGS_K_PARSE, st, [&] { k_mx_parse<<<(unsigned)((ns - k_done + 127) / 128), 128, 0, st>>>(P); });
         KGS_CUDA(h, cudaGetLastError());
