@@ -200,8 +200,6 @@ int kgs_fetch_region(kgs_handle h, void* host_dst, size_t nbytes);
 int kgs_segmented_mean_f64(kgs_handle h, const double* values, const uint64_t* offsets,
                            uint64_t n_series, double mul, double div, double* out);
 
-/* ---- measurement ---------------------------------------------------------------------- */
-/* Kernel launches issued by this handle since creation (bench.py's gpu_launches). */
 /* ---- value decode of a Prometheus answer on the GPU ---------------------------------------------
  * Replaces the reference's `requests.get(...).json()` + per-sample `float(val[1])` loops
  * (gpu_util_stats.py:25, :47-48, :73-74) for the bulk of an answer: `text` is the response body of
@@ -210,9 +208,12 @@ int kgs_segmented_mean_f64(kgs_handle h, const double* values, const uint64_t* o
  * [ts,"v"] pair (strings, escapes and nesting handled on the GPU) and convert both numbers to fp64
  * exactly as Python's float() does (correctly rounded, same grammar).  The result stays in device
  * memory as a CSR: values[offsets[s] .. offsets[s+1]) belong to series s, in text order.
- * `text` is a host pointer (pinned memory makes the copy asynchronous and faster), nbytes < 4 GiB.
+ * `text` is a host pointer, nbytes < 4 GiB; it is copied in 32 MB pieces on the copy stream and a
+ * piece is decoded while the next ones are in flight (pinned memory keeps that copy at PCIe speed).
  * Errors: KGS_ERR_PARSE if the text ends inside a string / with open brackets, or a sample is not
- * `[number, "text"]` with text that float() accepts (kgs_last_error names the byte).  Blocking. */
+ * `[number, "text"]` with text that float() accepts (kgs_last_error names the byte); an escape
+ * sequence inside a sample's value string is refused too (Prometheus never writes one).  Blocking;
+ * no copy reads `text` any more when the call returns, also on error. */
 enum { KGS_RESULT_MATRIX = 0, KGS_RESULT_VECTOR = 1 };
 int kgs_matrix_parse(kgs_handle h, const char* text, uint64_t nbytes, int result_type, uint64_t* n_series,
                      uint64_t* n_samples);
@@ -225,6 +226,8 @@ int kgs_matrix_fetch(kgs_handle h, double* ts, double* values, uint64_t* offsets
  * n_series entries.  mul / div as in kgs_segmented_mean_f64.  Blocking. */
 int kgs_matrix_mean(kgs_handle h, double mul, double div, double* out);
 
+/* ---- measurement ---------------------------------------------------------------------- */
+/* Kernel launches issued by this handle since creation (bench.py's gpu_launches). */
 int kgs_launch_count(kgs_handle h, uint64_t* out);
 /* With profiling on, every kernel launch is bracketed by CUDA events on the stream it runs
  * on; kgs_kernel_time returns the accumulated device time and launch count of one kernel
