@@ -18,4 +18,10 @@ Parity status
   tumbling/sliding windows, per-GPU / per-node keys, the (node,pid)->pod join).
   They have no reference counterpart at all; the rules are declared in that
   module's docstring and frozen by ``tests/golden/window_kat_*.json``.
+* ``oracle.prom_answer`` states, one byte at a time, which parts of a Prometheus
+  answer's text are series, value arrays and ``[ts, "v"]`` pairs (what
+  ``kgs_matrix_parse`` reports as offsets and byte spans).  The numbers of an
+  answer are checked against the reference's own calls, ``json.loads`` and
+  ``float()`` (gpu_util_stats.py:25,:48,:74) - for this row the checker is the
+  reference's code itself.
 """

@@ -154,3 +154,51 @@ def test_answer_skeleton_keeps_everything_but_the_samples():
                 res['values'] = []
         assert got == want
 
+
+
+def test_answer_scan_oracle_and_skeleton_on_random_answers():
+    """oracle/prom_answer.py (the structure kgs_matrix_parse reports) against json.loads, and the host
+    half of MatrixAnswer on its spans, for labels full of quotes, backslashes and brackets."""
+    import json
+    import random
+    import numpy as np
+    from kube_gpu_stats_b200 import gpu_util_stats as gus
+    from oracle import prom_answer
+    rng = random.Random(17)
+    alphabet = 'ab\\"[]{},: é\n'
+    for trial in range(200):
+        series = []
+        for _ in range(rng.randint(0, 6)):
+            metric = {''.join(rng.choice(alphabet) for _ in range(rng.randint(0, 9))): ''.join(rng.choice(alphabet) for _ in range(rng.randint(0, 30)))
+                      for _ in range(rng.randint(0, 3))}
+            values = [[1700000000 + j, repr(rng.random() * 100)] for j in range(rng.randint(0, 5))]
+            entry = {'metric': metric, 'values': values}
+            if rng.random() < 0.2:
+                del entry['values']
+            if rng.random() < 0.3:
+                entry = dict(reversed(list(entry.items())))
+            series.append(entry)
+        answer = {'status': 'success', 'data': {'resultType': 'matrix', 'result': series}}
+        dump = rng.choice(({}, {'separators': (',', ':')}, {'indent': 2}, {'ensure_ascii': False}))
+        raw = json.dumps(answer, **dump).encode()
+        pos, offsets, spans = prom_answer.scan_answer(raw)
+        assert len(spans) == len(series) and len(offsets) == len(series) + 1
+        for s, entry in enumerate(series):
+            so, vo, vc, sc = spans[s]
+            assert json.loads(raw[so:sc + 1]) == entry
+            vals = entry.get('values', [])
+            assert offsets[s + 1] - offsets[s] == len(vals)
+            if 'values' in entry:
+                assert json.loads(raw[vo:vc + 1]) == vals
+            else:
+                assert vo == prom_answer.NONE and vc == prom_answer.NONE
+            for k, p in enumerate(pos[offsets[s]:offsets[s + 1]]):
+                assert raw[p:p + 1] == b'[' and json.loads(raw[p:raw.index(b']', p) + 1]) == vals[k]
+        got = json.loads(gus.answer_skeleton(raw, np.array(spans, dtype=np.uint64).reshape(-1, 4)))
+        for entry in series:
+            if 'values' in entry:
+                entry['values'] = []
+        assert got == answer
+    import pytest
+    with pytest.raises(ValueError):
+        prom_answer.scan_answer(b'{"data":{"result":[{"metric":{"a":"b}')
