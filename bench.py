@@ -10,11 +10,14 @@ Workload at N=1: BASELINE.json configs[1] (1k nodes x 8 GPUs x 1 h @ 1 s = 28.8 
 node-sharding of configs[3]) and the step ends with the NCCL all_gather of the per-shard
 result tables.
 
-  value  device-resident throughput: the batch is already in HBM, CUDA events around K steps;
+  value  device-resident throughput: the batch is already in HBM, CUDA events around the K steps
+         (the K-step loop is repeated inside the two events until the timed region is >= 100 ms of
+         device time, so that the clock sampler sees it; ms_per_step = elapsed / (K * repeats));
   e2e    the same job through the public API from pinned HOST columns: chunked
          cudaMemcpyAsync overlapped with the kernels, table build, D2H of every result table;
-  roofline  dominant kernel (k_accum) timed per launch with CUDA events in a separate pass,
-         16 algorithmic bytes per sample, against MEASURED_PEAKS.json hbm_gbs;
+  roofline  every kernel of a step timed per launch with CUDA events in a separate pass; the block
+         names the kernel that takes longest, gives each kernel's own algorithmic bytes and the whole
+         step at 16 algorithmic bytes per sample, all against MEASURED_PEAKS.json hbm_gbs;
   cpu_baseline  the pure-Python oracle (the reference's algorithmic style; the Python-2
          reference itself cannot run) on a bounded slice of the same trace, 1 core.
 
@@ -193,7 +196,7 @@ def run_b200(args):
     n = tr.n
     eng = Engine(local)
     if world > 1:
-        eng.set_packed_exchange(True)    # 12 B/cell on the wire instead of 24
+        eng.set_packed_exchange(True)    # packed tables on the wire (config.exchange_bytes_per_cell)
     # pinned host columns (the e2e leg copies from these)
     host = [eng.pinned(n) for _ in range(4)]
     for dst, src in zip(host, (tr.ts, tr.gpu_gid, tr.pid, tr.util)):
@@ -217,7 +220,7 @@ def run_b200(args):
                 eng.window_stats_device(spec)
                 gather.all_gather()              # rendezvous now: every rank takes the same branch
             eng.sync()
-            exchange = 'copy-engine pushes of the packed 12 B/cell tables into every peer over NVLink (symmetric memory) + signal barrier, overlapped with the next step'
+            exchange = 'copy-engine pushes of the packed tables into every peer over NVLink (symmetric memory) + signal barrier, overlapped with the next step'
         except Exception as exc:                 # noqa: BLE001
             sys.stderr.write('rank %d: peer exchange not available (%s); using the NCCL all_gather\n' % (rank, exc))
             ok = torch.tensor([0], device='cuda')
@@ -226,7 +229,7 @@ def run_b200(args):
         dist.all_reduce(ok, op=dist.ReduceOp.MIN)
         if int(ok) == 0:
             gather = sharding.TableGather(eng, KINDS, world)
-            exchange = 'NCCL all_gather of the packed 12 B/cell exchange tables, overlapped with the next step'
+            exchange = 'NCCL all_gather of the packed exchange tables, overlapped with the next step'
 
     def step():
         # N > 1: the all_gather of step i's tables runs on a side stream while step i+1 computes
@@ -252,18 +255,32 @@ def run_b200(args):
         sampler = ClockSampler(local)
         if rank == 0:
             sampler.start()
+        # how often the K-step loop has to run for >= 100 ms of device time (same count on every rank)
+        p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        p0.record(stream)
+        for _ in range(args.steps):
+            step()
+        if gather is not None:
+            gather.join(stream)
+        p1.record(stream)
+        barrier()
+        probe_ms = torch.tensor([p0.elapsed_time(p1)], dtype=torch.float64, device='cuda')
+        if world > 1:
+            dist.all_reduce(probe_ms, op=dist.ReduceOp.MIN)
+        repeats = int(max(1, min(10000, np.ceil(args.min_timed_ms / max(float(probe_ms), 1e-3)))))
         launches0 = eng.launch_count()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         barrier()
         e0.record(stream)
-        for _ in range(args.steps):
-            step()
+        for _ in range(repeats):
+            for _ in range(args.steps):
+                step()
         if gather is not None:
             gather.join(stream)          # the last collectives belong to the timed region
         e1.record(stream)
         barrier()
-        ms_total = e0.elapsed_time(e1)
-        launches = eng.launch_count() - launches0
+        ms_total = e0.elapsed_time(e1) / repeats       # per K steps
+        launches = (eng.launch_count() - launches0) // repeats
 
         # ---- e2e: host columns -> result tables on the host, every step -----------------
         n_chunks = 8
@@ -291,8 +308,23 @@ def run_b200(args):
         barrier()
         e2e_s = time.perf_counter() - t0
         d2h_bytes = eng.result_region()[2]
+        xbytes_per_rank = eng.exchange_region()[1] if world > 1 else 0
         if rank == 0:
             clocks = sampler.stop()
+
+        # ---- copy-only leg: the same pinned chunks through cudaMemcpyAsync, no kernels ------------
+        # (what the host side of this box can deliver to N GPUs at once; explains e2e at N > 1)
+        def copy_only():
+            for a, b in zip(cuts[:-1], cuts[1:]):
+                eng.ingest(host[0][a:b], host[1][a:b], host[2][a:b], host[3][a:b])
+            eng.sync()
+        copy_only()
+        barrier()
+        tc = time.perf_counter()
+        for _ in range(3):
+            copy_only()
+        barrier()
+        copy_s = (time.perf_counter() - tc) / 3
 
         # ---- per-kernel pass (events around every launch; not the throughput pass) -------
         eng.ingest(*host)
@@ -306,25 +338,50 @@ def run_b200(args):
         ktimes = eng.kernel_times()
         eng.set_profiling(False)
 
-    t = torch.tensor([ms_total, e2e_s], dtype=torch.float64, device='cuda')
+    t = torch.tensor([ms_total, e2e_s, copy_s], dtype=torch.float64, device='cuda')
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_total, e2e_s = float(t[0]), float(t[1])
+    ms_total, e2e_s, copy_s = float(t[0]), float(t[1]), float(t[2])
     total_samples = n * world
 
     if rank == 0:
         peak, peak_src = measured_peak_gbs()
-        acc_ms, acc_n = ktimes['accum']
-        acc_avg_ms = acc_ms / max(1, acc_n)
-        achieved = ALGO_BYTES_PER_SAMPLE * n / (acc_avg_ms * 1e-3) / 1e9
-        step_kernel_ms = sum(v[0] for v in ktimes.values()) / prof_steps
-        traffic = None
-        tpath = os.path.join(ROOT, 'profiles', 'accum_traffic.json')
-        if os.path.exists(tpath):
+        # every kernel of a step: measured time, its own algorithmic bytes, and the DRAM
+        # traffic of one launch from the committed ncu capture (profiles/*_traffic.json) where there is one
+        n_q = len(QS)
+        cells = {'pod': tr.n_pods * N_WINDOWS, 'gpu': tr.n_gpus * N_WINDOWS, 'node': tr.n_nodes * N_WINDOWS}
+        n_cells = sum(cells.values())
+        cell_io = 20 + 28 + 8 * n_q                       # accumulators in, count/sum/max/mean/pct out
+        algo = {
+            'accum': ALGO_BYTES_PER_SAMPLE * n,                                            # the four sample columns, once
+            'finalize_groups': n + cells['gpu'] * 16 + n_cells * cell_io,                  # value log once, one run descriptor per gpu cell
+            'finalize_cells': n_cells * 1,                                                 # the done flags (cells it has to finish itself: data dependent)
+            'finalize_wide': 16,
+        }
+        traffic_file = {'accum': 'accum_traffic.json', 'finalize_groups': 'finalize_groups_traffic.json',
+                        'finalize_cells': 'finalize_traffic.json'}
+
+        def traffic_of(name):
+            path = os.path.join(ROOT, 'profiles', traffic_file.get(name, '-'))
             try:
-                traffic = json.load(open(tpath)).get('dram_bytes_per_launch')
+                return json.load(open(path)).get('dram_bytes_per_launch')
             except Exception:
-                traffic = None
+                return None
+        kernels = {}
+        for name, (ms, cnt) in ktimes.items():
+            if not cnt:
+                continue
+            avg = ms / cnt
+            ent = {'avg_launch_ms': avg, 'launches_per_step': cnt / prof_steps, 'ms_per_step': ms / prof_steps,
+                   'algorithmic_bytes_per_launch': algo.get(name), 'traffic': traffic_of(name)}
+            if algo.get(name):
+                ent['achieved'] = algo[name] / (avg * 1e-3) / 1e9
+                ent['frac'] = ent['achieved'] / peak
+            kernels[name] = ent
+        step_kernel_ms = sum(e['ms_per_step'] for e in kernels.values())
+        top = max(kernels, key=lambda k: kernels[k]['ms_per_step'])
+        step_ms = ms_total / args.steps
+        step_achieved = ALGO_BYTES_PER_SAMPLE * n / (step_ms * 1e-3) / 1e9
         # bounded CPU baseline on the same trace
         cpu = None
         crossover = None
@@ -354,18 +411,31 @@ def run_b200(args):
             'vs_baseline': None, 'dtype': 'u8 in / u64 + f64 out', 'data': 'synthetic',
             'config': {'workload': workload_name(n_nodes), 'samples_per_gpu': n, 'bytes_per_sample': 16,
                        'l2': 'input per step is %.0f MB, larger than the 126 MB L2 (no flush needed)' % (n * 16 / 1e6),
-                       'parallelism': 'node-sharded x%d' % world, 'collective': exchange},
+                       'parallelism': 'node-sharded x%d' % world, 'collective': exchange,
+                       'exchange_bytes_per_rank_per_step': xbytes_per_rank,
+                       'exchange_bytes_per_cell': (xbytes_per_rank / n_cells) if world > 1 else None,
+                       'timed_repeats': repeats, 'timed_region_ms': ms_total * repeats},
             'clocks': clocks,
             'e2e': {'value': total_samples * e2e_steps / e2e_s, 'unit': UNIT, 'h2d_bytes_per_step': h2d_bytes,
                     'd2h_bytes_per_step': d2h_bytes, 'steps': e2e_steps, 'ms_per_step': 1e3 * e2e_s / e2e_steps,
-                    'timing': 'host wall clock around blocking API calls, sync both sides'},
+                    'timing': 'host wall clock around blocking API calls, sync both sides',
+                    'copy_only': {'ms_per_step': 1e3 * copy_s, 'aggregate_h2d_gbs': world * n * 16 / copy_s / 1e9,
+                                  'note': 'the same 8 pinned chunks per rank through cudaMemcpyAsync with no kernels: '
+                                          'what the host side delivers to %d GPU(s) at once' % world}},
             'gpu_launches': int(launches),
-            'roofline': {'bound': 'hbm', 'kernel': 'k_accum<pct>', 'achieved': achieved, 'peak': peak,
-                         'unit': 'GB/s', 'frac': achieved / peak, 'traffic': traffic, 'peak_source': peak_src,
-                         'frac_of_nominal_8TBs': achieved / 8000.0, 'avg_launch_ms': acc_avg_ms,
-                         'algorithmic_bytes_per_launch': ALGO_BYTES_PER_SAMPLE * n,
-                         'step_kernel_ms': {k: v[0] / prof_steps for k, v in ktimes.items() if v[1]},
-                         'accum_share_of_step_kernels': (acc_ms / prof_steps) / step_kernel_ms if step_kernel_ms else None},
+            'roofline': {'bound': 'hbm', 'kernel': 'k_' + top, 'achieved': kernels[top].get('achieved'), 'peak': peak,
+                         'unit': 'GB/s', 'frac': kernels[top].get('frac'), 'traffic': kernels[top]['traffic'],
+                         'peak_source': peak_src, 'avg_launch_ms': kernels[top]['avg_launch_ms'],
+                         'algorithmic_bytes_per_launch': kernels[top]['algorithmic_bytes_per_launch'],
+                         'frac_of_nominal_8TBs': (kernels[top].get('achieved') or 0) / 8000.0,
+                         'step': {'algorithmic_bytes': ALGO_BYTES_PER_SAMPLE * n, 'ms': step_ms, 'achieved': step_achieved,
+                                  'frac': step_achieved / peak, 'frac_of_nominal_8TBs': step_achieved / 8000.0,
+                                  'note': '16 B per sample over the driver-timed step (all kernels, launch gaps%s)'
+                                          % (', table exchange' if world > 1 else '')},
+                         'kernels': kernels,
+                         'kernel_ms_sum_per_step': step_kernel_ms,
+                         'note': 'per-kernel times from a separate pass with CUDA events around every launch on the '
+                                 'launching stream; kernel = the one with the largest share of a step'},
             'cpu_baseline': cpu,
             'crossover': crossover,
             'decode': decode,
@@ -387,6 +457,7 @@ def main():
     ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
     ap.add_argument('--nodes', type=int, default=1000, help='nodes per GPU shard (configs[1] = 1000)')
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--min-timed-ms', type=float, default=100.0, help='repeat the K-step loop until the timed region is this long')
     args = ap.parse_args()
     if args.impl == 'reference':
         return run_reference(args)

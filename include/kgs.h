@@ -134,7 +134,11 @@ int kgs_probe(kgs_handle h, uint32_t gpus_per_node, uint32_t* out_pod_id);
  * cudaStream_t, NULL = default stream) and returns without waiting; it performs no cudaMalloc /
  * cudaFree.  The first call on each device resolves the table's device address - make it before
  * any stream capture.  All calls on a device share the one table and rebuild it from empty, so
- * calls whose kernels may overlap on the same GPU (two streams, two threads) race: serialise them. */
+ * calls whose kernels may overlap on the same GPU (two streams, two threads) race: serialise them.
+ * `stream` must belong to `device`; the caller's current device is the same after the call as before.
+ * The keys are read on the GPU only, so the reserved key 0xFFFFFFFFFFFFFFFF (the free-slot marker,
+ * which kgs_build_join refuses) cannot be refused here: a pair with that key is left out.  The table's
+ * address is looked up once per device and process; it does not survive a cudaDeviceReset. */
 #define KGS_NOALLOC_MAX_PAIRS 65536u
 int kgs_join_probe_noalloc(int device, const uint64_t* d_keys, const uint32_t* d_pod_ids, uint64_t m,
                            const uint32_t* d_gpu_gid, const uint32_t* d_pid, uint64_t n,
@@ -158,6 +162,15 @@ int kgs_window_stats(kgs_handle h, const kgs_window_spec* spec);
  * stream): it is the initial capacity, and every slab is sized for the worst case of one run per
  * sample.  A job that still overflows the pool fails at fetch time with KGS_ERR_CAPACITY. */
 int kgs_set_run_log_capacity(kgs_handle h, uint64_t entries);
+/* What the kernels of the open (or finalized) job met, for tests and tuning; blocking.
+ * KGS_JC_POOL_ENTRIES   run-log entries taken from the shared overflow pool (0 in collector order);
+ * KGS_JC_CACHE_CTAS     accumulate CTAs that folded runs in their shared-memory accumulator cache
+ *                       first (input far from collector order: the flat random stream of configs[2]);
+ * KGS_JC_BIG_CELLS      window cells of the last finalize counted by a whole warp (many samples);
+ * KGS_JC_WIDE_CELLS     window cells of the last finalize with a value >= 104 (or the 16-bit metric).
+ * No reference counterpart (the reference has one code path). */
+enum { KGS_JC_POOL_ENTRIES = 0, KGS_JC_CACHE_CTAS = 1, KGS_JC_BIG_CELLS = 2, KGS_JC_WIDE_CELLS = 3, KGS_N_JOB_COUNTERS = 4 };
+int kgs_job_counter(kgs_handle h, int which, uint64_t* out);
 /* Copy one key kind's result table to host arrays of n_keys * n_windows entries, cell index
  * key * n_windows + window (pct: n_q rows of that length).  Any pointer may be NULL. Blocking. */
 int kgs_fetch_stats(kgs_handle h, int key_kind, uint32_t* count, uint64_t* sum, uint32_t* max,
@@ -233,7 +246,7 @@ int kgs_launch_count(kgs_handle h, uint64_t* out);
  * on; kgs_kernel_time returns the accumulated device time and launch count of one kernel
  * (ids: KGS_K_*), kgs_reset_kernel_times clears them. */
 enum { KGS_K_BUILD = 0, KGS_K_BUILD_FIN = 1, KGS_K_PROBE = 2, KGS_K_ACCUM = 3, KGS_K_FINALIZE = 4,
-       KGS_K_FINALIZE_BIG = 5, KGS_K_SEGMEAN = 6, KGS_K_CLEAR = 7, KGS_K_FINALIZE_WIDE = 8, KGS_K_FINALIZE_BASIC = 9, KGS_K_SORT = 10, KGS_K_PARSE = 11, KGS_N_KERNELS = 12 };
+       KGS_K_FINALIZE_BIG = 5, KGS_K_SEGMEAN = 6, KGS_K_CLEAR = 7, KGS_K_FINALIZE_WIDE = 8, KGS_K_FINALIZE_BASIC = 9, KGS_K_SORT = 10, KGS_K_PARSE = 11, KGS_K_FINALIZE_GROUPS = 12, KGS_N_KERNELS = 13 };
 int kgs_set_profiling(kgs_handle h, int on);
 int kgs_kernel_time(kgs_handle h, int kernel_id, double* total_ms, uint64_t* launches);
 int kgs_reset_kernel_times(kgs_handle h);

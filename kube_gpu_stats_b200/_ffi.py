@@ -18,9 +18,10 @@ METRIC_SM, METRIC_MEM, METRIC_FB = 0, 1, 2
 POD_NONE = 0xFFFFFFFF
 MAX_Q = 8
 NOALLOC_MAX_PAIRS = 65536
-(K_BUILD, K_BUILD_FIN, K_PROBE, K_ACCUM, K_FINALIZE, K_FINALIZE_BIG, K_SEGMEAN, K_CLEAR, K_FINALIZE_WIDE, K_FINALIZE_BASIC, K_SORT, K_PARSE) = range(12)
+JC_POOL_ENTRIES, JC_CACHE_CTAS, JC_BIG_CELLS, JC_WIDE_CELLS = range(4)
+(K_BUILD, K_BUILD_FIN, K_PROBE, K_ACCUM, K_FINALIZE, K_FINALIZE_BIG, K_SEGMEAN, K_CLEAR, K_FINALIZE_WIDE, K_FINALIZE_BASIC, K_SORT, K_PARSE, K_FINALIZE_GROUPS) = range(13)
 KERNEL_NAMES = ['join_build', 'join_resolve', 'join_probe', 'accum', 'finalize_cells', 'finalize_big',
-                'segmean', 'join_clear', 'finalize_wide', 'finalize_basic', 'reorder', 'parse']
+                'segmean', 'join_clear', 'finalize_wide', 'finalize_basic', 'reorder', 'parse', 'finalize_groups']
 
 
 class WindowSpec(C.Structure):
@@ -67,6 +68,7 @@ def load(path=LIB_PATH):
         'kgs_stats_finalize': [H],
         'kgs_window_stats': [H, C.POINTER(WindowSpec)],
         'kgs_set_run_log_capacity': [H, C.c_uint64],
+        'kgs_job_counter': [H, C.c_int, u64p],
         'kgs_fetch_stats': [H, C.c_int, vp, vp, vp, vp, vp],
         'kgs_result_device_ptr': [H, C.c_int, C.c_int, C.POINTER(vp), C.POINTER(C.c_size_t)],
         'kgs_result_region': [H, C.POINTER(vp), C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)],

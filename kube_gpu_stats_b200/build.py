@@ -7,7 +7,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, 'csrc')
 LIB = os.path.join(HERE, 'libkgs.so')
 SOURCES = ['kgs.cu']
-HEADERS = ['common.cuh', 'join.cuh', 'accum.cuh', 'finalize.cuh', 'finalize_slide.cuh', 'segmean.cuh', 'sort.cuh', 'promjson.cuh', 'strtod.cuh', 'pow5_table.inc', 'noalloc.cuh']
+HEADERS = sorted(f for f in os.listdir(CSRC) if f.endswith(('.cuh', '.inc', '.h')))
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3', '-std=c++17',
               '-shared', '-Xcompiler', '-fPIC']
 

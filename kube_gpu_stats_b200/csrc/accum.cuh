@@ -65,7 +65,7 @@ struct AccumParams {
     uint32_t log_base;             // this launch's private run-log slab: warp w owns
     uint32_t log_per_warp;         //   [log_base + w*log_per_warp, +log_per_warp)
     uint32_t pool_end;             // shared overflow pool = entries [0, pool_end), cursor ctl[0]
-    uint32_t* ctl;                 // ctl[0] pool cursor, ctl[1] overflow flag
+    uint32_t* ctl;                 // ctl[0] pool cursor, ctl[1] overflow flag, ctl[4] CTAs that used the accumulator cache
     uint32_t agg_on;               // every cell index < 2^30: the per-CTA accumulator cache may be used
     uint32_t dense_ok;             // step >= 8 and no sampled windows: the dense-tile shortcut applies
 };
@@ -556,6 +556,7 @@ __global__ void __launch_bounds__(kAccumWarps * 32) k_accum(const __grid_constan
     flush_queue<PCT>(P, agg, lc, Q, queued, nk);
     if (P.agg_on) {   // write the CTA's accumulator cache out: one RED per occupied slot and statistic
         __syncthreads();
+        bool used = false;
         for (uint32_t i = threadIdx.x; i < kAggSlots; i += blockDim.x) {
             const uint32_t tag = table.tag[i];
             if (tag) {
@@ -563,8 +564,10 @@ __global__ void __launch_bounds__(kAccumWarps * 32) k_accum(const __grid_constan
                 atomicAdd(P.cnt[kind] + cell, table.cnt[i]);
                 atomicAdd(P.sum[kind] + cell, table.sum[i]);
                 atomicMax(P.mx[kind] + cell, table.mx[i]);
+                used = true;
             }
         }
+        if (__syncthreads_or(used) && threadIdx.x == 0) atomicAdd(P.ctl + 4, 1u);   // job counter: CTAs that used the cache
     }
 }
 

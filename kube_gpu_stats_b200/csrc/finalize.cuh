@@ -6,11 +6,11 @@
 // selection: for the u8 metrics a count per byte value is a complete one-digit radix select.
 // One THREAD owns one window cell and counts into a PRIVATE histogram in shared memory whose
 // layout keeps thread t on bank t%32 (conflict free, no atomics).  Three kernels:
-//   k_finalize_cells every cell: count/sum/max/mean; percentiles when the cell has <= 65 535
-//                    samples and max < 104 (u16 bins, 208 B per thread, 128 threads per CTA, 8 CTAs/SM);
-//                    other non-empty cells are appended to the wide list;
-//   k_finalize_rare  one launch for the two rare lists: values up to 255 with up to 65 535 samples per
-//                    cell (64 threads per CTA, u16 bins), and anything larger (a warp per cell, u32 bins).
+//   k_finalize_cells every cell k_finalize_groups (finalize_groups.cuh) has not finished: count/sum/max/mean;
+//                    percentiles when the cell has few samples (<= thread_cell_max) and max < 104 (u16 bins,
+//                    208 B per thread, 128 threads per CTA, 8 CTAs/SM); other non-empty cells go on the rare list;
+//   k_finalize_rare  one launch for the two parts of the rare list: values up to 255 with few samples per
+//                    cell (64 threads per CTA, u16 bins), and cells with many samples (a warp per cell, u32 bins).
 #pragma once
 #include "common.cuh"
 
@@ -51,11 +51,19 @@ struct FinParams {
     double q[8];
     const uint8_t* vals;
     const uint4* desc;
-    uint32_t* wide_list;                 // pairs (kind slot, cell) left to k_finalize_rare (wide part)
-    uint32_t* big_list;                  // pairs left to k_finalize_rare (big part)
-    uint32_t* ctl;                       // ctl[2] = big_list length, ctl[3] = wide_list length
-    uint32_t rare_wide_ctas;             // k_finalize_rare: CTAs working on the wide list (the rest: big list)
-    uint32_t wide_cap, big_cap;
+    uint32_t* rare_list;                 // pairs (kind slot, cell) left to k_finalize_rare: the wide cells fill it from
+                                         // the front, the big cells from the back; rare_cap = number of window cells,
+                                         // so it cannot overflow
+    uint32_t* ctl;                       // ctl[2] = big cells listed, ctl[3] = wide cells listed
+    uint32_t rare_wide_ctas;             // k_finalize_rare: CTAs working on the wide cells (the rest: big cells)
+    uint32_t rare_cap;
+    uint32_t thread_cell_max;            // cells above this many samples are counted by a whole warp (big part)
+    // k_finalize_groups (finalize_groups.cuh)
+    uint8_t* done;                       // per global window cell: == done_gen when k_finalize_groups finished the cell
+    uint32_t done_gen;
+    int g_gpu, g_pod, g_node;            // kind slots of the gpu / pod / node tables, -1 = not part of the job
+    uint32_t g_gs_log2;                  // lanes per (node, window) group = 1 << g_gs_log2 >= gpus per node
+    uint32_t g_gpn, g_nodes;             // gpus per node; nodes covered by the groups
     uint32_t packed_sum64;               // packed sums are u64 (a cell's sum may not fit 32 bits)
     uint32_t slide_chunk;                // windows per thread of k_finalize_slide
     uint32_t u16;                        // 16-bit metric: the value log holds 2 B/sample, cells go to k_finalize_u16
@@ -301,52 +309,49 @@ __device__ __forceinline__ const FinKind& kind_of_cell(const FinParams& P, uint3
     return P.kind[ks];
 }
 
-// Cells the private u16 histograms cannot take go on one of two lists (one atomic per warp and
-// list): above 65 535 samples -> big list (u32 bins, a warp per cell); otherwise (a value >= 104,
-// or a 16-bit metric) -> wide list.  The two lists are worked off by ONE launch (k_finalize_rare).
-__device__ __forceinline__ void defer_cell(const FinParams& P, bool later, unsigned long long count, uint32_t ks, uint32_t c) {
+// Cells the private u16 histograms should not take go on the rare list (one atomic per warp and
+// part): `big` cells (many samples: u32 bins, a whole warp per cell) are appended from the back,
+// `wide` cells (a value >= 104, or the 16-bit metric) from the front.  A cell is listed at most once
+// and the list has one entry per window cell, so the two parts cannot meet.  Both parts are worked
+// off by ONE launch (k_finalize_rare).
+__device__ __forceinline__ void defer_cell(const FinParams& P, bool wide, bool big, uint32_t ks, uint32_t c) {
     constexpr uint32_t kAll = 0xFFFFFFFFu;
-    const bool big = later && !P.u16 && count > kSmallMax;
-    const bool wide = later && !big;
     const uint32_t wide_mask = __ballot_sync(kAll, wide), big_mask = __ballot_sync(kAll, big);
     const uint32_t below = (1u << lane_id()) - 1u;
     if (wide_mask) {
         uint32_t at = 0;
         if (lane_id() == 0) at = atomicAdd(P.ctl + 3, (uint32_t)__popc(wide_mask));
         at = __shfl_sync(kAll, at, 0) + __popc(wide_mask & below);
-        if (wide && at < P.wide_cap) {
-            P.wide_list[2 * at] = ks;
-            P.wide_list[2 * at + 1] = c;
+        if (wide) {
+            P.rare_list[2 * (size_t)at] = ks;
+            P.rare_list[2 * (size_t)at + 1] = c;
         }
     }
     if (big_mask) {
         uint32_t at = 0;
         if (lane_id() == 0) at = atomicAdd(P.ctl + 2, (uint32_t)__popc(big_mask));
-        at = __shfl_sync(kAll, at, 0) + __popc(big_mask & below);
-        if (big && at < P.big_cap) {
-            P.big_list[2 * at] = ks;
-            P.big_list[2 * at + 1] = c;
+        at = P.rare_cap - 1u - (__shfl_sync(kAll, at, 0) + __popc(big_mask & below));
+        if (big) {
+            P.rare_list[2 * (size_t)at] = ks;
+            P.rare_list[2 * (size_t)at + 1] = c;
         }
     }
 }
 
-// Every window cell: count / sum / max / mean, and the percentiles of cells with up to 65 535
-// samples whose values stay below 104.  Cells are visited from the END of the index space
-// (node cells, the heaviest, are scheduled first).  Other non-empty cells go to the wide list.
+// Every window cell that k_finalize_groups has not finished: count / sum / max / mean, and the
+// percentiles of cells with up to thread_cell_max samples whose values stay below 104.  Cells are
+// visited from the END of the index space (node cells, the heaviest, are scheduled first).  Cells
+// with more samples go to the big part of the rare list (a warp per cell), other non-empty cells
+// (a value >= 104, the 16-bit metric) to its wide part.
 __global__ void __launch_bounds__(CellLayout::NT, 8) k_finalize_cells(const __grid_constant__ FinParams P) {
     using L = CellLayout;
     __shared__ uint32_t hist[L::WORDS * L::NT];
     const uint32_t tid = threadIdx.x;
-    if (P.n_q) {   // clear the CTA's histograms together (16 STS.128 per thread)
-        uint4* z = reinterpret_cast<uint4*>(hist);
-#pragma unroll
-        for (int i = 0; i < L::WORDS / 4; ++i) z[i * L::NT + tid] = make_uint4(0, 0, 0, 0);
-        __syncthreads();
-    }
     const uint32_t base = (uint32_t)__cvta_generic_to_shared(hist) + tid * 4;
     const uint32_t idx = blockIdx.x * L::NT + tid;
-    const bool live = idx < P.total_cells;
+    bool live = idx < P.total_cells;
     const uint32_t gc = live ? P.total_cells - 1 - idx : 0;
+    if (live && P.done && P.done[gc] == (uint8_t)P.done_gen) live = false;   // finished by k_finalize_groups
     uint32_t ks = 0, c = 0, pc0 = 0, vmax = 0;
     unsigned long long count = 0;
     if (live) {
@@ -366,15 +371,17 @@ __global__ void __launch_bounds__(CellLayout::NT, 8) k_finalize_cells(const __gr
     // a run log that overflowed holds incomplete lists: the host reports the error, skip selection
     if (P.n_q == 0 || P.ctl[1]) return;
     const FinKind& K = P.kind[ks];
-    const bool fast = live && count > 0 && count <= kSmallMax && vmax < (uint32_t)L::BINS && !P.u16;
-    const bool later = live && count > 0 && !fast;
-    defer_cell(P, later, count, ks, c);
+    const bool big = live && !P.u16 && count > P.thread_cell_max;
+    const bool fast = live && count > 0 && !big && vmax < (uint32_t)L::BINS && !P.u16;
+    const bool wide = live && count > 0 && !fast && !big;
+    defer_cell(P, wide, big, ks, c);
     // Twin cells.  With one process per GPU a (gpu, window) cell and its (pod, window) cell usually
     // consist of the very same single run, and k_accum wrote that run's descriptors side by side
     // (pod at index i, gpu at i + 1).  The pod cell's thread then selects once and stores the
     // percentiles in both tables; the gpu cell's thread, seeing the mirror-image condition on the
     // same immutable lists, does nothing.  Both sides test "my list is exactly this run" AND "the
-    // sibling's list is exactly the sibling descriptor", so they always agree.
+    // sibling's list is exactly the sibling descriptor", so they always agree.  (A pair that
+    // k_finalize_groups has finished never gets here: it marks both cells or neither.)
     bool work = fast;
     uint32_t twin_cell = kInvalid;
     if (fast && P.twin_pod >= 0) {
@@ -393,6 +400,13 @@ __global__ void __launch_bounds__(CellLayout::NT, 8) k_finalize_cells(const __gr
                 work = false;                                  // the pod cell's thread stores my percentiles
         }
     }
+    if (!__syncthreads_or(work)) return;   // nothing to count in this CTA (the usual case after k_finalize_groups)
+    {   // clear the CTA's histograms together (STS.128)
+        uint4* z = reinterpret_cast<uint4*>(hist);
+#pragma unroll
+        for (int i = 0; i < L::WORDS / 4; ++i) z[i * L::NT + tid] = make_uint4(0, 0, 0, 0);
+        __syncthreads();
+    }
     add_cell<L>(base, P, K, pc0, work);   // warp-synchronous: every lane takes part
     if (work) select_store<L>(base, P, K, c, (uint32_t)count, vmax, twin_cell);
 }
@@ -403,7 +417,7 @@ __device__ __forceinline__ void finalize_wide_part(const FinParams& P, uint32_t 
     using L = WideLayout;
     __shared__ uint32_t hist[L::WORDS * L::NT];
     const uint32_t tid = threadIdx.x;
-    const uint32_t n_wide = P.ctl[1] ? 0u : min(P.ctl[3], P.wide_cap);
+    const uint32_t n_wide = P.ctl[1] ? 0u : min(P.ctl[3], P.rare_cap);
     if (cta * L::NT >= n_wide) return;
     const uint32_t base = (uint32_t)__cvta_generic_to_shared(hist) + tid * 4;
     for (uint32_t a = base; a < base + L::WORDS * L::ROW; a += L::ROW) sts_u32(a, 0);
@@ -413,8 +427,8 @@ __device__ __forceinline__ void finalize_wide_part(const FinParams& P, uint32_t 
         uint32_t ks = 0, c = 0, vmax = 0, pc0 = 0;
         unsigned long long count = 0;
         if (valid) {
-            ks = P.wide_list[2 * it];
-            c = P.wide_list[2 * it + 1];
+            ks = P.rare_list[2 * (size_t)it];
+            c = P.rare_list[2 * (size_t)it + 1];
             count = P.kind[ks].o_count[c];
         }
         const FinKind& K = P.kind[ks];
@@ -430,18 +444,21 @@ __device__ __forceinline__ void finalize_wide_part(const FinParams& P, uint32_t 
     }
 }
 
-// Cells above kSmallMax samples: one warp per cell, u32 bins in shared memory.  Every lane reads
-// the same descriptor, the whole warp counts each run's bytes.  The CTAs behind the wide part.
+// Cells with many samples (above thread_cell_max): one warp per cell, u32 bins in shared memory.
+// Every lane reads the same descriptor, the whole warp counts each run's bytes; the ranks are then
+// located with a warp scan over the 256 bins (lane l owns bins 8l .. 8l+7).  The CTAs behind the wide part.
 __device__ __forceinline__ void finalize_big_part(const FinParams& P, uint32_t cta, uint32_t n_ctas) {
+    constexpr uint32_t kAll = 0xFFFFFFFFu;
     constexpr uint32_t kWarps = WideLayout::NT / 32;
     __shared__ uint32_t hist_all[kWarps][256];
     const uint32_t lane = lane_id(), wib = threadIdx.x >> 5;
     uint32_t* hist = hist_all[wib];
-    const uint32_t n_big = P.ctl[1] ? 0u : min(P.ctl[2], P.big_cap);
+    const uint32_t n_big = P.ctl[1] ? 0u : min(P.ctl[2], P.rare_cap);
     const uint32_t warps = n_ctas * kWarps;
     for (uint32_t it = cta * kWarps + wib; it < n_big; it += warps) {
-        const FinKind& K = P.kind[P.big_list[2 * it]];
-        const uint32_t c = P.big_list[2 * it + 1];
+        const size_t e = (size_t)(P.rare_cap - 1u - it);
+        const FinKind& K = P.kind[P.rare_list[2 * e]];
+        const uint32_t c = P.rare_list[2 * e + 1];
         const uint32_t key = c / P.n_windows, j = c - key * P.n_windows;
         const uint32_t pc0 = key * P.n_panes + j;
         for (uint32_t b = lane; b < 256; b += 32) hist[b] = 0;
@@ -455,22 +472,38 @@ __device__ __forceinline__ void finalize_big_part(const FinParams& P, uint32_t c
             }
         }
         __syncwarp();
-        const unsigned long long count = K.o_count[c];
-        if (lane == 0) {
-            for (uint32_t iq = 0; iq < P.n_q; ++iq) {
-                // a percentile job holds fewer than 2^32 samples, so u32 ranks suffice
-                uint32_t ilo, ihi;
-                double w;
-                pct_ranks(P.q[iq], (uint32_t)count, ilo, ihi, w);
-                uint32_t cum = 0, vlo = 0, vhi = 0;
-                for (uint32_t b = 0; b < 256; ++b) {
-                    const uint32_t cb = hist[b];
-                    if (ilo - cum < cb) vlo = b;
-                    if (ihi - cum < cb) vhi = b;
-                    cum += cb;
+        const uint32_t count = K.o_count[c];     // a percentile job holds fewer than 2^32 samples, so u32 ranks suffice
+        uint32_t mine[8], incl = 0;
+#pragma unroll
+        for (int b = 0; b < 8; ++b) {
+            mine[b] = hist[8 * lane + b];
+            incl += mine[b];
+        }
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t o = __shfl_up_sync(kAll, incl, d);
+            if (lane >= (uint32_t)d) incl += o;
+        }
+        const uint32_t excl = incl - (mine[0] + mine[1] + mine[2] + mine[3] + mine[4] + mine[5] + mine[6] + mine[7]);
+        auto value_of_rank = [&](uint32_t r) {   // every lane gets the answer
+            uint32_t v = 0;
+            if (excl <= r && r < incl) {
+                uint32_t cum = excl;
+#pragma unroll
+                for (int b = 0; b < 8; ++b) {
+                    if (r >= cum && r - cum < mine[b]) v = 8 * lane + b;
+                    cum += mine[b];
                 }
-                store_pct(P, K, c, iq, vlo, vhi, w);
             }
+            const uint32_t owner = __ballot_sync(kAll, excl <= r && r < incl);
+            return __shfl_sync(kAll, v, owner ? __ffs(owner) - 1 : 0);
+        };
+        for (uint32_t iq = 0; iq < P.n_q; ++iq) {
+            uint32_t ilo, ihi;
+            double w;
+            pct_ranks(P.q[iq], count, ilo, ihi, w);
+            const uint32_t vlo = value_of_rank(ilo), vhi = value_of_rank(ihi);
+            if (lane == 0) store_pct(P, K, c, iq, vlo, vhi, w);
         }
         __syncwarp();
     }
@@ -492,11 +525,11 @@ __global__ void __launch_bounds__(128) k_finalize_u16(const __grid_constant__ Fi
     const uint32_t lane = lane_id(), wib = threadIdx.x >> 5;
     uint32_t* hist = hist_all[wib];
     const uint16_t* vals = reinterpret_cast<const uint16_t*>(P.vals);
-    const uint32_t n_cells = P.ctl[1] ? 0u : min(P.ctl[3], P.wide_cap);
+    const uint32_t n_cells = P.ctl[1] ? 0u : min(P.ctl[3], P.rare_cap);
     const uint32_t warps = gridDim.x * 4;
     for (uint32_t it = blockIdx.x * 4 + wib; it < n_cells; it += warps) {
-        const FinKind& K = P.kind[P.wide_list[2 * it]];
-        const uint32_t c = P.wide_list[2 * it + 1];
+        const FinKind& K = P.kind[P.rare_list[2 * (size_t)it]];
+        const uint32_t c = P.rare_list[2 * (size_t)it + 1];
         const uint32_t key = c / P.n_windows, pc0 = key * P.n_panes + (c - key * P.n_windows);
         const uint32_t count = K.o_count[c];
         // digit pass over the cell's runs: `want` < 256 restricts to values with that high byte

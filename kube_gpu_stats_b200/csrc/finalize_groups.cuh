@@ -1,0 +1,215 @@
+// finalize_groups.cuh - the common case of a tumbling-window job finished without a histogram.
+//
+// In collector order (sorted by GPU, then time) the samples of one (gpu, window) cell are ONE
+// contiguous piece of the value log - a single run, or the few runs of a window in which the
+// tenant changed - and at 1 Hz with windows of up to a minute it has at most 64 values.  Such a
+// cell fits in 17 registers (four values per word).  k_finalize_groups gives every (gpu, window)
+// cell one thread which loads the cell's bytes ONCE and uses them three times:
+//   * its own percentiles,
+//   * the percentiles of the (pod, window) cell that consists of the very same run (one process
+//     per GPU: the usual case; k_accum wrote the pod descriptor right before the gpu descriptor),
+//   * together with the other GPUs of its node - the threads of one (node, window) GROUP are
+//     neighbouring lanes - the percentiles of the (node, window) cell, by summing the lanes' counts
+//     with warp shuffles.
+// Selection is an exact rank search by bisection on the value (rule R5 needs the values of rank lo
+// and hi): "how many of my values are > t" is answered for four values at a time - add 127 - t to
+// every byte (values are < 128, so no carry crosses a byte) and bit 7 of each byte is the answer;
+// dp4a on the SIGNED bytes sums those flags for a whole word in one instruction:
+//     sum_signed(x + c) = sum(x) + n_bytes * c - 256 * #{x > t}.
+// Seven steps of 2 instructions per word, the same for every lane (no divergence, no shared
+// memory, no dependent load-modify-store chain), instead of a 104-bin private histogram.
+// Takes over, for these cells, what k_finalize_cells does (gpu_util_stats.py:77-80 for the mean;
+// max and percentiles have no reference counterpart, rule R5 of oracle/window_stats.py).
+//
+// A cell that does not fit (more than 64 values, a value >= 128, runs that are not contiguous in
+// the log, the 16-bit metric, sliding windows) is left alone: the kernel marks what it finished in
+// P.done[] and k_finalize_cells, launched after it, skips exactly those cells.
+#pragma once
+#include "finalize.cuh"
+
+namespace kgs {
+
+constexpr int kGroupWords = 17;          // 64 values at any byte alignment
+constexpr uint32_t kGroupMaxCount = 64;
+constexpr int kGroupThreads = 128;
+
+__device__ __forceinline__ int dp4a_s8u8(uint32_t a, uint32_t b, int c) {
+    int d;
+    asm("dp4a.s32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+
+// Number of the lane's values that are > cand - 1, i.e. >= cand (1 <= cand <= 127).  x holds the values four per
+// word, unused bytes are 0; byte_total = sum of all bytes of x.
+__device__ __forceinline__ uint32_t count_ge(const uint32_t (&x)[kGroupWords], uint32_t byte_total, uint32_t cand) {
+    const uint32_t c = 128u - cand;                  // 127 - (cand - 1), 1..127: x + c <= 254 per byte
+    const uint32_t c4 = c * 0x01010101u;
+    int a0 = 0, a1 = 0;
+#pragma unroll
+    for (int k = 0; k + 1 < kGroupWords; k += 2) {
+        a0 = dp4a_s8u8(x[k] + c4, 0x01010101u, a0);
+        a1 = dp4a_s8u8(x[k + 1] + c4, 0x01010101u, a1);
+    }
+    a0 = dp4a_s8u8(x[kGroupWords - 1] + c4, 0x01010101u, a0);
+    return (byte_total + 4u * kGroupWords * c - (uint32_t)(a0 + a1)) >> 8;
+}
+
+// Sum over the lanes of a group (gs = 1 << gs_log2 aligned lanes); every lane gets the total.
+__device__ __forceinline__ uint32_t group_sum(uint32_t v, uint32_t gs) {
+    for (uint32_t d = 1; d < gs; d <<= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, d);
+    return v;
+}
+
+// The value of rank r (0-based, ascending) among n values: the lane's own (GROUP = false) or those of
+// all lanes of its group together (GROUP = true; n and r are then the group's, equal in all its lanes).
+template <bool GROUP>
+__device__ __forceinline__ uint32_t rank_select(const uint32_t (&x)[kGroupWords], uint32_t byte_total, uint32_t n,
+                                                uint32_t r, uint32_t gs) {
+    const uint32_t need = n - r;                     // v[r] >= cand  <=>  #{v >= cand} >= n - r
+    uint32_t ans = 0;
+#pragma unroll
+    for (int b = 6; b >= 0; --b) {
+        const uint32_t cand = ans | (1u << b);
+        uint32_t ge = count_ge(x, byte_total, cand);
+        if (GROUP) ge = group_sum(ge, gs);
+        if (ge >= need) ans = cand;
+    }
+    return ans;
+}
+
+__global__ void __launch_bounds__(kGroupThreads) k_finalize_groups(const __grid_constant__ FinParams P) {
+    constexpr uint32_t kAll = 0xFFFFFFFFu;
+    if (P.ctl[1]) return;                            // overflowed run log: lists are incomplete, the host reports it
+    const uint32_t gs = 1u << P.g_gs_log2;
+    const uint32_t lane = lane_id();
+    const uint64_t t = (uint64_t)blockIdx.x * kGroupThreads + threadIdx.x;
+    const uint32_t l = (uint32_t)t & (gs - 1);
+    const uint32_t grp = (uint32_t)(t >> P.g_gs_log2);
+    const uint32_t node = grp / P.n_windows, j = grp - node * P.n_windows;
+    const FinKind& G = P.kind[P.g_gpu];
+    const uint32_t g = node * P.g_gpn + l;
+    const bool have = node < P.g_nodes && l < P.g_gpn && g < G.n_keys;
+    const uint32_t c = g * P.n_windows + j;          // W == 1: pane cell == window cell
+    uint32_t count = 0, vmax = 0, h = 0;
+    unsigned long long total = 0;
+    if (have) {
+        count = G.cnt[c];
+        total = G.sum[c];
+        vmax = G.mx[c];
+        h = G.head[c];
+    }
+    // the cell's runs: at most four, together one contiguous piece of the value log
+    bool ok = true, single = false;
+    uint32_t start = 0;
+    uint4 d0 = make_uint4(0, 0, 0, 0);
+    if (count) {
+        ok = count <= kGroupMaxCount && vmax < 128u;
+        if (ok) {
+            uint32_t at = h, lo = 0xFFFFFFFFu, hi = 0, tot = 0, runs = 0;
+            while (at && runs < 4) {
+                const uint4 d = __ldg(P.desc + (at - 1));
+                if (runs == 0) d0 = d;
+                lo = min(lo, d.x);
+                hi = max(hi, d.x + d.y);
+                tot += d.y;
+                at = d.z;
+                ++runs;
+            }
+            ok = at == 0 && tot == count && hi - lo == count;
+            start = lo;
+            single = runs == 1;
+        }
+    }
+    const uint32_t n = (ok && count) ? count : 0;    // values this lane holds
+    uint32_t x[kGroupWords];
+    {
+        const uint32_t w0 = start & ~3u, end = start + n;
+        const uint32_t* src = reinterpret_cast<const uint32_t*>(P.vals + w0);
+#pragma unroll
+        for (int k = 0; k < kGroupWords; ++k) {
+            uint32_t w = 0;
+            if (w0 + 4u * k < end) w = __ldg(src + k);
+            const int e = (int)(end - (w0 + 4u * k));           // valid bytes of this word end at byte e
+            uint32_t m = e >= 4 ? 0xFFFFFFFFu : (e <= 0 ? 0u : (0xFFFFFFFFu >> (8 * (4 - e))));
+            if (k == 0) m &= 0xFFFFFFFFu << (8 * (start & 3u));
+            x[k] = w & m;
+        }
+    }
+    const uint32_t byte_total = n ? (uint32_t)total : 0u;
+    // ---- this GPU's cell, and the pod cell made of the same run ---------------------------------------
+    const bool mine = have && (count == 0 || ok);    // this thread finishes its gpu cell
+    uint32_t twin = kInvalid;
+    if (mine && count && single && P.g_pod >= 0 && h >= 2) {
+        const uint4 sib = __ldg(P.desc + (h - 2));   // the pod descriptor of the same run
+        if (sib.z == 0 && sib.w != kInvalid && sib.x == d0.x && sib.y == d0.y && P.kind[P.g_pod].head[sib.w] == h - 1)
+            twin = sib.w;
+    }
+    if (mine) {
+        store_basics(P, G, c, count, total, vmax);
+        P.done[G.cell_begin + c] = (uint8_t)P.done_gen;
+        if (twin != kInvalid) {
+            const FinKind& K = P.kind[P.g_pod];
+            store_basics(P, K, twin, count, total, vmax);
+            P.done[K.cell_begin + twin] = (uint8_t)P.done_gen;
+        }
+    }
+    if (__any_sync(kAll, n != 0)) {
+        for (uint32_t iq = 0; iq < P.n_q; ++iq) {
+            uint32_t ilo = 0, ihi = 0;
+            double w = 0.0;
+            if (n) pct_ranks(P.q[iq], n, ilo, ihi, w);
+            const uint32_t nn = n ? n : 1u;
+            const uint32_t vlo = rank_select<false>(x, byte_total, nn, ilo, gs);
+            uint32_t vhi = vlo;
+            if (__any_sync(kAll, ihi != ilo)) {
+                const uint32_t v2 = rank_select<false>(x, byte_total, nn, ihi, gs);
+                if (ihi != ilo) vhi = v2;
+            }
+            if (mine && n) {
+                store_pct(P, G, c, iq, vlo, vhi, w);
+                if (twin != kInvalid) store_pct(P, P.kind[P.g_pod], twin, iq, vlo, vhi, w);
+            }
+        }
+    }
+    // ---- the node's cell: the lanes of a group hold its values between them ----------------------------
+    if (P.g_node < 0) return;                        // warp-uniform
+    const FinKind& N = P.kind[P.g_node];
+    const uint32_t group_lanes = (gs == 32 ? kAll : ((1u << gs) - 1u)) << (lane & ~(gs - 1));
+    const bool lanes_ok = (__ballot_sync(kAll, ok) & group_lanes) == group_lanes;
+    const uint32_t held = group_sum(n, gs);
+    const bool node_here = l == 0 && node < P.g_nodes && node < N.n_keys;
+    const uint32_t nc = node * P.n_windows + j;
+    uint32_t ncount = 0, nmax = 0;
+    unsigned long long ntotal = 0;
+    if (node_here) {
+        ncount = N.cnt[nc];
+        ntotal = N.sum[nc];
+        nmax = N.mx[nc];
+    }
+    // every sample of the node cell must be in some lane's registers (a GPU outside the gpu table's
+    // domain, or a cell some lane could not take, leaves the node cell to k_finalize_cells)
+    const bool node_fast = node_here && lanes_ok && ncount == held;
+    if (node_fast) {
+        store_basics(P, N, nc, ncount, ntotal, nmax);
+        P.done[N.cell_begin + nc] = (uint8_t)P.done_gen;
+    }
+    const uint32_t base_lane = lane & ~(gs - 1);
+    const bool group_fast = __shfl_sync(kAll, (uint32_t)(node_fast && ncount > 0), base_lane) != 0;
+    if (!__any_sync(kAll, group_fast)) return;
+    const uint32_t gn = __shfl_sync(kAll, ncount, base_lane);
+    for (uint32_t iq = 0; iq < P.n_q; ++iq) {
+        uint32_t ilo = 0, ihi = 0;
+        double w = 0.0;
+        if (group_fast) pct_ranks(P.q[iq], gn, ilo, ihi, w);   // same n in every lane of the group: same ranks
+        const uint32_t nn = group_fast ? gn : 1u;
+        const uint32_t vlo = rank_select<true>(x, byte_total, nn, ilo, gs);
+        uint32_t vhi = vlo;
+        if (__any_sync(kAll, ihi != ilo)) {
+            const uint32_t v2 = rank_select<true>(x, byte_total, nn, ihi, gs);
+            if (ihi != ilo) vhi = v2;
+        }
+        if (node_fast && ncount) store_pct(P, N, nc, iq, vlo, vhi, w);
+    }
+}
+
+}  // namespace kgs

@@ -116,7 +116,7 @@ __global__ void __launch_bounds__(CellLayout::NT) k_finalize_slide(const __grid_
             add_list_sync<L>(base, P, in);
         }
         const bool later = on && count > 0 && (bad || count > kSmallMax);
-        defer_cell(P, later, count, ks, c);         // the slow kernel counts these windows pane by pane
+        defer_cell(P, later && count <= kSmallMax, later && count > kSmallMax, ks, c);   // the slow kernel counts these windows pane by pane
         if (on && count > 0 && !later) {
             for (uint32_t iq = 0; iq < P.n_q; ++iq) {
                 uint32_t ilo, ihi, vlo, vhi;

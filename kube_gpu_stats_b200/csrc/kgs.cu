@@ -12,6 +12,7 @@
 #include "common.cuh"
 #include "finalize.cuh"
 #include "finalize_slide.cuh"
+#include "finalize_groups.cuh"
 #include "join.cuh"
 #include "noalloc.cuh"
 #include "segmean.cuh"
@@ -85,10 +86,14 @@ struct kgs_ctx {
     uint32_t mx_piece_bytes = 32u << 20;
     bool mx_valid = false;
     size_t clear_bytes = 0;
-    uint32_t* ctl = nullptr;       // [0] run cursor [1] run-log overflow [2] big-list length [3] spare
-    uint32_t* big_list = nullptr;
-    uint32_t* wide_list = nullptr;
-    uint32_t big_cap = 0, wide_cap = 0;
+    uint32_t* ctl = nullptr;       // [0] run cursor [1] run-log overflow [2] big cells listed [3] wide cells listed
+    uint32_t* rare_list = nullptr; // cells left to k_finalize_rare: wide ones from the front, big ones from the back
+    uint32_t rare_cap = 0;
+    uint8_t* done = nullptr;       // per window cell: finished by k_finalize_groups in finalize pass done_gen
+    uint32_t done_gen = 0;
+    size_t done_bytes = 0;
+    bool groups_path = true;       // k_finalize_groups for tumbling-window jobs that include the per-GPU table
+    uint32_t thread_cell_max = 256;   // cells above this many samples are counted by a warp, not by a thread
     size_t result_off = 0, result_bytes = 0, exchange_bytes = 0;
     bool packed_exchange = false, packed_on = false, packed_sum64 = false;   // option; state of the open job
     size_t packed_off = 0, packed_bytes = 0;
@@ -251,6 +256,8 @@ int kgs_create(int device, kgs_handle* out) {
     if (const char* e = getenv("KGS_DENSE")) h->dense_path = atoi(e) != 0;
     if (const char* e = getenv("KGS_PARSE_PIECE_KB")) { const int v = atoi(e); if (v >= 16 && v <= (1 << 21)) h->mx_piece_bytes = (uint32_t)v << 10; }
     if (const char* e = getenv("KGS_ACCUM_TMA")) h->accum_tma = atoi(e) != 0;
+    if (const char* e = getenv("KGS_FINALIZE_GROUPS")) h->groups_path = atoi(e) != 0;
+    if (const char* e = getenv("KGS_THREAD_CELL_MAX")) { const int v = atoi(e); if (v >= 1 && v <= 65535) h->thread_cell_max = (uint32_t)v; }
     if (h->accum_tma) {
         h->accum_ctas_per_sm = 2;   // 64 KB of tile buffers + 42 KB static per CTA
         cudaFuncSetAttribute(k_accum<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTmaSmemBytes);
@@ -564,7 +571,15 @@ int kgs_join_probe_noalloc(int device, const uint64_t* d_keys, const uint32_t* d
         return bad(KGS_ERR_ARG, "kgs_join_probe_noalloc: null device pointer");
     if (((uintptr_t)d_gpu_gid | (uintptr_t)d_pid | (uintptr_t)d_out_pod_id) & 15)
         return bad(KGS_ERR_ARG, "kgs_join_probe_noalloc: sample columns and output must be 16-byte aligned");
-    cudaError_t e = cudaSetDevice(device);
+    // the caller's current device is put back on every way out
+    int prev_device = -1;
+    cudaError_t e = cudaGetDevice(&prev_device);
+    if (e != cudaSuccess) return bad(KGS_ERR_CUDA, std::string("cudaGetDevice: ") + cudaGetErrorString(e));
+    struct RestoreDevice {
+        int dev;
+        ~RestoreDevice() { if (dev >= 0) cudaSetDevice(dev); }
+    } restore{prev_device == device ? -1 : prev_device};
+    e = cudaSetDevice(device);
     if (e != cudaSuccess) return bad(KGS_ERR_CUDA, std::string("cudaSetDevice: ") + cudaGetErrorString(e));
     JoinSlot* slots = nullptr;   // the real device address of the module's table (set-up: once per device)
     e = noalloc_table(device, &slots);
@@ -621,6 +636,12 @@ int kgs_stats_begin(kgs_handle h, const kgs_window_spec* sp) {
         lay[k].mx = off; off = align_up(off + pc * 4, 256);
         lay[k].head = off; if (pct) off = align_up(off + pc * 4, 256);
     }
+    // one byte per window cell: the finalize pass (1..255) in which k_finalize_groups finished the cell
+    uint64_t window_cells = 0;
+    for (int k = 0; k < 3; ++k)
+        if (sp->key_mask & (1u << k)) window_cells += (uint64_t)nk_in[k] * sp->n_windows;
+    const size_t done_off = off;
+    if (pct) off = align_up(off + window_cells, 256);
     const size_t clear_bytes = off;
     for (int k = 0; k < 3; ++k) {
         if (!(sp->key_mask & (1u << k))) continue;
@@ -660,15 +681,11 @@ int kgs_stats_begin(kgs_handle h, const kgs_window_spec* sp) {
     const size_t result_area = off - clear_bytes;
     off += result_area;
     const size_t slot_shift = (h->job_seq++ & 1) ? result_area : 0;
-    const uint32_t big_cap = (uint32_t)(total_hint / kSmallMax * (W) + 16) * (uint32_t)n_kinds;
-    const size_t big_off = off;
-    off = align_up(off + (size_t)big_cap * 8, 256);
-    uint64_t wide_cap = 0;
-    if (pct)
-        for (int k = 0; k < 3; ++k)
-            if (sp->key_mask & (1u << k)) wide_cap += (uint64_t)nk_in[k] * sp->n_windows;
-    const size_t wide_off = off;
-    off = align_up(off + (size_t)wide_cap * 8, 256);
+    // the rare list has one entry per window cell (a cell is listed at most once), so it cannot overflow
+    if (window_cells >= (1ull << 32)) return fail(h, KGS_ERR_ARG, "too many window cells");
+    const uint64_t rare_cap = pct ? window_cells : 0;
+    const size_t rare_off = off;
+    off = align_up(off + (size_t)rare_cap * 8, 256);
     // queued kernels may still use the previous job's arena
     if (off > h->arena.cap) KGS_CUDA(h, cudaStreamSynchronize(h->compute));
     int rc;
@@ -703,10 +720,11 @@ int kgs_stats_begin(kgs_handle h, const kgs_window_spec* sp) {
     h->packed_sum64 = sum64;
     h->packed_off = packed_begin + slot_shift;
     h->packed_bytes = packed_end - packed_begin;
-    h->big_list = reinterpret_cast<uint32_t*>(base + big_off);
-    h->big_cap = big_cap;
-    h->wide_list = reinterpret_cast<uint32_t*>(base + wide_off);
-    h->wide_cap = (uint32_t)wide_cap;
+    h->rare_list = reinterpret_cast<uint32_t*>(base + rare_off);
+    h->rare_cap = (uint32_t)rare_cap;
+    h->done = pct ? reinterpret_cast<uint8_t*>(base + done_off) : nullptr;
+    h->done_bytes = pct ? (size_t)window_cells : 0;
+    h->done_gen = 0;
     h->clear_bytes = clear_bytes;
     if (pct) {
         const uint64_t vals_cap = total_hint + 16 * 4096 + 64;     // in samples; fb_mib takes 2 B each
@@ -873,15 +891,48 @@ int kgs_stats_finalize(kgs_handle h) {
     for (uint32_t i = 0; i < sp.n_q; ++i) P.q[i] = sp.q[i];
     P.vals = static_cast<const uint8_t*>(h->vals.p);
     P.desc = static_cast<const uint4*>(h->desc.p);
-    P.big_list = h->big_list;
-    P.wide_list = h->wide_list;
+    P.rare_list = h->rare_list;
+    P.rare_cap = h->rare_cap;
+    P.thread_cell_max = h->thread_cell_max;
     P.ctl = h->ctl;
-    P.big_cap = h->big_cap;
-    P.wide_cap = h->wide_cap;
     P.u16 = sp.metric == KGS_METRIC_FB ? 1u : 0u;
     P.slide_chunk = h->slide_chunk;
     P.packed_sum64 = h->packed_sum64 ? 1u : 0u;
     cudaStream_t st = h->compute;
+    // A job may be finalized more than once (more batches in between): the lists of cells left to
+    // k_finalize_rare start empty each time.
+    if (sp.n_q && h->job_final) KGS_CUDA(h, cudaMemsetAsync(h->ctl + 2, 0, 8, st));
+    // k_finalize_groups: tumbling (or sampled) windows of an 8-bit metric, per-GPU table part of the job
+    const int slot_of[3] = {(sp.key_mask & 1u) ? 0 : -1, (sp.key_mask & 2u) ? (int)__builtin_popcount(sp.key_mask & 1u) : -1,
+                            (sp.key_mask & 4u) ? (int)__builtin_popcount(sp.key_mask & 3u) : -1};
+    bool groups = h->groups_path && cells && sp.n_q && h->W == 1 && sp.metric != KGS_METRIC_FB && slot_of[1] >= 0;
+    if (groups) {
+        uint32_t gs_log2 = 0;
+        while ((1u << gs_log2) < sp.gpus_per_node && gs_log2 < 5) ++gs_log2;
+        const bool node_fits = (1u << gs_log2) >= sp.gpus_per_node;      // else: no node cooperation, one lane per GPU
+        P.g_gpu = slot_of[1];
+        P.g_pod = slot_of[0];
+        P.g_node = node_fits ? slot_of[2] : -1;
+        if (!node_fits) gs_log2 = 0;
+        P.g_gs_log2 = gs_log2;
+        P.g_gpn = node_fits ? sp.gpus_per_node : 1u;
+        uint64_t nodes = node_fits ? ((uint64_t)sp.n_gpus + sp.gpus_per_node - 1) / sp.gpus_per_node : sp.n_gpus;
+        if (P.g_node >= 0 && sp.n_nodes > nodes) nodes = sp.n_nodes;
+        P.g_nodes = (uint32_t)nodes;
+        const uint64_t threads = (nodes * sp.n_windows) << gs_log2;
+        const uint64_t grid = (threads + kGroupThreads - 1) / kGroupThreads;
+        if (grid == 0 || grid > 0x7FFFFFFFull) groups = false;
+        if (groups) {
+            if (++h->done_gen > 255) {   // the stamp is a byte: start over with clean flags
+                KGS_CUDA(h, cudaMemsetAsync(h->done, 0, h->done_bytes, st));
+                h->done_gen = 1;
+            }
+            P.done = h->done;
+            P.done_gen = h->done_gen;
+            launch(h, KGS_K_FINALIZE_GROUPS, st, [&] { k_finalize_groups<<<(unsigned)grid, kGroupThreads, 0, st>>>(P); });
+        }
+    }
+    if (!groups) P.done = nullptr;
     if (cells) {
         if (h->W > 1 && h->slide && sp.metric != KGS_METRIC_FB) {
             // sliding windows: per-cell basics, then one thread per chunk of windows keeps the histogram sliding
@@ -900,9 +951,9 @@ int kgs_stats_finalize(kgs_handle h) {
         }
         if (sp.n_q && sp.metric == KGS_METRIC_FB) {   // 16-bit values: two-digit radix select, warp per cell
             launch(h, KGS_K_FINALIZE_WIDE, st, [&] { k_finalize_u16<<<148 * 8, 128, 0, st>>>(P); });
-        } else if (sp.n_q) {   // one launch for the cells with values >= 104 and those above 65 535 samples
+        } else if (sp.n_q) {   // one launch for the cells with values >= 104 and those with many samples
             const int wide_grid = grid_for(cells, WideLayout::NT, 148 * 6);
-            const int big_grid = h->accumulated * h->W > kSmallMax ? 148 * 2 : 0;
+            const int big_grid = h->accumulated * h->W > h->thread_cell_max ? 148 * 4 : 0;
             P.rare_wide_ctas = (uint32_t)wide_grid;
             launch(h, KGS_K_FINALIZE_WIDE, st, [&] { k_finalize_rare<<<wide_grid + big_grid, WideLayout::NT, 0, st>>>(P); });
         }
@@ -927,6 +978,18 @@ static int check_job_flags(kgs_handle h) {
         return fail(h, KGS_ERR_CAPACITY,
                     "run log overflow: the shared pool needed " + std::to_string(ctl[0]) + " entries, total capacity " +
                         std::to_string(h->desc_cap) + " (input far from collector order; raise it with kgs_set_run_log_capacity)");
+    return KGS_OK;
+}
+
+int kgs_job_counter(kgs_handle h, int which, uint64_t* out) {
+    if (!h || !out || which < 0 || which >= KGS_N_JOB_COUNTERS) return KGS_ERR_ARG;
+    if (!h->job_open) return fail(h, KGS_ERR_STATE, "kgs_job_counter: no job");
+    KGS_CUDA(h, cudaSetDevice(h->device));
+    uint32_t ctl[8] = {0};
+    KGS_CUDA(h, cudaMemcpyAsync(ctl, h->ctl, sizeof(ctl), cudaMemcpyDeviceToHost, h->compute));
+    KGS_CUDA(h, cudaStreamSynchronize(h->compute));
+    static const int slot[KGS_N_JOB_COUNTERS] = {0, 4, 2, 3};
+    *out = ctl[slot[which]];
     return KGS_OK;
 }
 

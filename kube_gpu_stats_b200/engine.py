@@ -172,6 +172,15 @@ class Engine:
         self._n_keys['node'] = spec.n_nodes
         self._ck(self._lib.kgs_window_stats(self._h, C.byref(spec)))
 
+    def job_counter(self, which):
+        """One of the job's kernel-side counters (kgs_job_counter): 'pool_entries', 'cache_ctas',
+        'big_cells', 'wide_cells'."""
+        idx = {'pool_entries': _ffi.JC_POOL_ENTRIES, 'cache_ctas': _ffi.JC_CACHE_CTAS,
+               'big_cells': _ffi.JC_BIG_CELLS, 'wide_cells': _ffi.JC_WIDE_CELLS}[which]
+        out = C.c_uint64()
+        self._ck(self._lib.kgs_job_counter(self._h, idx, C.byref(out)))
+        return out.value
+
     def fetch(self, kind, want=('count', 'sum', 'max', 'mean', 'pct')):
         sp = self._spec
         ncell = self._n_keys[kind] * sp.n_windows

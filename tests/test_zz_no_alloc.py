@@ -8,14 +8,18 @@ stalls the device while it runs.  The entry point tested here keeps its hash tab
 
 The check: through the C ABI, on buffers this test owns (torch tensors stand in for the
 caller's arena), the pod of every sample must equal what the ordinary kgs_build_join +
-kgs_probe pair returns - bit for bit, on two calls in a row with DIFFERENT tables, so a table
-left over from the first call would be caught.  This file sorts last so that a run with -x has
+kgs_probe pair returns AND what the oracle's join (rule R2, oracle/window_stats.py) says - bit
+for bit, on two calls in a row with DIFFERENT tables, so a table left over from the first call
+would be caught.  The second call must also leave the amount of free device memory untouched
+and the caller's current device as it was: that is the property the entry point exists for.  This file sorts last so that a run with -x has
 already executed every other test when it gets here; it also passes on its own.
 """
 import ctypes as C
 
 import numpy as np
 import pytest
+
+from oracle import window_stats as ws
 
 pytestmark = pytest.mark.gpu
 
@@ -41,7 +45,7 @@ def test_noalloc_join_equals_regular_join_twice(engine):
     lib = _ffi.lib()
     dev = torch.device('cuda', 0)
     rng = np.random.default_rng(2026)
-    for m, n in ((5000, 100003), (60000, 250000)):          # two calls in a row, second table larger
+    for call, (m, n) in enumerate(((5000, 100003), (60000, 250000))):   # two calls in a row, second table larger
         keys, pods, gid, pid = _case(rng, m, n)
         # the regular path: library-owned table
         engine.build_join(keys, pods, 5000)
@@ -55,12 +59,17 @@ def test_noalloc_join_equals_regular_join_twice(engine):
         d_pid = torch.from_numpy(pid.view(np.int32)).to(dev)
         d_out = torch.full((n,), -7, dtype=torch.int32, device=dev)
         torch.cuda.synchronize()
+        free_before = torch.cuda.mem_get_info(0)[0]
         rc = lib.kgs_join_probe_noalloc(0, d_keys.data_ptr(), d_pods.data_ptr(), m, d_gid.data_ptr(),
                                         d_pid.data_ptr(), n, 8, d_out.data_ptr(), None)
         assert rc == _ffi.KGS_OK, lib.kgs_last_error(None).decode()
         torch.cuda.synchronize()
+        if call > 0:        # the first call on a device may load the module (which holds the 2 MiB table)
+            assert torch.cuda.mem_get_info(0)[0] == free_before, 'the call changed the free device memory'
+        assert torch.cuda.current_device() == 0
         got = d_out.cpu().numpy().view(np.uint32)
         np.testing.assert_array_equal(got, want)            # integer result: tolerance 0
+        np.testing.assert_array_equal(got, ws.probe_np(keys, pods, gid, pid, 8))    # and the oracle's join
 
 
 def test_noalloc_rejects_oversized_table(built_lib):
