@@ -210,17 +210,20 @@ def run_b200(args):
     stream = torch.cuda.ExternalStream(eng.stream('compute'), device=torch.device('cuda', local))
     gather, exchange = None, None
     if world > 1:
-        # tables travel as copy-engine pushes into peer-mapped symmetric memory (no SMs taken from the next
-        # job's kernels); the NCCL all_gather stays as the transport when symmetric memory cannot be set up
+        # The tables travel through the library's own exchange (kgs_exchange_push: copy-engine pushes into
+        # peer-mapped memory + one barrier kernel, no SMs taken from the next job's kernels); torch supplies the
+        # peer-mapped allocation.  kgs_exchange_nccl (one ncclAllGather issued by the library on its own
+        # communicator) is the transport when symmetric memory cannot be set up, or with KGS_EXCHANGE=nccl.
+        with torch.cuda.stream(stream):
+            eng.window_stats_device(spec)
+        eng.sync()
+        slot_bytes = eng.exchange_region()[1]
         try:
             if os.environ.get('KGS_EXCHANGE', 'peer') != 'peer':
                 raise RuntimeError('KGS_EXCHANGE asks for NCCL')
-            gather = sharding.PeerTableGather(eng, KINDS, world)
-            with torch.cuda.stream(stream):
-                eng.window_stats_device(spec)
-                gather.all_gather()              # rendezvous now: every rank takes the same branch
-            eng.sync()
-            exchange = 'copy-engine pushes of the packed tables into every peer over NVLink (symmetric memory) + signal barrier, overlapped with the next step'
+            gather = sharding.PeerExchange(eng, world, rank, slot_bytes)
+            exchange = ('kgs_exchange_push: copy-engine pushes of the packed tables into every peer over NVLink '
+                        '(peer-mapped symmetric memory) + one barrier kernel, overlapped with the next step')
         except Exception as exc:                 # noqa: BLE001
             sys.stderr.write('rank %d: peer exchange not available (%s); using the NCCL all_gather\n' % (rank, exc))
             ok = torch.tensor([0], device='cuda')
@@ -228,21 +231,23 @@ def run_b200(args):
             ok = torch.tensor([1], device='cuda')
         dist.all_reduce(ok, op=dist.ReduceOp.MIN)
         if int(ok) == 0:
-            gather = sharding.TableGather(eng, KINDS, world)
-            exchange = 'NCCL all_gather of the packed exchange tables, overlapped with the next step'
+            ids = [eng.nccl_unique_id() if rank == 0 else None]
+            dist.broadcast_object_list(ids, src=0)
+            eng.nccl_init(ids[0], world, rank)
+            gather = sharding.NcclExchange(eng, world, slot_bytes)
+            exchange = 'kgs_exchange_nccl: one ncclAllGather of the packed tables (library-owned communicator), overlapped with the next step'
 
     def step():
-        # N > 1: the all_gather of step i's tables runs on a side stream while step i+1 computes
-        # (double-buffered result regions); everything is joined before the closing barrier
-        if gather is not None:
-            gather.before_next_job(stream)
+        # N > 1: the exchange of step i's tables runs on the library's exchange stream while step i+1
+        # computes (double-buffered result regions, ordering inside the library); everything is joined
+        # before the closing barrier
         eng.window_stats_device(spec)
         if gather is not None:
-            gather.all_gather_async(stream)
+            gather.push()
 
     def barrier():
         if gather is not None:
-            gather.wait()
+            eng.exchange_sync()
         if world > 1:
             dist.barrier()
         eng.sync()
@@ -261,7 +266,7 @@ def run_b200(args):
         for _ in range(args.steps):
             step()
         if gather is not None:
-            gather.join(stream)
+            eng.exchange_join()
         p1.record(stream)
         barrier()
         probe_ms = torch.tensor([p0.elapsed_time(p1)], dtype=torch.float64, device='cuda')
@@ -276,7 +281,7 @@ def run_b200(args):
             for _ in range(args.steps):
                 step()
         if gather is not None:
-            gather.join(stream)          # the last collectives belong to the timed region
+            eng.exchange_join()          # the last exchanges belong to the timed region
         e1.record(stream)
         barrier()
         ms_total = e0.elapsed_time(e1) / repeats       # per K steps
@@ -295,7 +300,8 @@ def run_b200(args):
                 eng.stats_accumulate()
             eng.stats_finalize()
             if gather is not None:
-                gather.all_gather()
+                gather.push()
+                eng.exchange_join()
             return eng.fetch_all(KINDS)          # one D2H of the whole result region into pinned memory
 
         for _ in range(2):

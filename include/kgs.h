@@ -12,7 +12,7 @@
  *     kgs_last_error(h) returns the text of the most recent failure on that handle;
  *   - the caller owns every host buffer it passes; the library owns all device memory it
  *     allocates until kgs_destroy;
- *   - a handle owns two CUDA streams (copy, compute) on one device; a handle is NOT
+ *   - a handle owns three CUDA streams (copy, compute, exchange) on one device; a handle is NOT
  *     thread-safe, distinct handles are independent;
  *   - there is no CPU fallback: without a CUDA device kgs_create fails.
  */
@@ -101,6 +101,13 @@ int kgs_batch_append(kgs_handle h, const uint32_t* ts, const uint32_t* gpu_gid, 
  * its own run.  No reference counterpart (ingestion, north_star subsystem 1).  Queued on the compute
  * stream; needs a second copy of the batch in device memory. */
 int kgs_reorder_batch(kgs_handle h);
+/* kgs_ingest and the first kgs_batch_append look at a few hundred samples of the host columns: a batch
+ * that interleaves several series with a short period (all processes of a GPU, or all GPUs of a node,
+ * reported second by second) is marked, and kgs_stats_accumulate then reads a series-major copy of it
+ * (the same sort, into the other batch slot) instead.  The resident batch itself stays as ingested:
+ * kgs_probe and kgs_fetch_batch answer in the caller's order.  On by default; 0 switches it off
+ * (also KGS_AUTO_REORDER=0).  Columns adopted from device memory are never looked at. */
+int kgs_set_auto_reorder(kgs_handle h, int on);
 /* Copy the resident batch's columns back to host arrays of n entries (any pointer may be NULL). Blocking. */
 int kgs_fetch_batch(kgs_handle h, uint32_t* ts, uint32_t* gpu_gid, uint32_t* pid, uint32_t* util);
 /* Same, for columns that already live in this device's memory, 32-byte aligned (no copy is made;
@@ -203,6 +210,43 @@ int kgs_packed_offset(kgs_handle h, int key_kind, int which, size_t* offset, siz
 int kgs_result_offset(kgs_handle h, int key_kind, int which, size_t* offset, size_t* nbytes);
 int kgs_fetch_region(kgs_handle h, void* host_dst, size_t nbytes);
 
+/* ---- table exchange between the GPUs of one box (north_star: allgather of the per-shard tables) ----
+ * The reference's tables are keyed by (server, pod) (GUS:70-71) and a pod is bound to one node
+ * (WUG:33), so with nodes partitioned over the GPUs every cell lives on exactly one shard: the
+ * exchange moves bytes and merges by concatenation.  The reference's only cross-shard arithmetic is
+ * WUG:18-20 (GPU totals per type, a few integers), left to the caller.  What travels is the region
+ * kgs_exchange_region describes.  Everything here is queued on the handle's third stream
+ * (kgs_stream(h, 2, ..)) behind the finalize kernels of the job and runs beside the NEXT job's
+ * kernels; a result region is reused two jobs later, and kgs_stats_begin makes that job wait for the
+ * exchange that read it.  Not thread-safe per handle, like the rest.
+ *
+ * Peer pushes (no collective kernel, no SM taken from the statistics kernels):
+ *   setup: gathered[r] = rank r's gathered buffer and flags[r] = rank r's flag words, both AS MAPPED
+ *     ON THIS DEVICE (cudaIpcOpenMemHandle, cuMemMap, a symmetric-memory allocator ...; for r = my_rank
+ *     the local pointers).  A gathered buffer holds 2 halves x n_ranks slots of slot_bytes; the flag
+ *     words are 2 x 16 u32, zero before the first push.  n_ranks <= 16.
+ *   push: copies this rank's region into slot my_rank of the current half of EVERY rank's buffer
+ *     (one cudaMemcpyAsync per rank, copy engines over NVLink), then one small kernel tells every
+ *     peer "complete" and waits for every peer's word (10 s limit, reported by kgs_exchange_sync).
+ *     Every rank must push the same number of times.  *d_gathered = where rank r's tables of THIS
+ *     job will be on this device: (char*)*d_gathered + r * slot_bytes, valid once the exchange stream
+ *     has passed the push, until the next-but-one push.  Readers of a half must be ordered (same
+ *     stream, or an event) before this rank's next-but-one push.
+ *   join: the compute stream waits for every exchange queued so far.  sync: the host does.
+ * NCCL: kgs_exchange_nccl queues ONE ncclAllGather of the region into d_recv (n_ranks x the region's
+ *   size, rank order) on the exchange stream.  nccl_comm is the caller's ncclComm_t (it must come
+ *   from the libnccl.so.2 this process has loaded), or NULL for the handle's own communicator:
+ *   kgs_nccl_unique_id (one rank; share the 128 bytes by any means) + kgs_nccl_init (every rank;
+ *   collective).  libnccl is looked up with dlopen at the first call; KGS_ERR_STATE if absent. */
+int kgs_exchange_setup(kgs_handle h, int n_ranks, int my_rank, void* const* gathered, void* const* flags,
+                       size_t slot_bytes);
+int kgs_exchange_push(kgs_handle h, void** d_gathered, size_t* bytes_per_rank);
+int kgs_exchange_join(kgs_handle h);
+int kgs_exchange_sync(kgs_handle h);
+int kgs_nccl_unique_id(void* id128);
+int kgs_nccl_init(kgs_handle h, const void* id128, int n_ranks, int rank);
+int kgs_exchange_nccl(kgs_handle h, void* nccl_comm, void* d_recv, size_t recv_bytes, size_t* bytes_per_rank);
+
 /* ---- the reference's own statistic, exactly ------------------------------------------- */
 /* GUS:77-80 and GUS:51 on a CSR layout: series s owns values[offsets[s] .. offsets[s+1]).
  * out[s] = sum(values)/len (0.0 when empty) when div == 0 (GUS:77-80), otherwise
@@ -246,11 +290,11 @@ int kgs_launch_count(kgs_handle h, uint64_t* out);
  * on; kgs_kernel_time returns the accumulated device time and launch count of one kernel
  * (ids: KGS_K_*), kgs_reset_kernel_times clears them. */
 enum { KGS_K_BUILD = 0, KGS_K_BUILD_FIN = 1, KGS_K_PROBE = 2, KGS_K_ACCUM = 3, KGS_K_FINALIZE = 4,
-       KGS_K_FINALIZE_BIG = 5, KGS_K_SEGMEAN = 6, KGS_K_CLEAR = 7, KGS_K_FINALIZE_WIDE = 8, KGS_K_FINALIZE_BASIC = 9, KGS_K_SORT = 10, KGS_K_PARSE = 11, KGS_K_FINALIZE_GROUPS = 12, KGS_N_KERNELS = 13 };
+       KGS_K_FINALIZE_BIG = 5, KGS_K_SEGMEAN = 6, KGS_K_CLEAR = 7, KGS_K_FINALIZE_WIDE = 8, KGS_K_FINALIZE_BASIC = 9, KGS_K_SORT = 10, KGS_K_PARSE = 11, KGS_K_FINALIZE_GROUPS = 12, KGS_K_EXCHANGE = 13, KGS_N_KERNELS = 14 };
 int kgs_set_profiling(kgs_handle h, int on);
 int kgs_kernel_time(kgs_handle h, int kernel_id, double* total_ms, uint64_t* launches);
 int kgs_reset_kernel_times(kgs_handle h);
-/* The handle's CUDA streams as cudaStream_t values (which: 0 copy, 1 compute), for a caller that
+/* The handle's CUDA streams as cudaStream_t values (which: 0 copy, 1 compute, 2 exchange), for a caller that
  * wants to order its own device work (a collective, an event) after the library's kernels. */
 int kgs_stream(kgs_handle h, int which, void** out_stream);
 /* Device time between two marks on the compute stream (bench.py's timed region). */

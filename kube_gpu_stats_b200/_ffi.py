@@ -19,9 +19,9 @@ POD_NONE = 0xFFFFFFFF
 MAX_Q = 8
 NOALLOC_MAX_PAIRS = 65536
 JC_POOL_ENTRIES, JC_CACHE_CTAS, JC_BIG_CELLS, JC_WIDE_CELLS = range(4)
-(K_BUILD, K_BUILD_FIN, K_PROBE, K_ACCUM, K_FINALIZE, K_FINALIZE_BIG, K_SEGMEAN, K_CLEAR, K_FINALIZE_WIDE, K_FINALIZE_BASIC, K_SORT, K_PARSE, K_FINALIZE_GROUPS) = range(13)
+(K_BUILD, K_BUILD_FIN, K_PROBE, K_ACCUM, K_FINALIZE, K_FINALIZE_BIG, K_SEGMEAN, K_CLEAR, K_FINALIZE_WIDE, K_FINALIZE_BASIC, K_SORT, K_PARSE, K_FINALIZE_GROUPS, K_EXCHANGE) = range(14)
 KERNEL_NAMES = ['join_build', 'join_resolve', 'join_probe', 'accum', 'finalize_cells', 'finalize_big',
-                'segmean', 'join_clear', 'finalize_wide', 'finalize_basic', 'reorder', 'parse', 'finalize_groups']
+                'segmean', 'join_clear', 'finalize_wide', 'finalize_basic', 'reorder', 'parse', 'finalize_groups', 'exchange']
 
 
 class WindowSpec(C.Structure):
@@ -58,6 +58,7 @@ def load(path=LIB_PATH):
         'kgs_batch_reserve': [H, C.c_uint64],
         'kgs_batch_append': [H, vp, vp, vp, vp, C.c_uint64],
         'kgs_reorder_batch': [H],
+        'kgs_set_auto_reorder': [H, C.c_int],
         'kgs_fetch_batch': [H, vp, vp, vp, vp],
         'kgs_adopt_device_batch': [H, vp, vp, vp, vp, C.c_uint64],
         'kgs_build_join': [H, vp, vp, C.c_uint64, C.c_uint32],
@@ -77,6 +78,13 @@ def load(path=LIB_PATH):
         'kgs_packed_offset': [H, C.c_int, C.c_int, C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)],
         'kgs_result_offset': [H, C.c_int, C.c_int, C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)],
         'kgs_fetch_region': [H, vp, C.c_size_t],
+        'kgs_exchange_setup': [H, C.c_int, C.c_int, vp, vp, C.c_size_t],
+        'kgs_exchange_push': [H, C.POINTER(vp), C.POINTER(C.c_size_t)],
+        'kgs_exchange_join': [H],
+        'kgs_exchange_sync': [H],
+        'kgs_nccl_unique_id': [vp],
+        'kgs_nccl_init': [H, vp, C.c_int, C.c_int],
+        'kgs_exchange_nccl': [H, vp, vp, C.c_size_t, C.POINTER(C.c_size_t)],
         'kgs_segmented_mean_f64': [H, vp, vp, C.c_uint64, C.c_double, C.c_double, vp],
         'kgs_matrix_parse': [H, vp, C.c_uint64, C.c_int, u64p, u64p],
         'kgs_matrix_fetch': [H, vp, vp, vp, vp],

@@ -13,6 +13,7 @@
 #include "finalize.cuh"
 #include "finalize_slide.cuh"
 #include "finalize_groups.cuh"
+#include "exchange.cuh"
 #include "join.cuh"
 #include "noalloc.cuh"
 #include "segmean.cuh"
@@ -35,6 +36,7 @@ struct Batch {
     const uint32_t* ptr[4] = {nullptr, nullptr, nullptr, nullptr};
     uint64_t n = 0;
     cudaEvent_t ready = nullptr, consumed = nullptr;
+    bool interleaved = false;   // host columns looked like a feed that interleaves several series (looks_interleaved)
 };
 
 struct KindState {
@@ -67,6 +69,8 @@ struct kgs_ctx {
     std::string err;
     Batch batch[2];
     int cur = -1;
+    bool auto_reorder = true;      // accumulate from a series-major copy of a batch that interleaves its series
+    bool shadow_valid = false;     // the other batch slot holds that copy of batch[cur]
     // join table
     DevBuf slots, build_keys, build_pods;
     uint32_t n_slots = 0, n_pods = 0;
@@ -107,6 +111,19 @@ struct kgs_ctx {
     bool dense_path = true;
     bool accum_tma = false;        // stage tiles through shared memory with cp.async.bulk + mbarrier
     int accum_ctas_per_sm = 4;     // resident CTAs of 8 warps per SM at 64 registers
+    // table exchange (exchange.cuh)
+    cudaStream_t xchg = nullptr;               // pushes / collectives run here, beside the next job's kernels
+    cudaEvent_t fin_done = nullptr;            // the finalize kernels of the job being exchanged
+    cudaEvent_t region_free[2] = {nullptr, nullptr};   // result-region half i has been read by its exchange
+    bool region_busy[2] = {false, false};
+    int region_half = 0;                       // half the open job writes
+    int px_n = 0, px_me = 0;                   // peer exchange: ranks, my rank
+    char* px_gathered[kMaxRanks] = {nullptr};  // rank r's gathered buffer as mapped on this device
+    PeerFlags px_flags{};
+    size_t px_slot = 0;
+    uint32_t px_seq = 0;
+    uint32_t* px_timeout = nullptr;            // device word raised by k_peer_barrier when a peer never arrived
+    void* nccl_comm = nullptr;                 // own communicator (kgs_nccl_init)
     // measurement
     uint64_t launches = 0;
     bool prof = false;
@@ -203,6 +220,36 @@ int drain_timed(kgs_handle h) {
 
 inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
+// Does this batch interleave several series - a collector that reports all processes of a GPU (or all
+// GPUs of a node) second by second?  Then nearly every sample starts a new run and the statistics
+// kernels crawl (they stay exact).  Three windows of up to 512 samples are looked at on the host:
+// a window votes yes when at least a quarter of its neighbours differ in (gpu, pid) AND the keys
+// repeat with some period of 2..64 samples.  Collector order fails the first test after a few
+// hundred compares; a random stream (configs[2]) fails the second, and is left to the accumulator
+// cache, which is the faster way for it.
+bool looks_interleaved(const uint32_t* gid, const uint32_t* pid, uint64_t n) {
+    if (n < 128) return false;
+    const uint64_t win = n < 512 ? n : 512;
+    const uint64_t at[3] = {0, (n - win) / 2, n - win};
+    int yes = 0;
+    for (int w = 0; w < 3; ++w) {
+        const uint32_t* g = gid + at[w];
+        const uint32_t* p = pid + at[w];
+        uint64_t changes = 0;
+        for (uint64_t i = 0; i + 1 < win; ++i) changes += (g[i] != g[i + 1]) | (p[i] != p[i + 1]);
+        if (changes * 4 < win) continue;
+        for (uint64_t period = 2; period <= 64 && period * 2 < win; ++period) {
+            uint64_t same = 0;
+            for (uint64_t i = 0; i + period < win; ++i) same += (g[i] == g[i + period]) & (p[i] == p[i + period]);
+            if (same * 4 >= 3 * (win - period)) {
+                ++yes;
+                break;
+            }
+        }
+    }
+    return yes >= 2;
+}
+
 int grid_for(uint64_t work_items, int per_block, int max_blocks) {
     uint64_t b = (work_items + per_block - 1) / per_block;
     if (b < 1) b = 1;
@@ -248,6 +295,12 @@ int kgs_create(int device, kgs_handle* out) {
         if ((e = cudaEventCreateWithFlags(&h->batch[b].consumed, cudaEventDisableTiming)) != cudaSuccess) return bail(e, "cudaEventCreate");
         if ((e = cudaEventCreate(&h->mark[b])) != cudaSuccess) return bail(e, "cudaEventCreate");
     }
+    if ((e = cudaStreamCreateWithFlags(&h->xchg, cudaStreamNonBlocking)) != cudaSuccess) return bail(e, "cudaStreamCreate");
+    if ((e = cudaEventCreateWithFlags(&h->fin_done, cudaEventDisableTiming)) != cudaSuccess) return bail(e, "cudaEventCreate");
+    for (int b = 0; b < 2; ++b)
+        if ((e = cudaEventCreateWithFlags(&h->region_free[b], cudaEventDisableTiming)) != cudaSuccess) return bail(e, "cudaEventCreate");
+    if ((e = cudaMalloc(reinterpret_cast<void**>(&h->px_timeout), 256)) != cudaSuccess) return bail(e, "cudaMalloc");
+    if ((e = cudaMemset(h->px_timeout, 0, 256)) != cudaSuccess) return bail(e, "cudaMemset");
     if ((e = cudaFuncSetAttribute(k_sort_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSortSmemBytes)) != cudaSuccess)
         return bail(e, "cudaFuncSetAttribute(k_sort_scatter)");
     if (const char* e = getenv("KGS_SLIDE")) h->slide = atoi(e) != 0;
@@ -257,6 +310,7 @@ int kgs_create(int device, kgs_handle* out) {
     if (const char* e = getenv("KGS_PARSE_PIECE_KB")) { const int v = atoi(e); if (v >= 16 && v <= (1 << 21)) h->mx_piece_bytes = (uint32_t)v << 10; }
     if (const char* e = getenv("KGS_ACCUM_TMA")) h->accum_tma = atoi(e) != 0;
     if (const char* e = getenv("KGS_FINALIZE_GROUPS")) h->groups_path = atoi(e) != 0;
+    if (const char* e = getenv("KGS_AUTO_REORDER")) h->auto_reorder = atoi(e) != 0;
     if (const char* e = getenv("KGS_THREAD_CELL_MAX")) { const int v = atoi(e); if (v >= 1 && v <= 65535) h->thread_cell_max = (uint32_t)v; }
     if (h->accum_tma) {
         h->accum_ctas_per_sm = 2;   // 64 KB of tile buffers + 42 KB static per CTA
@@ -276,6 +330,13 @@ int kgs_destroy(kgs_handle h) {
     cudaSetDevice(h->device);
     cudaStreamSynchronize(h->copy);
     cudaStreamSynchronize(h->compute);
+    if (h->xchg) cudaStreamSynchronize(h->xchg);
+    if (h->nccl_comm && nccl_api().ok) nccl_api().comm_destroy(h->nccl_comm);
+    if (h->xchg) cudaStreamDestroy(h->xchg);
+    if (h->fin_done) cudaEventDestroy(h->fin_done);
+    for (int b = 0; b < 2; ++b)
+        if (h->region_free[b]) cudaEventDestroy(h->region_free[b]);
+    if (h->px_timeout) cudaFree(h->px_timeout);
     for (auto& t : h->timed) {
         cudaEventDestroy(t.e0);
         cudaEventDestroy(t.e1);
@@ -308,6 +369,7 @@ int kgs_sync(kgs_handle h) {
     KGS_CUDA(h, cudaSetDevice(h->device));
     KGS_CUDA(h, cudaStreamSynchronize(h->copy));
     KGS_CUDA(h, cudaStreamSynchronize(h->compute));
+    KGS_CUDA(h, cudaStreamSynchronize(h->xchg));
     return KGS_OK;
 }
 
@@ -350,8 +412,10 @@ int kgs_ingest(kgs_handle h, const uint32_t* ts, const uint32_t* gpu_gid, const 
         if (n) KGS_CUDA(h, cudaMemcpyAsync(B.col[c].p, src[c], n * 4, cudaMemcpyHostToDevice, h->copy));
     }
     B.n = n;
+    B.interleaved = h->auto_reorder && looks_interleaved(gpu_gid, pid, n);
     KGS_CUDA(h, cudaEventRecord(B.ready, h->copy));
     h->cur = b;
+    h->shadow_valid = false;
     return KGS_OK;
 }
 
@@ -369,8 +433,10 @@ int kgs_batch_reserve(kgs_handle h, uint64_t capacity) {
         B.ptr[c] = static_cast<const uint32_t*>(B.col[c].p);
     }
     B.n = 0;
+    B.interleaved = false;
     KGS_CUDA(h, cudaEventRecord(B.ready, h->copy));
     h->cur = b;
+    h->shadow_valid = false;
     return KGS_OK;
 }
 
@@ -388,14 +454,17 @@ int kgs_batch_append(kgs_handle h, const uint32_t* ts, const uint32_t* gpu_gid, 
     // kernels queued on the compute stream may be reading the part already there; appending does not touch it
     for (int c = 0; c < 4; ++c)
         if (n) KGS_CUDA(h, cudaMemcpyAsync(static_cast<uint32_t*>(B.col[c].p) + B.n, src[c], n * 4, cudaMemcpyHostToDevice, h->copy));
+    if (B.n == 0 && n) B.interleaved = h->auto_reorder && looks_interleaved(gpu_gid, pid, n);
     B.n += n;
+    h->shadow_valid = false;
     KGS_CUDA(h, cudaEventRecord(B.ready, h->copy));
     return KGS_OK;
 }
 
-int kgs_reorder_batch(kgs_handle h) {
-    if (!h) return KGS_ERR_ARG;
-    if (h->cur < 0) return fail(h, KGS_ERR_STATE, "kgs_reorder_batch: no resident batch");
+// Stable radix sort of the resident batch by (gpu_gid, pid) into the OTHER batch slot.  switch_cur: the
+// sorted copy becomes the resident batch (kgs_reorder_batch); otherwise the resident batch stays what
+// the caller ingested and the copy is kept beside it for kgs_stats_accumulate (shadow_valid).
+static int reorder_impl(kgs_handle h, bool switch_cur) {
     KGS_CUDA(h, cudaSetDevice(h->device));
     Batch& src = h->batch[h->cur];
     const uint64_t n = src.n;
@@ -455,8 +524,26 @@ int kgs_reorder_batch(kgs_handle h) {
     KGS_CUDA(h, cudaEventRecord(src.consumed, st));
     for (int c = 0; c < 4; ++c) dst.ptr[c] = slot_cols[c];
     dst.n = n;
+    dst.interleaved = false;
     KGS_CUDA(h, cudaEventRecord(dst.ready, st));
-    h->cur = (h->cur + 1) & 1;
+    if (switch_cur) {
+        h->cur = (h->cur + 1) & 1;
+        h->shadow_valid = false;
+    } else {
+        h->shadow_valid = true;
+    }
+    return KGS_OK;
+}
+
+int kgs_reorder_batch(kgs_handle h) {
+    if (!h) return KGS_ERR_ARG;
+    if (h->cur < 0) return fail(h, KGS_ERR_STATE, "kgs_reorder_batch: no resident batch");
+    return reorder_impl(h, true);
+}
+
+int kgs_set_auto_reorder(kgs_handle h, int on) {
+    if (!h) return KGS_ERR_ARG;
+    h->auto_reorder = on != 0;
     return KGS_OK;
 }
 
@@ -484,8 +571,10 @@ int kgs_adopt_device_batch(kgs_handle h, const uint32_t* d_ts, const uint32_t* d
     Batch& B = h->batch[b];
     B.ptr[0] = d_ts; B.ptr[1] = d_gpu_gid; B.ptr[2] = d_pid; B.ptr[3] = d_util;
     B.n = n;
+    B.interleaved = false;   // device columns: the host cannot look; the caller may call kgs_reorder_batch
     KGS_CUDA(h, cudaEventRecord(B.ready, h->copy));
     h->cur = b;
+    h->shadow_valid = false;
     return KGS_OK;
 }
 
@@ -680,14 +769,23 @@ int kgs_stats_begin(kgs_handle h, const kgs_window_spec* sp) {
     // host, to other GPUs) while job i+1 is being computed
     const size_t result_area = off - clear_bytes;
     off += result_area;
-    const size_t slot_shift = (h->job_seq++ & 1) ? result_area : 0;
+    const int half = (int)(h->job_seq++ & 1);
+    const size_t slot_shift = half ? result_area : 0;
+    h->region_half = half;
+    if (h->region_busy[half]) {   // the exchange of the job two back read this half: its kernels come first
+        KGS_CUDA(h, cudaStreamWaitEvent(h->compute, h->region_free[half], 0));
+        h->region_busy[half] = false;
+    }
     // the rare list has one entry per window cell (a cell is listed at most once), so it cannot overflow
     if (window_cells >= (1ull << 32)) return fail(h, KGS_ERR_ARG, "too many window cells");
     const uint64_t rare_cap = pct ? window_cells : 0;
     const size_t rare_off = off;
     off = align_up(off + (size_t)rare_cap * 8, 256);
     // queued kernels may still use the previous job's arena
-    if (off > h->arena.cap) KGS_CUDA(h, cudaStreamSynchronize(h->compute));
+    if (off > h->arena.cap) {
+        KGS_CUDA(h, cudaStreamSynchronize(h->compute));
+        KGS_CUDA(h, cudaStreamSynchronize(h->xchg));
+    }
     int rc;
     if ((rc = reserve(h, h->arena, off))) return rc;
     char* base = static_cast<char*>(h->arena.p);
@@ -763,8 +861,14 @@ int kgs_stats_accumulate(kgs_handle h) {
     if (!h->job_open) return fail(h, KGS_ERR_STATE, "kgs_stats_accumulate: no open job (call kgs_stats_begin)");
     if (h->cur < 0) return fail(h, KGS_ERR_STATE, "kgs_stats_accumulate: no resident batch (call kgs_ingest)");
     KGS_CUDA(h, cudaSetDevice(h->device));
-    Batch& B = h->batch[h->cur];
-    if (B.n == 0) return KGS_OK;
+    if (h->batch[h->cur].n == 0) return KGS_OK;
+    // a batch that interleaves its series is accumulated from a series-major copy (same tables, long runs)
+    if (h->auto_reorder && h->batch[h->cur].interleaved && !h->shadow_valid && h->batch[h->cur].n >= 2) {
+        int rc0 = reorder_impl(h, false);
+        if (rc0) return rc0;
+    }
+    const bool from_shadow = h->shadow_valid && h->batch[h->cur].interleaved;
+    Batch& B = h->batch[from_shadow ? ((h->cur + 1) & 1) : h->cur];
     const kgs_window_spec& sp = h->spec;
     const bool pct = sp.n_q > 0;
     if (h->accumulated + B.n >= (1ull << 32))
@@ -1101,6 +1205,145 @@ int kgs_fetch_region(kgs_handle h, void* host_dst, size_t nbytes) {
     return KGS_OK;
 }
 
+// ---- table exchange ----------------------------------------------------------------------------------
+static int exchange_source(kgs_handle h, const char* who, char** src, size_t* nbytes) {
+    if (!h->job_final) return fail(h, KGS_ERR_STATE, std::string(who) + ": no finalized job");
+    if (h->packed_on) {
+        *src = static_cast<char*>(h->arena.p) + h->packed_off;
+        *nbytes = h->packed_bytes;
+    } else {
+        *src = static_cast<char*>(h->arena.p) + h->result_off;
+        *nbytes = h->exchange_bytes;
+    }
+    return KGS_OK;
+}
+
+int kgs_exchange_setup(kgs_handle h, int n_ranks, int my_rank, void* const* gathered, void* const* flags, size_t slot_bytes) {
+    if (!h || !gathered || !flags) return fail(h, KGS_ERR_ARG, "kgs_exchange_setup: null argument");
+    if (n_ranks < 1 || n_ranks > kMaxRanks || my_rank < 0 || my_rank >= n_ranks)
+        return fail(h, KGS_ERR_ARG, "kgs_exchange_setup: 1 <= n_ranks <= 16 and 0 <= my_rank < n_ranks");
+    if (slot_bytes == 0 || (slot_bytes & 15)) return fail(h, KGS_ERR_ARG, "kgs_exchange_setup: slot_bytes must be a positive multiple of 16");
+    KGS_CUDA(h, cudaSetDevice(h->device));
+    KGS_CUDA(h, cudaStreamSynchronize(h->xchg));
+    for (int r = 0; r < n_ranks; ++r) {
+        if (!gathered[r] || !flags[r]) return fail(h, KGS_ERR_ARG, "kgs_exchange_setup: null buffer");
+        h->px_gathered[r] = static_cast<char*>(gathered[r]);
+        h->px_flags.row[r] = static_cast<uint32_t*>(flags[r]);
+    }
+    h->px_n = n_ranks;
+    h->px_me = my_rank;
+    h->px_slot = slot_bytes;
+    h->px_seq = 0;
+    return KGS_OK;
+}
+
+int kgs_exchange_push(kgs_handle h, void** d_gathered, size_t* bytes_per_rank) {
+    if (!h) return KGS_ERR_ARG;
+    if (h->px_n == 0) return fail(h, KGS_ERR_STATE, "kgs_exchange_push: call kgs_exchange_setup first");
+    char* src = nullptr;
+    size_t nbytes = 0;
+    int rc = exchange_source(h, "kgs_exchange_push", &src, &nbytes);
+    if (rc) return rc;
+    if (nbytes > h->px_slot)
+        return fail(h, KGS_ERR_CAPACITY, "kgs_exchange_push: the job's tables (" + std::to_string(nbytes) + " bytes) exceed slot_bytes (" +
+                                             std::to_string(h->px_slot) + ")");
+    KGS_CUDA(h, cudaSetDevice(h->device));
+    const int n = h->px_n, me = h->px_me;
+    const uint32_t seq = ++h->px_seq;
+    const int half = (int)(seq & 1u);
+    KGS_CUDA(h, cudaEventRecord(h->fin_done, h->compute));
+    KGS_CUDA(h, cudaStreamWaitEvent(h->xchg, h->fin_done, 0));
+    for (int k = 0; k < n; ++k) {   // the neighbour first: spreads the links
+        const int r = (me + 1 + k) % n;
+        char* dst = h->px_gathered[r] + ((size_t)half * n + me) * h->px_slot;
+        KGS_CUDA(h, cudaMemcpyAsync(dst, src, nbytes, cudaMemcpyDeviceToDevice, h->xchg));
+    }
+    launch(h, KGS_K_EXCHANGE, h->xchg, [&] {
+        k_peer_barrier<<<1, 32, 0, h->xchg>>>(h->px_flags, n, me, half, seq, 10ull * 1000 * 1000 * 1000, h->px_timeout);
+    });
+    KGS_CUDA(h, cudaGetLastError());
+    KGS_CUDA(h, cudaEventRecord(h->region_free[h->region_half], h->xchg));
+    h->region_busy[h->region_half] = true;
+    if (d_gathered) *d_gathered = h->px_gathered[me] + (size_t)half * n * h->px_slot;
+    if (bytes_per_rank) *bytes_per_rank = nbytes;
+    return KGS_OK;
+}
+
+int kgs_exchange_join(kgs_handle h) {
+    if (!h) return KGS_ERR_ARG;
+    KGS_CUDA(h, cudaSetDevice(h->device));
+    for (int b = 0; b < 2; ++b)
+        if (h->region_busy[b]) KGS_CUDA(h, cudaStreamWaitEvent(h->compute, h->region_free[b], 0));
+    return KGS_OK;
+}
+
+int kgs_exchange_sync(kgs_handle h) {
+    if (!h) return KGS_ERR_ARG;
+    KGS_CUDA(h, cudaSetDevice(h->device));
+    KGS_CUDA(h, cudaStreamSynchronize(h->xchg));
+    uint32_t flag = 0;
+    KGS_CUDA(h, cudaMemcpy(&flag, h->px_timeout, 4, cudaMemcpyDeviceToHost));
+    if (flag) {
+        KGS_CUDA(h, cudaMemset(h->px_timeout, 0, 4));
+        return fail(h, KGS_ERR_STATE, "kgs_exchange_sync: a peer did not reach the barrier within 10 s");
+    }
+    return KGS_OK;
+}
+
+int kgs_nccl_unique_id(void* id128) {
+    if (!id128) return KGS_ERR_ARG;
+    const NcclApi& api = nccl_api();
+    if (!api.ok) {
+        g_create_error = api.load_error ? api.load_error : "NCCL not available";
+        return KGS_ERR_STATE;
+    }
+    const int r = api.get_unique_id(id128);
+    if (r) {
+        g_create_error = std::string("ncclGetUniqueId: ") + api.get_error_string(r);
+        return KGS_ERR_CUDA;
+    }
+    return KGS_OK;
+}
+
+int kgs_nccl_init(kgs_handle h, const void* id128, int n_ranks, int rank) {
+    if (!h || !id128 || n_ranks < 1 || rank < 0 || rank >= n_ranks) return fail(h, KGS_ERR_ARG, "kgs_nccl_init: bad argument");
+    const NcclApi& api = nccl_api();
+    if (!api.ok) return fail(h, KGS_ERR_STATE, api.load_error ? api.load_error : "NCCL not available");
+    KGS_CUDA(h, cudaSetDevice(h->device));
+    if (h->nccl_comm) {
+        api.comm_destroy(h->nccl_comm);
+        h->nccl_comm = nullptr;
+    }
+    NcclApi::UniqueId id;
+    memcpy(id.bytes, id128, sizeof(id.bytes));
+    const int r = api.comm_init_rank(&h->nccl_comm, n_ranks, id, rank);
+    if (r) return fail(h, KGS_ERR_CUDA, std::string("ncclCommInitRank: ") + api.get_error_string(r));
+    return KGS_OK;
+}
+
+int kgs_exchange_nccl(kgs_handle h, void* nccl_comm, void* d_recv, size_t recv_bytes, size_t* bytes_per_rank) {
+    if (!h || !d_recv) return fail(h, KGS_ERR_ARG, "kgs_exchange_nccl: null receive buffer");
+    const NcclApi& api = nccl_api();
+    if (!api.ok) return fail(h, KGS_ERR_STATE, api.load_error ? api.load_error : "NCCL not available");
+    void* comm = nccl_comm ? nccl_comm : h->nccl_comm;
+    if (!comm) return fail(h, KGS_ERR_STATE, "kgs_exchange_nccl: no communicator (pass one, or call kgs_nccl_init)");
+    char* src = nullptr;
+    size_t nbytes = 0;
+    int rc = exchange_source(h, "kgs_exchange_nccl", &src, &nbytes);
+    if (rc) return rc;
+    if (recv_bytes < nbytes) return fail(h, KGS_ERR_CAPACITY, "kgs_exchange_nccl: receive buffer smaller than one rank's tables");
+    KGS_CUDA(h, cudaSetDevice(h->device));
+    KGS_CUDA(h, cudaEventRecord(h->fin_done, h->compute));
+    KGS_CUDA(h, cudaStreamWaitEvent(h->xchg, h->fin_done, 0));
+    const int r = api.all_gather(src, d_recv, nbytes, kNcclUint8, comm, h->xchg);
+    if (r) return fail(h, KGS_ERR_CUDA, std::string("ncclAllGather: ") + api.get_error_string(r));
+    h->launches++;
+    KGS_CUDA(h, cudaEventRecord(h->region_free[h->region_half], h->xchg));
+    h->region_busy[h->region_half] = true;
+    if (bytes_per_rank) *bytes_per_rank = nbytes;
+    return KGS_OK;
+}
+
 int kgs_segmented_mean_f64(kgs_handle h, const double* values, const uint64_t* offsets, uint64_t n_series,
                            double mul, double div, double* out) {
     if (!h) return KGS_ERR_ARG;
@@ -1358,8 +1601,8 @@ int kgs_reset_kernel_times(kgs_handle h) {
 }
 
 int kgs_stream(kgs_handle h, int which, void** out_stream) {
-    if (!h || !out_stream || which < 0 || which > 1) return KGS_ERR_ARG;
-    *out_stream = which ? (void*)h->compute : (void*)h->copy;
+    if (!h || !out_stream || which < 0 || which > 2) return KGS_ERR_ARG;
+    *out_stream = which == 2 ? (void*)h->xchg : which ? (void*)h->compute : (void*)h->copy;
     return KGS_OK;
 }
 

@@ -106,6 +106,10 @@ class Engine:
         self._ck(self._lib.kgs_reorder_batch(self._h))
         self._keep = []
 
+    def set_auto_reorder(self, on):
+        """Accumulate batches that interleave their series from a series-major copy (default on)."""
+        self._ck(self._lib.kgs_set_auto_reorder(self._h, 1 if on else 0))
+
     def fetch_batch(self):
         """The resident batch's four columns back on the host (testing / inspection)."""
         cols = [np.empty(self.n_resident, dtype=np.uint32) for _ in range(4)]
@@ -284,6 +288,45 @@ class Engine:
             out['kinds'][k] = t
         return out
 
+    # -- table exchange between the GPUs of one box (kgs_exchange_*) ---------------------
+    def exchange_setup(self, n_ranks, my_rank, gathered_ptrs, flag_ptrs, slot_bytes):
+        """Register the peer-mapped gathered buffers and flag words (device addresses valid on THIS
+        device, one per rank; see include/kgs.h)."""
+        arr = C.c_void_p * int(n_ranks)
+        self._ck(self._lib.kgs_exchange_setup(self._h, int(n_ranks), int(my_rank), arr(*[int(p) for p in gathered_ptrs]),
+                                              arr(*[int(p) for p in flag_ptrs]), int(slot_bytes)))
+
+    def exchange_push(self):
+        """Push the finalized job's tables into every rank's gathered buffer (asynchronous, exchange
+        stream).  Returns (device address of this job's gathered half on this device, bytes per rank)."""
+        p, n = C.c_void_p(), C.c_size_t()
+        self._ck(self._lib.kgs_exchange_push(self._h, C.byref(p), C.byref(n)))
+        return p.value, n.value
+
+    def exchange_join(self):
+        self._ck(self._lib.kgs_exchange_join(self._h))
+
+    def exchange_sync(self):
+        self._ck(self._lib.kgs_exchange_sync(self._h))
+
+    def nccl_unique_id(self):
+        buf = (C.c_char * 128)()
+        rc = self._lib.kgs_nccl_unique_id(buf)
+        if rc:
+            raise KgsError(rc, self._lib.kgs_last_error(None).decode())
+        return bytes(buf)
+
+    def nccl_init(self, unique_id, n_ranks, rank):
+        buf = (C.c_char * 128).from_buffer_copy(unique_id)
+        self._ck(self._lib.kgs_nccl_init(self._h, buf, int(n_ranks), int(rank)))
+
+    def exchange_nccl(self, recv_ptr, recv_bytes, comm=None):
+        """One ncclAllGather of the finalized job's tables into recv_ptr (asynchronous, exchange
+        stream); comm = a caller's ncclComm_t as an integer, None = the handle's own (nccl_init)."""
+        n = C.c_size_t()
+        self._ck(self._lib.kgs_exchange_nccl(self._h, comm, int(recv_ptr), int(recv_bytes), C.byref(n)))
+        return n.value
+
     # -- the reference's statistic ------------------------------------------------------
     def segmented_mean(self, values, offsets, mul=0.0, div=0.0):
         values = np.ascontiguousarray(values, dtype=np.float64)
@@ -356,9 +399,9 @@ class Engine:
         return out
 
     def stream(self, which='compute'):
-        """cudaStream_t of the handle's copy / compute stream as an integer."""
+        """cudaStream_t of the handle's copy / compute / exchange stream as an integer."""
         p = C.c_void_p()
-        self._ck(self._lib.kgs_stream(self._h, 1 if which == 'compute' else 0, C.byref(p)))
+        self._ck(self._lib.kgs_stream(self._h, {'copy': 0, 'compute': 1, 'exchange': 2}[which], C.byref(p)))
         return p.value or 0
 
     def mark(self, which):

@@ -211,6 +211,70 @@ class PeerTableGather(TableGather):
         return dst
 
 
+class PeerExchange:
+    """The table exchange through the C ABI (kgs_exchange_setup / kgs_exchange_push, include/kgs.h):
+    torch supplies only the peer-mapped allocation and its rendezvous (symmetric memory); the
+    pushes, the barrier kernel, the double buffering and the ordering against the next job are the
+    library's.  One call per step from the host.  Every rank's tables must fit `slot_bytes`."""
+
+    FLAG_BYTES = 4096
+
+    def __init__(self, engine, world, rank, slot_bytes, group=None):
+        import torch
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm
+        self.eng, self.world, self.rank = engine, world, rank
+        self.group = group if group is not None else dist.group.WORLD
+        self.slot = (int(slot_bytes) + 255) // 256 * 256
+        dev = torch.device('cuda', engine.device)
+        agreed = torch.tensor([self.slot], dtype=torch.int64, device=dev)
+        dist.all_reduce(agreed, op=dist.ReduceOp.MAX, group=self.group)
+        self.slot = int(agreed)
+        self.local = symm.empty(2 * world * self.slot + self.FLAG_BYTES, dtype=torch.uint8, device=dev)
+        self.local.zero_()
+        torch.cuda.synchronize(dev)
+        self.hdl = symm.rendezvous(self.local, self.group)
+        bases = [int(p) for p in self.hdl.buffer_ptrs]
+        flags = [p + 2 * world * self.slot for p in bases]
+        engine.exchange_setup(world, rank, bases, flags, self.slot)
+        self._base = bases[rank]
+        dist.barrier(group=self.group)          # nobody pushes before every rank's flag words are zero
+
+    def push(self):
+        """Queue the exchange of the finalized job; returns the [world, bytes] view of the gathered
+        tables (filled when the exchange stream has passed the push: exchange_join / exchange_sync)."""
+        ptr, nbytes = self.eng.exchange_push()
+        half = (ptr - self._base) // (self.world * self.slot)
+        a = half * self.world * self.slot
+        return self.local[a:a + self.world * self.slot].view(self.world, self.slot)[:, :nbytes]
+
+
+class NcclExchange:
+    """The same exchange as ONE ncclAllGather issued by the library (kgs_exchange_nccl) on torch's
+    communicator (or on the library's own: Engine.nccl_init).  Receive buffers alternate."""
+
+    def __init__(self, engine, world, slot_bytes, comm=None):
+        import torch
+        self.eng, self.world, self.slot, self.comm = engine, world, int(slot_bytes), comm
+        dev = torch.device('cuda', engine.device)
+        self.recv = [torch.empty(world * self.slot, dtype=torch.uint8, device=dev) for _ in range(2)]
+        self._i = 0
+
+    @staticmethod
+    def torch_comm(device):
+        """ncclComm_t of torch's default process group for `device`, as an integer."""
+        import torch
+        import torch.distributed as dist
+        backend = dist.distributed_c10d._get_default_group()._get_backend(torch.device('cuda', device))
+        return int(backend._comm_ptr())
+
+    def push(self):
+        buf = self.recv[self._i]
+        self._i ^= 1
+        n = self.eng.exchange_nccl(buf.data_ptr(), buf.numel(), self.comm)
+        return buf[:self.world * n].view(self.world, n)
+
+
 def decode_packed(buf, layout):
     """One shard's packed exchange region (uint8 array) -> {kind: {count,sum,max,mean,pct}}.
     mean and the percentiles are recomputed with the sender's own operation order (one fp64 divide;

@@ -1,7 +1,9 @@
 """Two (or more) GPUs, one process each: every rank computes the tables of its node shard with the
-CUDA path, the ranks exchange the packed tables GPU to GPU (copy-engine pushes into peer memory,
-and the NCCL all_gather), and the merged tables are held to the oracle on the GLOBAL trace, bit for
-bit.  Skipped on a box with one GPU (tests/test_sharding.py covers the host logic over gloo)."""
+CUDA path, the ranks exchange the packed tables GPU to GPU - through the library's C entry points
+(kgs_exchange_push: copy-engine pushes into peer memory + barrier kernel; kgs_exchange_nccl: one
+ncclAllGather on the library's own and on torch's communicator) and through the Python-driven
+transports of round 1 - every transport must deliver identical bytes, and the merged tables are held
+to the oracle on the GLOBAL trace, bit for bit.  Skipped on a box with one GPU (tests/test_sharding.py covers the host logic over gloo)."""
 import os
 
 import numpy as np
@@ -54,16 +56,43 @@ def _worker(rank, world, port, out_dir):
     stream = torch.cuda.ExternalStream(eng.stream('compute'), device=torch.device('cuda', rank))
     results = {}
     with torch.cuda.stream(stream):
+        eng.window_stats_device(spec)
+        eng.sync()
+        nbytes = eng.exchange_region()[1]
+        # (1) the Python-driven transports of round 1
         for name, cls in (('peer', sharding.PeerTableGather), ('nccl', sharding.TableGather)):
-            eng.window_stats_device(spec)
             gather = cls(eng, KINDS, world)
             dst = gather.all_gather()
             eng.sync()
             torch.cuda.synchronize()
-            nbytes = eng.exchange_region()[1]
             results[name] = dst.reshape(world, -1)[:, :nbytes].cpu().numpy()
+        # (2) the library's own exchange through the C ABI: peer pushes, three jobs in a row (both buffer
+        # halves and the reuse of a result region two jobs later), then NCCL on the library's own
+        # communicator and on torch's
+        px = sharding.PeerExchange(eng, world, rank, nbytes)
+        for i in range(3):
+            eng.window_stats_device(spec)
+            view = px.push()
+        eng.exchange_sync()
+        results['c_peer'] = view.cpu().numpy()
+        ids = [eng.nccl_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(ids, src=0)
+        eng.nccl_init(ids[0], world, rank)
+        own = sharding.NcclExchange(eng, world, nbytes)
+        eng.window_stats_device(spec)
+        view = own.push()
+        eng.exchange_sync()
+        results['c_nccl_own'] = view.cpu().numpy()
+        dist.barrier()
+        torch.cuda.synchronize()
+        theirs = sharding.NcclExchange(eng, world, nbytes, comm=sharding.NcclExchange.torch_comm(rank))
+        eng.window_stats_device(spec)
+        view = theirs.push()
+        eng.exchange_sync()
+        results['c_nccl_torch'] = view.cpu().numpy()
     layout = eng.packed_layout(KINDS)
-    np.testing.assert_array_equal(results['peer'], results['nccl'])
+    for name in ('nccl', 'c_peer', 'c_nccl_own', 'c_nccl_torch'):
+        np.testing.assert_array_equal(results['peer'], results[name], err_msg=name)
     if rank == 0:
         per_rank = [sharding.decode_packed(results['peer'][r], layout) for r in range(world)]
         np.savez(os.path.join(out_dir, 'tables.npz'),

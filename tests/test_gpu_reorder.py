@@ -59,3 +59,37 @@ def test_interleaved_processes_same_tables_after_reorder(engine):
         want = ws.window_stats_np(tr.ts, tr.gpu_gid, tr.pid, tr.util, tr.keys, tr.pod_ids, key_kind=kid, metric=0,
                                   gpus_per_node=8, t0=tr.t0, step=60, width=60, n_windows=30, n_keys=nk, qs=(0.5, 0.95))
         assert_stats_equal(got[kind], want, what='reordered ' + kind)
+
+
+@pytest.mark.parametrize('shape', ['procs_per_gpu', 'time_major'])
+def test_interleaved_feed_is_accumulated_from_a_sorted_copy(engine, shape):
+    """A feed that interleaves its series (8 processes of a GPU second by second; all GPUs of the box
+    second by second) is noticed at ingest and accumulated from a series-major copy: the sort runs,
+    the tables are exact, and the resident batch still answers in the caller's order."""
+    if shape == 'procs_per_gpu':
+        tr = synth.cluster_trace(2, 8, 8, 900, n_tenancies=150, pids_per_pod=2, seed=12)
+        cols = (tr.ts, tr.gpu_gid, tr.pid, tr.util)
+    else:
+        tr = synth.cluster_trace(2, 8, 1, 900, n_tenancies=20, seed=12)
+        o = np.argsort(tr.ts, kind='stable')
+        cols = (tr.ts[o], tr.gpu_gid[o], tr.pid[o], tr.util[o])
+    live = synth.Trace(*cols, tr.keys, tr.pod_ids, tr.n_pods, tr.n_nodes, 8, tr.t0, 900)
+    kw = dict(kinds=('pod', 'gpu', 'node'), metric='sm', gpus_per_node=8, t0=tr.t0, step=60, n_windows=15,
+              n_gpus=tr.n_gpus, n_nodes=tr.n_nodes, qs=(0.5, 0.95))
+    want = {kind: ws.window_stats_np(*cols, tr.keys, tr.pod_ids, key_kind=kid, metric=0, gpus_per_node=8, t0=tr.t0,
+                                     step=60, width=60, n_windows=15, n_keys=nk, qs=(0.5, 0.95))
+            for kind, kid, nk in (('pod', ws.KEY_POD, tr.n_pods), ('gpu', ws.KEY_GPU, tr.n_gpus), ('node', ws.KEY_NODE, tr.n_nodes))}
+    engine.build_join(tr.keys, tr.pod_ids, tr.n_pods)
+    engine.set_profiling(True)
+    for auto in (True, False):
+        engine.set_auto_reorder(auto)
+        engine.reset_kernel_times()
+        engine.ingest(*cols)
+        got = engine.window_stats(**kw)
+        sorts = engine.kernel_times()['reorder'][1]
+        assert (sorts > 0) == auto, 'auto %s: %d sort launches' % (auto, sorts)
+        for kind in kw['kinds']:
+            assert_stats_equal(got[kind], want[kind], what='%s auto %s %s' % (shape, auto, kind))
+        np.testing.assert_array_equal(engine.probe(8), ws.probe_np(tr.keys, tr.pod_ids, live.gpu_gid, live.pid, 8))
+        for g, w in zip(engine.fetch_batch(), cols):
+            np.testing.assert_array_equal(g, w)
