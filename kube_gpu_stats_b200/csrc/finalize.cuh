@@ -348,67 +348,72 @@ __global__ void __launch_bounds__(CellLayout::NT, 8) k_finalize_cells(const __gr
     __shared__ uint32_t hist[L::WORDS * L::NT];
     const uint32_t tid = threadIdx.x;
     const uint32_t base = (uint32_t)__cvta_generic_to_shared(hist) + tid * 4;
-    const uint32_t idx = blockIdx.x * L::NT + tid;
-    bool live = idx < P.total_cells;
-    const uint32_t gc = live ? P.total_cells - 1 - idx : 0;
-    if (live && P.done && P.done[gc] == (uint8_t)P.done_gen) live = false;   // finished by k_finalize_groups
-    uint32_t ks = 0, c = 0, pc0 = 0, vmax = 0;
-    unsigned long long count = 0;
-    if (live) {
-        const FinKind& K = kind_of_cell(P, gc, ks);
-        c = gc - K.cell_begin;
-        const uint32_t key = c / P.n_windows;
-        const uint32_t j = c - key * P.n_windows;
-        pc0 = key * P.n_panes + j;
-        unsigned long long total = 0;
-        for (uint32_t d = 0; d < P.W; ++d) {
-            count += K.cnt[pc0 + d];
-            total += K.sum[pc0 + d];
-            vmax = max(vmax, K.mx[pc0 + d]);
+    const uint32_t n_blocks = (P.total_cells + L::NT - 1) / L::NT;
+    // a CTA walks blocks of 128 cells; after k_finalize_groups most blocks have nothing left to do
+    for (uint32_t blk = blockIdx.x; blk < n_blocks; blk += gridDim.x) {
+        const uint32_t idx = blk * L::NT + tid;
+        bool live = idx < P.total_cells;
+        const uint32_t gc = live ? P.total_cells - 1 - idx : 0;
+        if (live && P.done && P.done[gc] == (uint8_t)P.done_gen) live = false;   // finished by k_finalize_groups
+        uint32_t ks = 0, c = 0, pc0 = 0, vmax = 0;
+        unsigned long long count = 0;
+        if (live) {
+            const FinKind& K = kind_of_cell(P, gc, ks);
+            c = gc - K.cell_begin;
+            const uint32_t key = c / P.n_windows;
+            const uint32_t j = c - key * P.n_windows;
+            pc0 = key * P.n_panes + j;
+            unsigned long long total = 0;
+            for (uint32_t d = 0; d < P.W; ++d) {
+                count += K.cnt[pc0 + d];
+                total += K.sum[pc0 + d];
+                vmax = max(vmax, K.mx[pc0 + d]);
+            }
+            store_basics(P, K, c, count, total, vmax);
         }
-        store_basics(P, K, c, count, total, vmax);
-    }
-    // a run log that overflowed holds incomplete lists: the host reports the error, skip selection
-    if (P.n_q == 0 || P.ctl[1]) return;
-    const FinKind& K = P.kind[ks];
-    const bool big = live && !P.u16 && count > P.thread_cell_max;
-    const bool fast = live && count > 0 && !big && vmax < (uint32_t)L::BINS && !P.u16;
-    const bool wide = live && count > 0 && !fast && !big;
-    defer_cell(P, wide, big, ks, c);
-    // Twin cells.  With one process per GPU a (gpu, window) cell and its (pod, window) cell usually
-    // consist of the very same single run, and k_accum wrote that run's descriptors side by side
-    // (pod at index i, gpu at i + 1).  The pod cell's thread then selects once and stores the
-    // percentiles in both tables; the gpu cell's thread, seeing the mirror-image condition on the
-    // same immutable lists, does nothing.  Both sides test "my list is exactly this run" AND "the
-    // sibling's list is exactly the sibling descriptor", so they always agree.  (A pair that
-    // k_finalize_groups has finished never gets here: it marks both cells or neither.)
-    bool work = fast;
-    uint32_t twin_cell = kInvalid;
-    if (fast && P.twin_pod >= 0) {
-        const uint32_t h = K.head[pc0];
-        if ((int)ks == P.twin_pod) {
-            const uint4 mine = __ldg(P.desc + (h - 1));
-            const uint4 sib = __ldg(P.desc + h);              // the gpu descriptor of the same run
-            if (mine.z == 0 && sib.z == 0 && sib.w != kInvalid && sib.x == mine.x && sib.y == mine.y &&
-                P.kind[P.twin_gpu].head[sib.w] == h + 1)
-                twin_cell = sib.w;
-        } else if ((int)ks == P.twin_gpu && h >= 2) {
-            const uint4 mine = __ldg(P.desc + (h - 1));
-            const uint4 sib = __ldg(P.desc + (h - 2));        // the pod descriptor of the same run
-            if (mine.z == 0 && sib.z == 0 && sib.w != kInvalid && sib.x == mine.x && sib.y == mine.y &&
-                P.kind[P.twin_pod].head[sib.w] == h - 1)
-                work = false;                                  // the pod cell's thread stores my percentiles
+        // a run log that overflowed holds incomplete lists: the host reports the error, skip selection
+        if (P.n_q == 0 || P.ctl[1]) continue;
+        const FinKind& K = P.kind[ks];
+        const bool big = live && !P.u16 && count > P.thread_cell_max;
+        const bool fast = live && count > 0 && !big && vmax < (uint32_t)L::BINS && !P.u16;
+        const bool wide = live && count > 0 && !fast && !big;
+        defer_cell(P, wide, big, ks, c);
+        // Twin cells.  With one process per GPU a (gpu, window) cell and its (pod, window) cell usually
+        // consist of the very same single run, and k_accum wrote that run's descriptors side by side
+        // (pod at index i, gpu at i + 1).  The pod cell's thread then selects once and stores the
+        // percentiles in both tables; the gpu cell's thread, seeing the mirror-image condition on the
+        // same immutable lists, does nothing.  Both sides test "my list is exactly this run" AND "the
+        // sibling's list is exactly the sibling descriptor", so they always agree.  (A pair that
+        // k_finalize_groups has finished never gets here: it marks both cells or neither.)
+        bool work = fast;
+        uint32_t twin_cell = kInvalid;
+        if (fast && P.twin_pod >= 0) {
+            const uint32_t h = K.head[pc0];
+            if ((int)ks == P.twin_pod) {
+                const uint4 mine = __ldg(P.desc + (h - 1));
+                const uint4 sib = __ldg(P.desc + h);              // the gpu descriptor of the same run
+                if (mine.z == 0 && sib.z == 0 && sib.w != kInvalid && sib.x == mine.x && sib.y == mine.y &&
+                    P.kind[P.twin_gpu].head[sib.w] == h + 1)
+                    twin_cell = sib.w;
+            } else if ((int)ks == P.twin_gpu && h >= 2) {
+                const uint4 mine = __ldg(P.desc + (h - 1));
+                const uint4 sib = __ldg(P.desc + (h - 2));        // the pod descriptor of the same run
+                if (mine.z == 0 && sib.z == 0 && sib.w != kInvalid && sib.x == mine.x && sib.y == mine.y &&
+                    P.kind[P.twin_pod].head[sib.w] == h - 1)
+                    work = false;                                  // the pod cell's thread stores my percentiles
+            }
         }
-    }
-    if (!__syncthreads_or(work)) return;   // nothing to count in this CTA (the usual case after k_finalize_groups)
-    {   // clear the CTA's histograms together (STS.128)
-        uint4* z = reinterpret_cast<uint4*>(hist);
+        // (this barrier also separates the previous block's selection from the clearing below)
+        if (!__syncthreads_or(work)) continue;   // nothing to count in this block (the usual case after k_finalize_groups)
+        {   // clear the CTA's histograms together (STS.128)
+            uint4* z = reinterpret_cast<uint4*>(hist);
 #pragma unroll
-        for (int i = 0; i < L::WORDS / 4; ++i) z[i * L::NT + tid] = make_uint4(0, 0, 0, 0);
-        __syncthreads();
+            for (int i = 0; i < L::WORDS / 4; ++i) z[i * L::NT + tid] = make_uint4(0, 0, 0, 0);
+            __syncthreads();
+        }
+        add_cell<L>(base, P, K, pc0, work);   // warp-synchronous: every lane takes part
+        if (work) select_store<L>(base, P, K, c, (uint32_t)count, vmax, twin_cell);
     }
-    add_cell<L>(base, P, K, pc0, work);   // warp-synchronous: every lane takes part
-    if (work) select_store<L>(base, P, K, c, (uint32_t)count, vmax, twin_cell);
 }
 
 // The wide list: values up to 255 (u16 bins, 256 values), at most 65 535 samples per cell.

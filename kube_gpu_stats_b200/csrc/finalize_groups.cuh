@@ -7,7 +7,9 @@
 // cell one thread which loads the cell's bytes ONCE and uses them three times:
 //   * its own percentiles,
 //   * the percentiles of the (pod, window) cell that consists of the very same run (one process
-//     per GPU: the usual case; k_accum wrote the pod descriptor right before the gpu descriptor),
+//     per GPU: the usual case; k_accum wrote the pod descriptor right before the gpu descriptor) -
+//     and, in a window where the tenant changed, of the two pods' cells, each a sub-range of the
+//     bytes the lane already holds,
 //   * together with the other GPUs of its node - the threads of one (node, window) GROUP are
 //     neighbouring lanes - the percentiles of the (node, window) cell, by summing the lanes' counts
 //     with warp shuffles.
@@ -99,27 +101,32 @@ __global__ void __launch_bounds__(kGroupThreads) k_finalize_groups(const __grid_
         h = G.head[c];
     }
     // the cell's runs: at most four, together one contiguous piece of the value log
-    bool ok = true, single = false;
-    uint32_t start = 0;
-    uint4 d0 = make_uint4(0, 0, 0, 0);
+    bool ok = true;
+    uint32_t start = 0, runs = 0;
+    uint32_t run_at[4] = {0, 0, 0, 0}, run_start[4] = {0, 0, 0, 0}, run_len[4] = {0, 0, 0, 0};   // constant indices only
     if (count) {
         ok = count <= kGroupMaxCount && vmax < 128u;
         if (ok) {
-            uint32_t at = h, lo = 0xFFFFFFFFu, hi = 0, tot = 0, runs = 0;
-            while (at && runs < 4) {
-                const uint4 d = __ldg(P.desc + (at - 1));
-                if (runs == 0) d0 = d;
-                lo = min(lo, d.x);
-                hi = max(hi, d.x + d.y);
-                tot += d.y;
-                at = d.z;
-                ++runs;
+            uint32_t at = h, lo = 0xFFFFFFFFu, hi = 0, tot = 0;
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                if (at) {
+                    const uint4 d = __ldg(P.desc + (at - 1));
+                    run_at[r] = at;
+                    run_start[r] = d.x;
+                    run_len[r] = d.y;
+                    lo = min(lo, d.x);
+                    hi = max(hi, d.x + d.y);
+                    tot += d.y;
+                    at = d.z;
+                    ++runs;
+                }
             }
             ok = at == 0 && tot == count && hi - lo == count;
             start = lo;
-            single = runs == 1;
         }
     }
+    const bool single = ok && runs == 1;
     const uint32_t n = (ok && count) ? count : 0;    // values this lane holds
     uint32_t x[kGroupWords];
     {
@@ -141,7 +148,7 @@ __global__ void __launch_bounds__(kGroupThreads) k_finalize_groups(const __grid_
     uint32_t twin = kInvalid;
     if (mine && count && single && P.g_pod >= 0 && h >= 2) {
         const uint4 sib = __ldg(P.desc + (h - 2));   // the pod descriptor of the same run
-        if (sib.z == 0 && sib.w != kInvalid && sib.x == d0.x && sib.y == d0.y && P.kind[P.g_pod].head[sib.w] == h - 1)
+        if (sib.z == 0 && sib.w != kInvalid && sib.x == run_start[0] && sib.y == run_len[0] && P.kind[P.g_pod].head[sib.w] == h - 1)
             twin = sib.w;
     }
     if (mine) {
@@ -168,6 +175,62 @@ __global__ void __launch_bounds__(kGroupThreads) k_finalize_groups(const __grid_
             if (mine && n) {
                 store_pct(P, G, c, iq, vlo, vhi, w);
                 if (twin != kInvalid) store_pct(P, P.kind[P.g_pod], twin, iq, vlo, vhi, w);
+            }
+        }
+    }
+    // ---- a window in which the tenant changed: the cell is two to four runs, each of which is (usually) the
+    // whole of a (pod, window) cell - a sub-range of the bytes this lane already holds -----------------------
+    if (P.g_pod >= 0) {                              // warp-uniform
+        const FinKind& K = P.kind[P.g_pod];
+        const bool multi = mine && n && runs >= 2;
+        if (__any_sync(kAll, multi)) {
+#pragma unroll 1
+            for (uint32_t r = 0; r < 4; ++r) {
+                const uint32_t at = r == 0 ? run_at[0] : r == 1 ? run_at[1] : r == 2 ? run_at[2] : run_at[3];
+                const uint32_t rs = r == 0 ? run_start[0] : r == 1 ? run_start[1] : r == 2 ? run_start[2] : run_start[3];
+                const uint32_t rl = r == 0 ? run_len[0] : r == 1 ? run_len[1] : r == 2 ? run_len[2] : run_len[3];
+                uint32_t pcell = kInvalid, pn = 0, pmax = 0;
+                unsigned long long ptotal = 0;
+                if (multi && r < runs && at >= 2) {
+                    const uint4 sib = __ldg(P.desc + (at - 2));   // the pod descriptor of this run
+                    if (sib.z == 0 && sib.w != kInvalid && sib.x == rs && sib.y == rl && K.head[sib.w] == at - 1) {
+                        pcell = sib.w;
+                        pn = K.cnt[pcell];
+                        ptotal = K.sum[pcell];
+                        pmax = K.mx[pcell];
+                        if (pn != rl) pcell = kInvalid;          // cannot happen for a single-run cell; stay safe
+                    }
+                }
+                const bool here = pcell != kInvalid;
+                if (!__any_sync(kAll, here)) continue;
+                uint32_t y[kGroupWords];
+                {
+                    const int b0 = here ? (int)(rs - (start & ~3u)) : 0, b1 = here ? b0 + (int)rl : 0;   // bytes [b0, b1) of x
+#pragma unroll
+                    for (int k = 0; k < kGroupWords; ++k) {
+                        const int lo = b0 - 4 * k, hi = b1 - 4 * k;
+                        uint32_t m = hi >= 4 ? 0xFFFFFFFFu : (hi <= 0 ? 0u : (0xFFFFFFFFu >> (8 * (4 - hi))));
+                        if (lo > 0) m &= lo >= 4 ? 0u : (0xFFFFFFFFu << (8 * lo));
+                        y[k] = x[k] & m;
+                    }
+                }
+                if (here) {
+                    store_basics(P, K, pcell, pn, ptotal, pmax);
+                    P.done[K.cell_begin + pcell] = (uint8_t)P.done_gen;
+                }
+                for (uint32_t iq = 0; iq < P.n_q; ++iq) {
+                    uint32_t ilo = 0, ihi = 0;
+                    double w = 0.0;
+                    if (here) pct_ranks(P.q[iq], pn, ilo, ihi, w);
+                    const uint32_t nn = here ? pn : 1u;
+                    const uint32_t vlo = rank_select<false>(y, (uint32_t)ptotal, nn, ilo, gs);
+                    uint32_t vhi = vlo;
+                    if (__any_sync(kAll, ihi != ilo)) {
+                        const uint32_t v2 = rank_select<false>(y, (uint32_t)ptotal, nn, ihi, gs);
+                        if (ihi != ilo) vhi = v2;
+                    }
+                    if (here) store_pct(P, K, pcell, iq, vlo, vhi, w);
+                }
             }
         }
     }

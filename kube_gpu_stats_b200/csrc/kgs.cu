@@ -1049,8 +1049,8 @@ int kgs_stats_finalize(kgs_handle h) {
                 if (grid) launch(h, KGS_K_FINALIZE, st, [&] { k_finalize_slide<<<grid, CellLayout::NT, 0, st>>>(P); });
             }
         } else {
-            launch(h, KGS_K_FINALIZE, st, [&] {
-                k_finalize_cells<<<(cells + CellLayout::NT - 1) / CellLayout::NT, CellLayout::NT, 0, st>>>(P);
+            launch(h, KGS_K_FINALIZE, st, [&] {   // at most one wave of CTAs (8 per SM), each walking blocks of cells
+                k_finalize_cells<<<grid_for(cells, CellLayout::NT, 148 * 8), CellLayout::NT, 0, st>>>(P);
             });
         }
         if (sp.n_q && sp.metric == KGS_METRIC_FB) {   // 16-bit values: two-digit radix select, warp per cell
