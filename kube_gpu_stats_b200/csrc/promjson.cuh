@@ -312,7 +312,7 @@ __global__ void __launch_bounds__(128) k_mx_parse(const __grid_constant__ MxPara
         // (the text is padded with zero bytes, so the digit loops stop inside the buffer)
         const char* p = s + open + 1;
         const uint32_t a = parse_short_decimal(p, &ts);
-        if (a && p[a] == ',' && p[a + 1] == '"') {
+        if (a && p[a] == ',' && p[a + 1] == '"' && json_number_ok(p, a)) {   // the timestamp is a bare JSON number
             const char* q = p + a + 2;
             const uint32_t b = parse_short_decimal(q, &v);
             if (b && q[b] == '"' && q[b + 1] == ']') {
@@ -327,7 +327,7 @@ __global__ void __launch_bounds__(128) k_mx_parse(const __grid_constant__ MxPara
     while (i < n && mx_blank(s[i])) ++i;
     unsigned long long a = i;
     while (i < n && s[i] != ',' && s[i] != ']' && !mx_blank(s[i])) ++i;
-    ok = ok && i > a && i - a < 4096 && parse_float(s + a, (uint32_t)(i - a), &ts);
+    ok = ok && i > a && i - a < 4096 && json_number_ok(s + a, (uint32_t)(i - a)) && parse_float(s + a, (uint32_t)(i - a), &ts);
     while (i < n && mx_blank(s[i])) ++i;
     ok = ok && i < n && s[i] == ',';
     ++i;
@@ -340,7 +340,7 @@ __global__ void __launch_bounds__(128) k_mx_parse(const __grid_constant__ MxPara
     } else {
         a = i;
         while (i < n && s[i] != ',' && s[i] != ']' && !mx_blank(s[i])) ++i;
-        ok = ok && i > a && i - a < 4096 && parse_float(s + a, (uint32_t)(i - a), &v);
+        ok = ok && i > a && i - a < 4096 && json_number_ok(s + a, (uint32_t)(i - a)) && parse_float(s + a, (uint32_t)(i - a), &v);
     }
     while (i < n && mx_blank(s[i])) ++i;
     ok = ok && i < n && s[i] == ']';

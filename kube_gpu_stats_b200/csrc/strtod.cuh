@@ -3,8 +3,9 @@
 //
 // CPython's float() is David Gay's correctly rounded strtod; to be bit-identical this has to be
 // correctly rounded too, for every input.  Three steps:
-//   1. scan the token with Python's float() grammar (sign, digits with '.' and single underscores
-//      between digits, exponent, inf / infinity / nan in any case, blanks around) into at most 19
+//   1. scan the token with the float() grammar of Python 2, the reference's interpreter (sign, digits
+//      with '.', exponent, inf / infinity / nan in any case, blanks around; the underscores Python 3.6
+//      added are refused, as Python 2 refuses them) into at most 19
 //      significant digits w, a decimal exponent q and a "digits were dropped" flag;
 //   2. Eisel-Lemire: w * 5^q from a 128-bit table of powers of five, one or two 64x64->128
 //      multiplications; for w of at most 19 digits this is always decisive (Mushtak & Lemire,
@@ -273,7 +274,41 @@ KGS_HD inline bool word_is(const char* s, uint32_t a, uint32_t b, const char* w,
     return true;
 }
 
-// Python float(str) for the ASCII token s[0, len).  false = float() would raise ValueError (or a
+// A BARE number of a JSON text as json.loads reads it (the timestamps of an answer, and a value that is
+// not a string): -?(0|[1-9][0-9]*)(.[0-9]+)?([eE][+-]?[0-9]+)? or one of NaN, Infinity, -Infinity,
+// which Python's json accepts beyond the standard.  What float() would also take - '+1', '.5', '5.',
+// '007', 'nan' - makes the reference's .json() raise, so it is refused here too.
+KGS_HD inline bool json_number_ok(const char* s, uint32_t len) {
+    uint32_t i = 0;
+    if (len == 3 && s[0] == 'N' && s[1] == 'a' && s[2] == 'N') return true;
+    if (i < len && s[i] == '-') ++i;
+    if (len - i == 8) {
+        const char* w = "Infinity";
+        bool same = true;
+        for (uint32_t k = 0; k < 8; ++k) same = same && s[i + k] == w[k];
+        if (same) return true;
+    }
+    if (i >= len || s[i] < '0' || s[i] > '9') return false;
+    if (s[i] == '0') {
+        ++i;
+    } else {
+        while (i < len && s[i] >= '0' && s[i] <= '9') ++i;
+    }
+    if (i < len && s[i] == '.') {
+        ++i;
+        if (i >= len || s[i] < '0' || s[i] > '9') return false;
+        while (i < len && s[i] >= '0' && s[i] <= '9') ++i;
+    }
+    if (i < len && (s[i] == 'e' || s[i] == 'E')) {
+        ++i;
+        if (i < len && (s[i] == '+' || s[i] == '-')) ++i;
+        if (i >= len || s[i] < '0' || s[i] > '9') return false;
+        while (i < len && s[i] >= '0' && s[i] <= '9') ++i;
+    }
+    return i == len;
+}
+
+// float(str) of Python 2 for the ASCII token s[0, len).  false = float() would raise ValueError (or a
 // multi-word number did not fit, which no finite input reaches).
 KGS_HD inline bool parse_float(const char* s, uint32_t len, double* out) {
     uint32_t i = 0, end = len;
@@ -311,9 +346,6 @@ KGS_HD inline bool parse_float(const char* s, uint32_t len, double* out) {
                     trunc |= dg != 0;
                     if (!point) ++e10;
                 }
-            } else if (c == '_') {
-                if (!prev_digit || i + 1 >= end || !is_digit(s[i + 1])) return false;
-                prev_digit = false;
             } else if (c == '.' && !point) {
                 point = true;
                 prev_digit = false;
@@ -339,9 +371,6 @@ KGS_HD inline bool parse_float(const char* s, uint32_t len, double* out) {
                     eseen = true;
                     prev_digit = true;
                     if (e < 100000000) e = e * 10 + (c - '0');
-                } else if (c == '_') {
-                    if (!prev_digit || i + 1 >= end || !is_digit(s[i + 1])) return false;
-                    prev_digit = false;
                 } else {
                     break;
                 }

@@ -39,6 +39,7 @@ class Engine:
         self._n_keys = {}
         self.n_resident = 0
         self._matrix = (0, 0)
+        self.matrix_generation = 0   # bumped by every matrix_parse: a holder of a decoded answer can tell it is still resident
 
     # -- plumbing ---------------------------------------------------------------------
     def _ck(self, rc):
@@ -353,6 +354,7 @@ class Engine:
         kind = {'matrix': _ffi.RESULT_MATRIX, 'vector': _ffi.RESULT_VECTOR}[result_type]
         ns, nv = C.c_uint64(), C.c_uint64()
         self._matrix = (0, 0)
+        self.matrix_generation += 1
         rc = self._lib.kgs_matrix_parse(self._h, addr, nbytes, kind, C.byref(ns), C.byref(nv))
         if rc == _ffi.KGS_ERR_PARSE:
             raise ValueError(self._lib.kgs_last_error(self._h).decode())

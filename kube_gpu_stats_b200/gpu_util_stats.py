@@ -110,6 +110,25 @@ class _Series(dict):
             raise KeyError(key)
         return self._owner.values_of(self._index)
 
+    # the reference's decoded JSON has 'values' as an ordinary key: answer the usual dict questions the same way
+    def __contains__(self, key):
+        return key == 'values' or super().__contains__(key)
+
+    def get(self, key, default=None):
+        return self['values'] if key == 'values' else super().get(key, default)
+
+    def keys(self):
+        return list(super().keys()) + ['values']
+
+    def __iter__(self):
+        return iter(self.keys())
+
+    def __len__(self):
+        return super().__len__() + 1
+
+    def items(self):
+        return [(k, self[k]) for k in self.keys()]
+
 
 def answer_skeleton(raw, spans):
     """The answer's text with the inside of every ``values`` array cut out: what is left (status,
@@ -130,7 +149,6 @@ class MatrixAnswer(dict):
     """A /query_range answer decoded by ``kgs_matrix_parse`` (GUS:25 ``.json()`` + GUS:47-48,
     GUS:73-74 ``float(val[1])``).  Looks like the reference's decoded JSON; the per-sample numbers
     stay on the GPU as a CSR in series order."""
-    _generation = 0
 
     def __init__(self, body):
         self.raw = bytes(body)
@@ -148,14 +166,15 @@ class MatrixAnswer(dict):
             result[i] = _Series(fields, self, i) if had else fields
 
     def _parse(self):
-        self.n_series, self.n_samples = engine().matrix_parse(self.raw, 'matrix')
-        MatrixAnswer._generation += 1
-        self._mine = MatrixAnswer._generation
+        eng = engine()
+        self.n_series, self.n_samples = eng.matrix_parse(self.raw, 'matrix')
+        self._mine = (id(eng), eng.matrix_generation)      # the engine counts every decode, whoever asked for it
 
     def _resident(self):
-        if self._mine != MatrixAnswer._generation:     # another answer was decoded since
+        eng = engine()
+        if self._mine != (id(eng), eng.matrix_generation):   # another answer was decoded since (or the engine is new)
             self._parse()
-        return engine()
+        return eng
 
     def values_of(self, index):
         so, vo, vc, sc = (int(x) for x in self.spans[index])

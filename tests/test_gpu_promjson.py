@@ -84,7 +84,7 @@ def test_strings_that_look_like_structure(engine):
 
 
 def test_value_grammar_is_floats(engine):
-    toks = ['NaN', '+Inf', '-Inf', 'inf', 'nan', 'Infinity', '1e5', '1E-5', '.5', '5.', '1_000', ' 7 ', '+3', '-0', '0.1', '0.30000000000000004',
+    toks = ['NaN', '+Inf', '-Inf', 'inf', 'nan', 'Infinity', '1e5', '1E-5', '.5', '5.', ' 7 ', '+3', '-0', '0.1', '0.30000000000000004',
             '999999999999999', '9999999999999999', '-.5', '00012.50', '0.000000000000001', '123456789.123456', '1234567890.123456', '2.675', '-0.0',
             '4.9406564584124654e-324', '2.4703282292062328e-324', '1.7976931348623157e308', '1.7976931348623159e308', '1e400',
             '9007199254740993', '9007199254740992.5', '9007199254740993.0000000000000000000000001', '123456789012345678901234567890',
@@ -105,6 +105,13 @@ def test_value_grammar_is_floats(engine):
 @pytest.mark.parametrize('bad,where', [
     ('{"data":{"result":[{"metric":{},"values":[[1,"abc"]]}]}}', 'malformed sample'),
     ('{"data":{"result":[{"metric":{},"values":[[1,"1__0"]]}]}}', 'malformed sample'),
+    ('{"data":{"result":[{"metric":{},"values":[[1,"1_000"]]}]}}', 'malformed sample'),     # Python 2's float() has no underscores
+    ('{"data":{"result":[{"metric":{},"values":[[+1,"2"]]}]}}', 'malformed sample'),        # bare numbers follow json.loads, not float()
+    ('{"data":{"result":[{"metric":{},"values":[[.5,"2"]]}]}}', 'malformed sample'),
+    ('{"data":{"result":[{"metric":{},"values":[[5.,"2"]]}]}}', 'malformed sample'),
+    ('{"data":{"result":[{"metric":{},"values":[[007,"2"]]}]}}', 'malformed sample'),
+    ('{"data":{"result":[{"metric":{},"values":[[nan,"2"]]}]}}', 'malformed sample'),
+    ('{"data":{"result":[{"metric":{},"values":[[1, 0x10]]}]}}', 'malformed sample'),
     ('{"data":{"result":[{"metric":{},"values":[[1,"1\\u0030"]]}]}}', 'malformed sample'),
     ('{"data":{"result":[{"metric":{},"values":[[1,null]]}]}}', 'malformed sample'),
     ('{"data":{"result":[{"metric":{},"values":[[1]]}]}}', 'malformed sample'),

@@ -31,6 +31,10 @@ def checker(tmp_path_factory):
 
 
 def expected(token):
+    """float() of Python 2, the reference's interpreter: Python 3's float() minus the underscores that
+    3.6 added (everything else about the grammar and the rounding is the same since 2.7)."""
+    if '_' in token:
+        return (0, 0)
     try:
         v = float(token)
     except ValueError:
