@@ -79,7 +79,23 @@ __device__ __forceinline__ uint32_t rank_select(const uint32_t (&x)[kGroupWords]
     return ans;
 }
 
-__global__ void __launch_bounds__(kGroupThreads) k_finalize_groups(const __grid_constant__ FinParams P) {
+// The lane's bytes [b0, b1) of the 4 * kGroupWords bytes that start at the word holding log position `start`.
+__device__ __forceinline__ void load_values(const FinParams& P, uint32_t start, uint32_t b0, uint32_t b1,
+                                            uint32_t (&x)[kGroupWords]) {
+    const uint32_t w0 = start & ~3u;
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(P.vals + w0);
+#pragma unroll
+    for (int k = 0; k < kGroupWords; ++k) {
+        const int lo = (int)b0 - 4 * k, hi = (int)b1 - 4 * k;          // valid bytes of this word: [lo, hi)
+        uint32_t w = 0;
+        if (hi > 0 && lo < 4) w = __ldg(src + k);
+        uint32_t m = hi >= 4 ? 0xFFFFFFFFu : (hi <= 0 ? 0u : (0xFFFFFFFFu >> (8 * (4 - hi))));
+        if (lo > 0) m &= lo >= 4 ? 0u : (0xFFFFFFFFu << (8 * lo));
+        x[k] = w & m;
+    }
+}
+
+__global__ void __launch_bounds__(kGroupThreads, 8) k_finalize_groups(const __grid_constant__ FinParams P) {
     constexpr uint32_t kAll = 0xFFFFFFFFu;
     if (P.ctl[1]) return;                            // overflowed run log: lists are incomplete, the host reports it
     const uint32_t gs = 1u << P.g_gs_log2;
@@ -100,21 +116,25 @@ __global__ void __launch_bounds__(kGroupThreads) k_finalize_groups(const __grid_
         vmax = G.mx[c];
         h = G.head[c];
     }
-    // the cell's runs: at most four, together one contiguous piece of the value log
+    // the cell's runs: at most four, together one contiguous piece of the value log; with the pod table
+    // in the job, the pod descriptor of a run sits right before its gpu descriptor (k_accum, emit_run)
     bool ok = true;
     uint32_t start = 0, runs = 0;
-    uint32_t run_at[4] = {0, 0, 0, 0}, run_start[4] = {0, 0, 0, 0}, run_len[4] = {0, 0, 0, 0};   // constant indices only
+    uint32_t run_start[4] = {0, 0, 0, 0}, run_len[4] = {0, 0, 0, 0}, run_pod[4] = {kInvalid, kInvalid, kInvalid, kInvalid};
     if (count) {
         ok = count <= kGroupMaxCount && vmax < 128u;
         if (ok) {
             uint32_t at = h, lo = 0xFFFFFFFFu, hi = 0, tot = 0;
 #pragma unroll
-            for (int r = 0; r < 4; ++r) {
+            for (int r = 0; r < 4; ++r) {            // constant indices: the arrays stay in registers
                 if (at) {
                     const uint4 d = __ldg(P.desc + (at - 1));
-                    run_at[r] = at;
                     run_start[r] = d.x;
                     run_len[r] = d.y;
+                    if (P.g_pod >= 0 && at >= 2) {
+                        const uint4 sib = __ldg(P.desc + (at - 2));
+                        if (sib.x == d.x && sib.y == d.y) run_pod[r] = sib.w;     // pod cell of this run (kInvalid: no pod)
+                    }
                     lo = min(lo, d.x);
                     hi = max(hi, d.x + d.y);
                     tot += d.y;
@@ -126,30 +146,25 @@ __global__ void __launch_bounds__(kGroupThreads) k_finalize_groups(const __grid_
             start = lo;
         }
     }
-    const bool single = ok && runs == 1;
     const uint32_t n = (ok && count) ? count : 0;    // values this lane holds
     uint32_t x[kGroupWords];
-    {
-        const uint32_t w0 = start & ~3u, end = start + n;
-        const uint32_t* src = reinterpret_cast<const uint32_t*>(P.vals + w0);
-#pragma unroll
-        for (int k = 0; k < kGroupWords; ++k) {
-            uint32_t w = 0;
-            if (w0 + 4u * k < end) w = __ldg(src + k);
-            const int e = (int)(end - (w0 + 4u * k));           // valid bytes of this word end at byte e
-            uint32_t m = e >= 4 ? 0xFFFFFFFFu : (e <= 0 ? 0u : (0xFFFFFFFFu >> (8 * (4 - e))));
-            if (k == 0) m &= 0xFFFFFFFFu << (8 * (start & 3u));
-            x[k] = w & m;
-        }
-    }
+    load_values(P, start, start & 3u, (start & 3u) + n, x);
     const uint32_t byte_total = n ? (uint32_t)total : 0u;
-    // ---- this GPU's cell, and the pod cell made of the same run ---------------------------------------
+    // ---- this GPU's cell, and the pod cell that holds exactly the same samples ----------------------------
+    // A pod cell whose count equals the length of the runs of mine that carry its id consists of those runs
+    // and nothing else.  Usually that is the whole cell (one process per GPU; a run cut in two where one
+    // warp's share of the input ended is still one pod): the pod cell gets my numbers.
     const bool mine = have && (count == 0 || ok);    // this thread finishes its gpu cell
     uint32_t twin = kInvalid;
-    if (mine && count && single && P.g_pod >= 0 && h >= 2) {
-        const uint4 sib = __ldg(P.desc + (h - 2));   // the pod descriptor of the same run
-        if (sib.z == 0 && sib.w != kInvalid && sib.x == run_start[0] && sib.y == run_len[0] && P.kind[P.g_pod].head[sib.w] == h - 1)
-            twin = sib.w;
+    bool split = false;                              // my runs belong to different pods: the tenant changed in this window
+    if (mine && n && P.g_pod >= 0) {
+        const bool same = (runs < 2 || run_pod[1] == run_pod[0]) && (runs < 3 || run_pod[2] == run_pod[0]) &&
+                          (runs < 4 || run_pod[3] == run_pod[0]);
+        if (same) {
+            if (run_pod[0] != kInvalid && P.kind[P.g_pod].cnt[run_pod[0]] == count) twin = run_pod[0];
+        } else {
+            split = true;
+        }
     }
     if (mine) {
         store_basics(P, G, c, count, total, vmax);
@@ -178,100 +193,96 @@ __global__ void __launch_bounds__(kGroupThreads) k_finalize_groups(const __grid_
             }
         }
     }
-    // ---- a window in which the tenant changed: the cell is two to four runs, each of which is (usually) the
-    // whole of a (pod, window) cell - a sub-range of the bytes this lane already holds -----------------------
-    if (P.g_pod >= 0) {                              // warp-uniform
-        const FinKind& K = P.kind[P.g_pod];
-        const bool multi = mine && n && runs >= 2;
-        if (__any_sync(kAll, multi)) {
-#pragma unroll 1
-            for (uint32_t r = 0; r < 4; ++r) {
-                const uint32_t at = r == 0 ? run_at[0] : r == 1 ? run_at[1] : r == 2 ? run_at[2] : run_at[3];
-                const uint32_t rs = r == 0 ? run_start[0] : r == 1 ? run_start[1] : r == 2 ? run_start[2] : run_start[3];
-                const uint32_t rl = r == 0 ? run_len[0] : r == 1 ? run_len[1] : r == 2 ? run_len[2] : run_len[3];
-                uint32_t pcell = kInvalid, pn = 0, pmax = 0;
-                unsigned long long ptotal = 0;
-                if (multi && r < runs && at >= 2) {
-                    const uint4 sib = __ldg(P.desc + (at - 2));   // the pod descriptor of this run
-                    if (sib.z == 0 && sib.w != kInvalid && sib.x == rs && sib.y == rl && K.head[sib.w] == at - 1) {
-                        pcell = sib.w;
-                        pn = K.cnt[pcell];
-                        ptotal = K.sum[pcell];
-                        pmax = K.mx[pcell];
-                        if (pn != rl) pcell = kInvalid;          // cannot happen for a single-run cell; stay safe
-                    }
+    // ---- the node's cell: the lanes of a group hold its values between them ----------------------------
+    if (P.g_node >= 0) {                             // warp-uniform
+        const FinKind& N = P.kind[P.g_node];
+        const uint32_t group_lanes = (gs == 32 ? kAll : ((1u << gs) - 1u)) << (lane & ~(gs - 1));
+        const bool lanes_ok = (__ballot_sync(kAll, ok) & group_lanes) == group_lanes;
+        const uint32_t held = group_sum(n, gs);
+        const bool node_here = l == 0 && node < P.g_nodes && node < N.n_keys;
+        const uint32_t nc = node * P.n_windows + j;
+        uint32_t ncount = 0, nmax = 0;
+        unsigned long long ntotal = 0;
+        if (node_here) {
+            ncount = N.cnt[nc];
+            ntotal = N.sum[nc];
+            nmax = N.mx[nc];
+        }
+        // every sample of the node cell must be in some lane's registers (a GPU outside the gpu table's
+        // domain, or a cell some lane could not take, leaves the node cell to k_finalize_cells)
+        const bool node_fast = node_here && lanes_ok && ncount == held;
+        if (node_fast) {
+            store_basics(P, N, nc, ncount, ntotal, nmax);
+            P.done[N.cell_begin + nc] = (uint8_t)P.done_gen;
+        }
+        const uint32_t base_lane = lane & ~(gs - 1);
+        const bool group_fast = __shfl_sync(kAll, (uint32_t)(node_fast && ncount > 0), base_lane) != 0;
+        if (__any_sync(kAll, group_fast)) {
+            const uint32_t gn = __shfl_sync(kAll, ncount, base_lane);
+            for (uint32_t iq = 0; iq < P.n_q; ++iq) {
+                uint32_t ilo = 0, ihi = 0;
+                double w = 0.0;
+                if (group_fast) pct_ranks(P.q[iq], gn, ilo, ihi, w);   // same n in every lane of the group: same ranks
+                const uint32_t nn = group_fast ? gn : 1u;
+                const uint32_t vlo = rank_select<true>(x, byte_total, nn, ilo, gs);
+                uint32_t vhi = vlo;
+                if (__any_sync(kAll, ihi != ilo)) {
+                    const uint32_t v2 = rank_select<true>(x, byte_total, nn, ihi, gs);
+                    if (ihi != ilo) vhi = v2;
                 }
-                const bool here = pcell != kInvalid;
-                if (!__any_sync(kAll, here)) continue;
-                uint32_t y[kGroupWords];
-                {
-                    const int b0 = here ? (int)(rs - (start & ~3u)) : 0, b1 = here ? b0 + (int)rl : 0;   // bytes [b0, b1) of x
-#pragma unroll
-                    for (int k = 0; k < kGroupWords; ++k) {
-                        const int lo = b0 - 4 * k, hi = b1 - 4 * k;
-                        uint32_t m = hi >= 4 ? 0xFFFFFFFFu : (hi <= 0 ? 0u : (0xFFFFFFFFu >> (8 * (4 - hi))));
-                        if (lo > 0) m &= lo >= 4 ? 0u : (0xFFFFFFFFu << (8 * lo));
-                        y[k] = x[k] & m;
-                    }
-                }
-                if (here) {
-                    store_basics(P, K, pcell, pn, ptotal, pmax);
-                    P.done[K.cell_begin + pcell] = (uint8_t)P.done_gen;
-                }
-                for (uint32_t iq = 0; iq < P.n_q; ++iq) {
-                    uint32_t ilo = 0, ihi = 0;
-                    double w = 0.0;
-                    if (here) pct_ranks(P.q[iq], pn, ilo, ihi, w);
-                    const uint32_t nn = here ? pn : 1u;
-                    const uint32_t vlo = rank_select<false>(y, (uint32_t)ptotal, nn, ilo, gs);
-                    uint32_t vhi = vlo;
-                    if (__any_sync(kAll, ihi != ilo)) {
-                        const uint32_t v2 = rank_select<false>(y, (uint32_t)ptotal, nn, ihi, gs);
-                        if (ihi != ilo) vhi = v2;
-                    }
-                    if (here) store_pct(P, K, pcell, iq, vlo, vhi, w);
-                }
+                if (node_fast && ncount) store_pct(P, N, nc, iq, vlo, vhi, w);
             }
         }
     }
-    // ---- the node's cell: the lanes of a group hold its values between them ----------------------------
-    if (P.g_node < 0) return;                        // warp-uniform
-    const FinKind& N = P.kind[P.g_node];
-    const uint32_t group_lanes = (gs == 32 ? kAll : ((1u << gs) - 1u)) << (lane & ~(gs - 1));
-    const bool lanes_ok = (__ballot_sync(kAll, ok) & group_lanes) == group_lanes;
-    const uint32_t held = group_sum(n, gs);
-    const bool node_here = l == 0 && node < P.g_nodes && node < N.n_keys;
-    const uint32_t nc = node * P.n_windows + j;
-    uint32_t ncount = 0, nmax = 0;
-    unsigned long long ntotal = 0;
-    if (node_here) {
-        ncount = N.cnt[nc];
-        ntotal = N.sum[nc];
-        nmax = N.mx[nc];
-    }
-    // every sample of the node cell must be in some lane's registers (a GPU outside the gpu table's
-    // domain, or a cell some lane could not take, leaves the node cell to k_finalize_cells)
-    const bool node_fast = node_here && lanes_ok && ncount == held;
-    if (node_fast) {
-        store_basics(P, N, nc, ncount, ntotal, nmax);
-        P.done[N.cell_begin + nc] = (uint8_t)P.done_gen;
-    }
-    const uint32_t base_lane = lane & ~(gs - 1);
-    const bool group_fast = __shfl_sync(kAll, (uint32_t)(node_fast && ncount > 0), base_lane) != 0;
-    if (!__any_sync(kAll, group_fast)) return;
-    const uint32_t gn = __shfl_sync(kAll, ncount, base_lane);
-    for (uint32_t iq = 0; iq < P.n_q; ++iq) {
-        uint32_t ilo = 0, ihi = 0;
-        double w = 0.0;
-        if (group_fast) pct_ranks(P.q[iq], gn, ilo, ihi, w);   // same n in every lane of the group: same ranks
-        const uint32_t nn = group_fast ? gn : 1u;
-        const uint32_t vlo = rank_select<true>(x, byte_total, nn, ilo, gs);
-        uint32_t vhi = vlo;
-        if (__any_sync(kAll, ihi != ilo)) {
-            const uint32_t v2 = rank_select<true>(x, byte_total, nn, ihi, gs);
-            if (ihi != ilo) vhi = v2;
+    // ---- a window in which the tenant changed: every pod's cell is a sub-range (or two) of the bytes this
+    // lane has just used; they are read again (L1) with the other runs masked out ----------------------------
+    if (P.g_pod < 0 || !__any_sync(kAll, split)) return;
+    const FinKind& K = P.kind[P.g_pod];
+#pragma unroll 1
+    for (uint32_t r = 0; r < 4; ++r) {
+        const uint32_t pod = r == 0 ? run_pod[0] : r == 1 ? run_pod[1] : r == 2 ? run_pod[2] : run_pod[3];
+        // the first run with this pod id speaks for all runs of mine that carry it
+        bool first = split && r < runs && pod != kInvalid;
+        uint32_t len = 0, b0 = 0xFFFFFFFFu, b1 = 0;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            if ((uint32_t)q < runs && run_pod[q] == pod) {
+                if ((uint32_t)q < r) first = false;
+                len += run_len[q];
+                b0 = min(b0, run_start[q]);
+                b1 = max(b1, run_start[q] + run_len[q]);
+            }
         }
-        if (node_fast && ncount) store_pct(P, N, nc, iq, vlo, vhi, w);
+        // its runs must be neighbours in the log (one byte range) and be all the pod cell holds
+        uint32_t pn = 0, pmax = 0;
+        unsigned long long ptotal = 0;
+        bool here = first && b1 - b0 == len;
+        if (here) {
+            pn = K.cnt[pod];
+            here = pn == len;
+        }
+        if (!__any_sync(kAll, here)) continue;
+        if (here) {
+            ptotal = K.sum[pod];
+            pmax = K.mx[pod];
+            store_basics(P, K, pod, pn, ptotal, pmax);
+            P.done[K.cell_begin + pod] = (uint8_t)P.done_gen;
+        }
+        const uint32_t off = here ? b0 - (start & ~3u) : 0u;
+        load_values(P, start, off, off + (here ? len : 0u), x);
+        for (uint32_t iq = 0; iq < P.n_q; ++iq) {
+            uint32_t ilo = 0, ihi = 0;
+            double w = 0.0;
+            if (here) pct_ranks(P.q[iq], pn, ilo, ihi, w);
+            const uint32_t nn = here ? pn : 1u;
+            const uint32_t vlo = rank_select<false>(x, (uint32_t)ptotal, nn, ilo, gs);
+            uint32_t vhi = vlo;
+            if (__any_sync(kAll, ihi != ilo)) {
+                const uint32_t v2 = rank_select<false>(x, (uint32_t)ptotal, nn, ihi, gs);
+                if (ihi != ilo) vhi = v2;
+            }
+            if (here) store_pct(P, K, pod, iq, vlo, vhi, w);
+        }
     }
 }
 
