@@ -56,27 +56,41 @@ __device__ __forceinline__ uint32_t count_ge(const uint32_t (&x)[kGroupWords], u
     return (byte_total + 4u * kGroupWords * c - (uint32_t)(a0 + a1)) >> 8;
 }
 
-// Sum over the lanes of a group (gs = 1 << gs_log2 aligned lanes); every lane gets the total.
-__device__ __forceinline__ uint32_t group_sum(uint32_t v, uint32_t gs) {
-    for (uint32_t d = 1; d < gs; d <<= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, d);
+// Sum over the lanes of a group (GS aligned lanes, a power of two); every lane gets the total.
+template <int GS>
+__device__ __forceinline__ uint32_t group_sum(uint32_t v) {
+#pragma unroll
+    for (int d = 1; d < GS; d <<= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, d);
     return v;
 }
 
-// The value of rank r (0-based, ascending) among n values: the lane's own (GROUP = false) or those of
-// all lanes of its group together (GROUP = true; n and r are then the group's, equal in all its lanes).
-template <bool GROUP>
-__device__ __forceinline__ uint32_t rank_select(const uint32_t (&x)[kGroupWords], uint32_t byte_total, uint32_t n,
-                                                uint32_t r, uint32_t gs) {
-    const uint32_t need = n - r;                     // v[r] >= cand  <=>  #{v >= cand} >= n - r
-    uint32_t ans = 0;
+// The values of rank r_lo and r_hi (0-based, ascending; r_hi = r_lo or r_lo + 1) among n values: the
+// lane's own (GS = 1) or those of all GS lanes of its group together (n and the ranks are then the
+// group's, equal in all its lanes).  Both ranks are found by bisection on the value, most significant
+// bit first: v[r] >= cand  <=>  #{v >= cand} >= n - r.  The two searches ask the same question until
+// one step has exactly n - r_hi values at or above its candidate; neighbouring order statistics differ
+// in their low bits if at all, so the second count is needed in the last steps only (and only if some
+// lane of the WARP has got there).
+template <int GS>
+__device__ __forceinline__ void rank_select2(const uint32_t (&x)[kGroupWords], uint32_t byte_total, uint32_t n,
+                                             uint32_t r_lo, uint32_t r_hi, uint32_t& v_lo, uint32_t& v_hi) {
+    const uint32_t need_hi = n - r_hi, need_lo = n - r_lo;
+    uint32_t a_hi = 0, a_lo = 0;
 #pragma unroll
     for (int b = 6; b >= 0; --b) {
-        const uint32_t cand = ans | (1u << b);
-        uint32_t ge = count_ge(x, byte_total, cand);
-        if (GROUP) ge = group_sum(ge, gs);
-        if (ge >= need) ans = cand;
+        const uint32_t c_hi = a_hi | (1u << b), c_lo = a_lo | (1u << b);
+        uint32_t ge_hi = count_ge(x, byte_total, c_hi);
+        if (GS > 1) ge_hi = group_sum<GS>(ge_hi);
+        uint32_t ge_lo = ge_hi;
+        if (__any_sync(0xFFFFFFFFu, a_lo != a_hi)) {
+            ge_lo = count_ge(x, byte_total, c_lo);
+            if (GS > 1) ge_lo = group_sum<GS>(ge_lo);
+        }
+        if (ge_hi >= need_hi) a_hi = c_hi;
+        if (ge_lo >= need_lo) a_lo = c_lo;
     }
-    return ans;
+    v_lo = a_lo;
+    v_hi = a_hi;
 }
 
 // The lane's bytes [b0, b1) of the 4 * kGroupWords bytes that start at the word holding log position `start`.
@@ -89,16 +103,18 @@ __device__ __forceinline__ void load_values(const FinParams& P, uint32_t start, 
         const int lo = (int)b0 - 4 * k, hi = (int)b1 - 4 * k;          // valid bytes of this word: [lo, hi)
         uint32_t w = 0;
         if (hi > 0 && lo < 4) w = __ldg(src + k);
-        uint32_t m = hi >= 4 ? 0xFFFFFFFFu : (hi <= 0 ? 0u : (0xFFFFFFFFu >> (8 * (4 - hi))));
-        if (lo > 0) m &= lo >= 4 ? 0u : (0xFFFFFFFFu << (8 * lo));
-        x[k] = w & m;
+        // bytes below hi, minus bytes below lo (both clamped to 0..4): two 64-bit shifts of all-ones
+        const uint32_t below_hi = (uint32_t)(~(0xFFFFFFFFFFFFFFFFull << (8 * min(max(hi, 0), 4))));
+        const uint32_t below_lo = (uint32_t)(~(0xFFFFFFFFFFFFFFFFull << (8 * min(max(lo, 0), 4))));
+        x[k] = w & below_hi & ~below_lo;
     }
 }
 
+template <int GS>
 __global__ void __launch_bounds__(kGroupThreads, 8) k_finalize_groups(const __grid_constant__ FinParams P) {
     constexpr uint32_t kAll = 0xFFFFFFFFu;
     if (P.ctl[1]) return;                            // overflowed run log: lists are incomplete, the host reports it
-    const uint32_t gs = 1u << P.g_gs_log2;
+    constexpr uint32_t gs = GS;                      // lanes per (node, window) group = 1 << P.g_gs_log2
     const uint32_t lane = lane_id();
     const uint64_t t = (uint64_t)blockIdx.x * kGroupThreads + threadIdx.x;
     const uint32_t l = (uint32_t)t & (gs - 1);
@@ -181,12 +197,8 @@ __global__ void __launch_bounds__(kGroupThreads, 8) k_finalize_groups(const __gr
             double w = 0.0;
             if (n) pct_ranks(P.q[iq], n, ilo, ihi, w);
             const uint32_t nn = n ? n : 1u;
-            const uint32_t vlo = rank_select<false>(x, byte_total, nn, ilo, gs);
-            uint32_t vhi = vlo;
-            if (__any_sync(kAll, ihi != ilo)) {
-                const uint32_t v2 = rank_select<false>(x, byte_total, nn, ihi, gs);
-                if (ihi != ilo) vhi = v2;
-            }
+            uint32_t vlo, vhi;
+            rank_select2<1>(x, byte_total, nn, ilo, ihi, vlo, vhi);
             if (mine && n) {
                 store_pct(P, G, c, iq, vlo, vhi, w);
                 if (twin != kInvalid) store_pct(P, P.kind[P.g_pod], twin, iq, vlo, vhi, w);
@@ -198,7 +210,7 @@ __global__ void __launch_bounds__(kGroupThreads, 8) k_finalize_groups(const __gr
         const FinKind& N = P.kind[P.g_node];
         const uint32_t group_lanes = (gs == 32 ? kAll : ((1u << gs) - 1u)) << (lane & ~(gs - 1));
         const bool lanes_ok = (__ballot_sync(kAll, ok) & group_lanes) == group_lanes;
-        const uint32_t held = group_sum(n, gs);
+        const uint32_t held = group_sum<GS>(n);
         const bool node_here = l == 0 && node < P.g_nodes && node < N.n_keys;
         const uint32_t nc = node * P.n_windows + j;
         uint32_t ncount = 0, nmax = 0;
@@ -224,12 +236,8 @@ __global__ void __launch_bounds__(kGroupThreads, 8) k_finalize_groups(const __gr
                 double w = 0.0;
                 if (group_fast) pct_ranks(P.q[iq], gn, ilo, ihi, w);   // same n in every lane of the group: same ranks
                 const uint32_t nn = group_fast ? gn : 1u;
-                const uint32_t vlo = rank_select<true>(x, byte_total, nn, ilo, gs);
-                uint32_t vhi = vlo;
-                if (__any_sync(kAll, ihi != ilo)) {
-                    const uint32_t v2 = rank_select<true>(x, byte_total, nn, ihi, gs);
-                    if (ihi != ilo) vhi = v2;
-                }
+                uint32_t vlo, vhi;
+                rank_select2<GS>(x, byte_total, nn, ilo, ihi, vlo, vhi);
                 if (node_fast && ncount) store_pct(P, N, nc, iq, vlo, vhi, w);
             }
         }
@@ -275,12 +283,8 @@ __global__ void __launch_bounds__(kGroupThreads, 8) k_finalize_groups(const __gr
             double w = 0.0;
             if (here) pct_ranks(P.q[iq], pn, ilo, ihi, w);
             const uint32_t nn = here ? pn : 1u;
-            const uint32_t vlo = rank_select<false>(x, (uint32_t)ptotal, nn, ilo, gs);
-            uint32_t vhi = vlo;
-            if (__any_sync(kAll, ihi != ilo)) {
-                const uint32_t v2 = rank_select<false>(x, (uint32_t)ptotal, nn, ihi, gs);
-                if (ihi != ilo) vhi = v2;
-            }
+            uint32_t vlo, vhi;
+            rank_select2<1>(x, (uint32_t)ptotal, nn, ilo, ihi, vlo, vhi);
             if (here) store_pct(P, K, pod, iq, vlo, vhi, w);
         }
     }

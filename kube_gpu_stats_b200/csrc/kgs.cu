@@ -1033,7 +1033,16 @@ int kgs_stats_finalize(kgs_handle h) {
             }
             P.done = h->done;
             P.done_gen = h->done_gen;
-            launch(h, KGS_K_FINALIZE_GROUPS, st, [&] { k_finalize_groups<<<(unsigned)grid, kGroupThreads, 0, st>>>(P); });
+            launch(h, KGS_K_FINALIZE_GROUPS, st, [&] {
+                switch (gs_log2) {
+                    case 0: k_finalize_groups<1><<<(unsigned)grid, kGroupThreads, 0, st>>>(P); break;
+                    case 1: k_finalize_groups<2><<<(unsigned)grid, kGroupThreads, 0, st>>>(P); break;
+                    case 2: k_finalize_groups<4><<<(unsigned)grid, kGroupThreads, 0, st>>>(P); break;
+                    case 3: k_finalize_groups<8><<<(unsigned)grid, kGroupThreads, 0, st>>>(P); break;
+                    case 4: k_finalize_groups<16><<<(unsigned)grid, kGroupThreads, 0, st>>>(P); break;
+                    default: k_finalize_groups<32><<<(unsigned)grid, kGroupThreads, 0, st>>>(P); break;
+                }
+            });
         }
     }
     if (!groups) P.done = nullptr;
