@@ -196,7 +196,7 @@ def run_b200(args):
     n = tr.n
     eng = Engine(local)
     if world > 1:
-        eng.set_packed_exchange(True)    # packed tables on the wire (config.exchange_bytes_per_cell)
+        eng.set_packed_exchange('compact')    # compact tables on the wire (config.exchange_bytes_per_cell)
     # pinned host columns (the e2e leg copies from these)
     host = [eng.pinned(n) for _ in range(4)]
     for dst, src in zip(host, (tr.ts, tr.gpu_gid, tr.pid, tr.util)):

@@ -194,16 +194,25 @@ int kgs_result_device_ptr(kgs_handle h, int key_kind, int which, void** d_ptr, s
  * the host in one transfer (blocking; use a pinned destination).  Consecutive jobs alternate between
  * two result regions, so job i's region stays intact while job i+1 is computed (not job i+2). */
 int kgs_result_region(kgs_handle h, void** d_ptr, size_t* exchange_bytes, size_t* total_bytes);
-/* Packed exchange tables, for jobs whose tables travel between GPUs every step.  With the option on
- * (it applies from the next kgs_stats_begin), finalize also writes, per key kind, sum (u32 when a
- * cell's sum provably fits - total_samples_hint * metric maximum < 2^32 - else u64), count u32,
- * max u16, and per percentile the two selected values (u8 | u8<<8; u16 | u16<<16 for fb_mib):
- * 10 + 2*n_q bytes per cell instead of 16 + 8*n_q.  The receiver rebuilds mean = sum/count and the
- * percentile with the same two roundings as the sender (rule R5), so nothing is lost.
- * kgs_exchange_region returns the region one collective has to move: the packed tables when they
- * are on (*packed = 1 for u32 sums, 2 for u64 sums), else the exchange part of kgs_result_region
- * (*packed = 0).  kgs_packed_offset: offset and size of one packed table inside that region
- * (which: 0 count, 1 sum, 2 max, 4 selected values). */
+/* Packed exchange tables, for jobs whose tables travel between GPUs every step.  The option applies
+ * from the next kgs_stats_begin; finalize then also writes, per key kind, what another shard needs to
+ * rebuild the cell - the receiver recomputes mean = sum/count and each percentile from the two SELECTED
+ * values with the sender's own roundings (rule R5), so nothing is lost.
+ *   on = 1, packed: sum u32 (u64 when total_samples_hint * metric maximum >= 2^32; a job that accumulates
+ *     more than the hint allowed for 32 bits fails at finalize with KGS_ERR_CAPACITY), count u32, max u16,
+ *     per percentile u8|u8<<8 (u16|u16<<16 for fb_mib): 10 + 2*n_q bytes per cell instead of 16 + 8*n_q.
+ *   on = 2, compact (8-bit metrics; fb_mib jobs fall back to packed): count u16, sum 24 bits (a u16 table
+ *     and a u8 table), max u8, per percentile u8|u8<<8: 6 + 2*n_q bytes per cell.  A cell above 65 534
+ *     samples has count 0xFFFF in the table and its full count and sum on an escape list at the head of
+ *     the region ({u32 entries, 3 x u32 zero}, then {u32 global cell, u32 count, u64 sum} each; global
+ *     cell = cells of the earlier key kinds + key * n_windows + window).  The list has room for 1/64 of
+ *     the cells + 1024; beyond that the sender's next fetch fails with KGS_ERR_CAPACITY and the receiver
+ *     sees entries > capacity - meant for windows of minutes, not of days.
+ * kgs_exchange_region returns the region one collective has to move: the packed tables when they are on
+ * (*packed = 1 u32 sums, 2 u64 sums, 3 compact), else the exchange part of kgs_result_region (*packed = 0).
+ * kgs_packed_offset: offset and size of one packed table inside that region (which: 0 count, 1 sum -
+ * compact: its low 16 bits -, 2 max, 4 selected values, 5 compact: bits 16..23 of the sum, 6 compact: the
+ * escape list, key_kind any kind of the job). */
 int kgs_set_packed_exchange(kgs_handle h, int on);
 int kgs_exchange_region(kgs_handle h, void** d_ptr, size_t* nbytes, int* packed);
 int kgs_packed_offset(kgs_handle h, int key_kind, int which, size_t* offset, size_t* nbytes);

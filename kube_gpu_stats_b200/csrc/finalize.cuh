@@ -35,9 +35,10 @@ struct FinKind {
     double* o_mean;
     double* o_pct;                       // [n_q][n_keys * n_windows]
     // packed exchange tables (optional, nullptr = off): what another shard needs to rebuild the cell
-    void* p_sum;                         // u32 or u64 per cell (FinParams::packed_sum64)
-    uint32_t* p_count;
-    uint16_t* p_max;
+    void* p_sum;                         // u32 or u64 per cell (FinParams::packed_sum64); compact: the low 16 bits
+    uint8_t* p_sum_hi;                   // compact only: bits 16..23 of the sum
+    void* p_count;                       // u32 per cell; compact: u16, 0xFFFF = see the escape list
+    void* p_max;                         // u16 per cell; compact: u8
     void* p_rank;                        // per percentile and cell: the two selected values, u8|u8<<8 (u16|u16<<16 for fb_mib)
 };
 
@@ -65,6 +66,10 @@ struct FinParams {
     uint32_t g_gs_log2;                  // lanes per (node, window) group = 1 << g_gs_log2 >= gpus per node
     uint32_t g_gpn, g_nodes;             // gpus per node; nodes covered by the groups
     uint32_t packed_sum64;               // packed sums are u64 (a cell's sum may not fit 32 bits)
+    uint32_t packed_compact;             // compact packed tables: count u16, sum 24 bits, max u8 (8-bit metrics)
+    uint32_t* esc_hdr;                   // compact: [0] = cells on the escape list, which follows at esc
+    uint4* esc;                          //   {global cell, count, sum low, sum high} of a cell above 65 534 samples
+    uint32_t esc_cap;
     uint32_t slide_chunk;                // windows per thread of k_finalize_slide
     uint32_t u16;                        // 16-bit metric: the value log holds 2 B/sample, cells go to k_finalize_u16
 };
@@ -106,9 +111,20 @@ __device__ __forceinline__ void store_basics(const FinParams& P, const FinKind& 
     K.o_sum[c] = total;
     K.o_max[c] = vmax;
     K.o_mean[c] = count ? __ddiv_rn((double)total, (double)count) : 0.0;
-    if (K.p_count) {
-        K.p_count[c] = (uint32_t)count;
-        K.p_max[c] = (uint16_t)vmax;
+    if (K.p_count && P.packed_compact) {
+        // a cell of up to 65 534 samples of an 8-bit metric: its sum is below 2^24
+        const bool esc = count > 0xFFFEull;
+        static_cast<uint16_t*>(K.p_count)[c] = esc ? (uint16_t)0xFFFFu : (uint16_t)count;
+        static_cast<uint16_t*>(K.p_sum)[c] = (uint16_t)total;
+        K.p_sum_hi[c] = (uint8_t)(total >> 16);
+        static_cast<uint8_t*>(K.p_max)[c] = (uint8_t)vmax;
+        if (esc) {   // rare: the full numbers go on a list the receiver patches in (overflow is reported by the host)
+            const uint32_t at = atomicAdd(P.esc_hdr, 1u);
+            if (at < P.esc_cap) P.esc[at] = make_uint4(K.cell_begin + c, (uint32_t)count, (uint32_t)total, (uint32_t)(total >> 32));
+        }
+    } else if (K.p_count) {
+        static_cast<uint32_t*>(K.p_count)[c] = (uint32_t)count;
+        static_cast<uint16_t*>(K.p_max)[c] = (uint16_t)vmax;
         if (P.packed_sum64) static_cast<unsigned long long*>(K.p_sum)[c] = total;
         else static_cast<uint32_t*>(K.p_sum)[c] = (uint32_t)total;
     }

@@ -51,8 +51,9 @@ struct KindState {
     double* o_mean = nullptr;
     double* o_pct = nullptr;
     void* p_sum = nullptr;
-    uint32_t* p_count = nullptr;
-    uint16_t* p_max = nullptr;
+    uint8_t* p_sum_hi = nullptr;
+    void* p_count = nullptr;
+    void* p_max = nullptr;
     void* p_rank = nullptr;
 };
 
@@ -99,7 +100,10 @@ struct kgs_ctx {
     bool groups_path = true;       // k_finalize_groups for tumbling-window jobs that include the per-GPU table
     uint32_t thread_cell_max = 256;   // cells above this many samples are counted by a warp, not by a thread
     size_t result_off = 0, result_bytes = 0, exchange_bytes = 0;
-    bool packed_exchange = false, packed_on = false, packed_sum64 = false;   // option; state of the open job
+    int packed_exchange = 0;       // option: 0 off, 1 packed, 2 compact (kgs_set_packed_exchange)
+    bool packed_on = false, packed_sum64 = false, packed_compact = false;   // state of the open job
+    uint32_t* esc_hdr = nullptr;   // compact: escape list header + entries inside the packed region
+    uint32_t esc_cap = 0;
     size_t packed_off = 0, packed_bytes = 0;
     uint64_t vals_cap = 0, vals_used = 0, accumulated = 0;
     uint32_t desc_cap = 0, desc_pool_base = 0, desc_priv_next = 0;
@@ -748,19 +752,37 @@ int kgs_stats_begin(kgs_handle h, const kgs_window_spec* sp) {
     }
     // optional packed exchange tables: sum (u32 if a cell's sum provably fits, else u64), count u32,
     // max u16, and per percentile the two selected values (u8 pair, u16 pair for fb_mib)
-    const bool packed = h->packed_exchange;
+    const bool packed = h->packed_exchange != 0;
     const uint64_t metric_max = sp->metric == KGS_METRIC_FB ? 65535u : 255u;
     const bool sum64 = total_hint * metric_max >= (1ull << 32);
+    // compact tables (8-bit metrics): count u16, sum 24 bits as u16 + u8, max u8 - 6 + 2*n_q bytes per cell; the
+    // few cells above 65 534 samples go on an escape list at the head of the region
+    const bool compact = h->packed_exchange == 2 && sp->metric != KGS_METRIC_FB;
     const size_t rank_bytes = sp->metric == KGS_METRIC_FB ? 4 : 2;
-    struct PLay { size_t sum, cnt, mx, rank; } play[3];
+    struct PLay { size_t sum, sum_hi, cnt, mx, rank; } play[3];
     const size_t packed_begin = off;
+    size_t esc_off = 0;
+    uint64_t esc_cap = 0;
+    if (packed && compact) {
+        esc_cap = window_cells / 64 + 1024;
+        esc_off = off;
+        off = align_up(off + 16 + esc_cap * 16, 256);
+    }
     if (packed) {
         for (int k = 0; k < 3; ++k) {
             if (!(sp->key_mask & (1u << k))) continue;
             const uint64_t wc = (uint64_t)nk_in[k] * sp->n_windows;
-            play[k].sum = off; off = align_up(off + wc * (sum64 ? 8 : 4), 256);
-            play[k].cnt = off; off = align_up(off + wc * 4, 256);
-            play[k].mx = off; off = align_up(off + wc * 2, 256);
+            play[k].sum_hi = 0;
+            if (compact) {
+                play[k].sum = off; off = align_up(off + wc * 2, 256);
+                play[k].sum_hi = off; off = align_up(off + wc, 256);
+                play[k].cnt = off; off = align_up(off + wc * 2, 256);
+                play[k].mx = off; off = align_up(off + wc, 256);
+            } else {
+                play[k].sum = off; off = align_up(off + wc * (sum64 ? 8 : 4), 256);
+                play[k].cnt = off; off = align_up(off + wc * 4, 256);
+                play[k].mx = off; off = align_up(off + wc * 2, 256);
+            }
             play[k].rank = off; off = align_up(off + wc * rank_bytes * sp->n_q, 256);
         }
     }
@@ -806,8 +828,9 @@ int kgs_stats_begin(kgs_handle h, const kgs_window_spec* sp) {
         K.o_max = reinterpret_cast<uint32_t*>(base + slot_shift + lay[k].om);
         if (packed) {
             K.p_sum = base + slot_shift + play[k].sum;
-            K.p_count = reinterpret_cast<uint32_t*>(base + slot_shift + play[k].cnt);
-            K.p_max = reinterpret_cast<uint16_t*>(base + slot_shift + play[k].mx);
+            K.p_sum_hi = compact ? reinterpret_cast<uint8_t*>(base + slot_shift + play[k].sum_hi) : nullptr;
+            K.p_count = base + slot_shift + play[k].cnt;
+            K.p_max = base + slot_shift + play[k].mx;
             K.p_rank = sp->n_q ? base + slot_shift + play[k].rank : nullptr;
         }
     }
@@ -816,6 +839,9 @@ int kgs_stats_begin(kgs_handle h, const kgs_window_spec* sp) {
     h->exchange_bytes = exchange_end - clear_bytes;
     h->packed_on = packed;
     h->packed_sum64 = sum64;
+    h->packed_compact = packed && compact;
+    h->esc_hdr = (packed && compact) ? reinterpret_cast<uint32_t*>(base + slot_shift + esc_off) : nullptr;
+    h->esc_cap = (uint32_t)esc_cap;
     h->packed_off = packed_begin + slot_shift;
     h->packed_bytes = packed_end - packed_begin;
     h->rare_list = reinterpret_cast<uint32_t*>(base + rare_off);
@@ -975,7 +1001,7 @@ int kgs_stats_finalize(kgs_handle h) {
         F.cell_begin = cells;
         F.cnt = K.cnt; F.sum = K.sum; F.mx = K.mx; F.head = K.head;
         F.o_count = K.o_count; F.o_sum = K.o_sum; F.o_max = K.o_max; F.o_mean = K.o_mean; F.o_pct = K.o_pct;
-        F.p_sum = K.p_sum; F.p_count = K.p_count; F.p_max = K.p_max; F.p_rank = K.p_rank;
+        F.p_sum = K.p_sum; F.p_sum_hi = K.p_sum_hi; F.p_count = K.p_count; F.p_max = K.p_max; F.p_rank = K.p_rank;
         const uint64_t wc = (uint64_t)K.n_keys * sp.n_windows;
         if (cells + wc >= (1ull << 32)) return fail(h, KGS_ERR_ARG, "too many window cells");
         cells += (uint32_t)wc;
@@ -1002,7 +1028,18 @@ int kgs_stats_finalize(kgs_handle h) {
     P.u16 = sp.metric == KGS_METRIC_FB ? 1u : 0u;
     P.slide_chunk = h->slide_chunk;
     P.packed_sum64 = h->packed_sum64 ? 1u : 0u;
+    P.packed_compact = h->packed_compact ? 1u : 0u;
+    P.esc_hdr = h->esc_hdr;
+    P.esc = h->esc_hdr ? reinterpret_cast<uint4*>(h->esc_hdr + 4) : nullptr;
+    P.esc_cap = h->esc_cap;
+    if (h->packed_on && !h->packed_compact && !h->packed_sum64) {
+        const unsigned long long metric_max = sp.metric == KGS_METRIC_FB ? 65535ull : 255ull;
+        if (h->accumulated * metric_max >= (1ull << 32))
+            return fail(h, KGS_ERR_CAPACITY, "packed exchange tables hold 32-bit sums, sized from total_samples_hint; this job accumulated " +
+                                                 std::to_string(h->accumulated) + " samples: give a larger hint");
+    }
     cudaStream_t st = h->compute;
+    if (h->packed_compact) KGS_CUDA(h, cudaMemsetAsync(h->esc_hdr, 0, 16, st));   // escape list: no entries yet
     // A job may be finalized more than once (more batches in between): the lists of cells left to
     // k_finalize_rare start empty each time.
     if (sp.n_q && h->job_final) KGS_CUDA(h, cudaMemsetAsync(h->ctl + 2, 0, 8, st));
@@ -1087,6 +1124,14 @@ static int check_job_flags(kgs_handle h) {
     uint32_t ctl[4] = {0, 0, 0, 0};
     KGS_CUDA(h, cudaMemcpyAsync(ctl, h->ctl, sizeof(ctl), cudaMemcpyDeviceToHost, h->compute));
     KGS_CUDA(h, cudaStreamSynchronize(h->compute));
+    if (h->packed_compact && h->job_final) {
+        uint32_t n_esc = 0;
+        KGS_CUDA(h, cudaMemcpyAsync(&n_esc, h->esc_hdr, 4, cudaMemcpyDeviceToHost, h->compute));
+        KGS_CUDA(h, cudaStreamSynchronize(h->compute));
+        if (n_esc > h->esc_cap)
+            return fail(h, KGS_ERR_CAPACITY, "compact exchange tables: " + std::to_string(n_esc) + " cells above 65 534 samples, the escape list holds " +
+                                                 std::to_string(h->esc_cap) + " (use kgs_set_packed_exchange(h, 1) for windows this long)");
+    }
     if (ctl[1])
         return fail(h, KGS_ERR_CAPACITY,
                     "run log overflow: the shared pool needed " + std::to_string(ctl[0]) + " entries, total capacity " +
@@ -1155,7 +1200,8 @@ int kgs_result_region(kgs_handle h, void** d_ptr, size_t* exchange_bytes, size_t
 
 int kgs_set_packed_exchange(kgs_handle h, int on) {
     if (!h) return KGS_ERR_ARG;
-    h->packed_exchange = on != 0;
+    if (on < 0 || on > 2) return fail(h, KGS_ERR_ARG, "kgs_set_packed_exchange: 0 (off), 1 (packed) or 2 (compact)");
+    h->packed_exchange = on;
     return KGS_OK;
 }
 
@@ -1169,7 +1215,7 @@ int kgs_exchange_region(kgs_handle h, void** d_ptr, size_t* nbytes, int* packed)
         *d_ptr = static_cast<char*>(h->arena.p) + h->result_off;
         *nbytes = h->exchange_bytes;
     }
-    if (packed) *packed = h->packed_on ? (h->packed_sum64 ? 2 : 1) : 0;
+    if (packed) *packed = h->packed_on ? (h->packed_compact ? 3 : h->packed_sum64 ? 2 : 1) : 0;
     return KGS_OK;
 }
 
@@ -1181,12 +1227,15 @@ int kgs_packed_offset(kgs_handle h, int key_kind, int which, size_t* offset, siz
     const size_t wc = (size_t)K.n_keys * h->spec.n_windows;
     const char* base = static_cast<char*>(h->arena.p) + h->packed_off;
     const void* p;
+    const bool cp = h->packed_compact;
     switch (which) {
-        case 0: p = K.p_count; *nbytes = wc * 4; break;
-        case 1: p = K.p_sum; *nbytes = wc * (h->packed_sum64 ? 8 : 4); break;
-        case 2: p = K.p_max; *nbytes = wc * 2; break;
+        case 0: p = K.p_count; *nbytes = wc * (cp ? 2 : 4); break;
+        case 1: p = K.p_sum; *nbytes = wc * (cp ? 2 : h->packed_sum64 ? 8 : 4); break;
+        case 2: p = K.p_max; *nbytes = wc * (cp ? 1 : 2); break;
         case 4: p = K.p_rank ? K.p_rank : K.p_max; *nbytes = K.p_rank ? wc * (h->spec.metric == KGS_METRIC_FB ? 4 : 2) * h->spec.n_q : 0; break;
-        default: return fail(h, KGS_ERR_ARG, "which must be 0 (count), 1 (sum), 2 (max) or 4 (selected values)");
+        case 5: p = cp ? static_cast<const void*>(K.p_sum_hi) : K.p_sum; *nbytes = cp ? wc : 0; break;
+        case 6: p = cp ? static_cast<const void*>(h->esc_hdr) : static_cast<const void*>(base); *nbytes = cp ? 16 + (size_t)h->esc_cap * 16 : 0; break;
+        default: return fail(h, KGS_ERR_ARG, "which must be 0 (count), 1 (sum), 2 (max), 4 (selected values), 5 (sum, high byte) or 6 (escape list)");
     }
     *offset = (size_t)(static_cast<const char*>(p) - base);
     return KGS_OK;

@@ -265,8 +265,10 @@ class Engine:
         return p.value, e.value, t.value
 
     def set_packed_exchange(self, on):
-        """From the next job on, finalize also writes the packed exchange tables (include/kgs.h)."""
-        self._ck(self._lib.kgs_set_packed_exchange(self._h, 1 if on else 0))
+        """From the next job on, finalize also writes the packed exchange tables (include/kgs.h):
+        False/0 off, True/1 packed (10 + 2*n_q bytes per cell), 2 or 'compact' (6 + 2*n_q)."""
+        mode = 2 if on == 'compact' else int(on)
+        self._ck(self._lib.kgs_set_packed_exchange(self._h, mode))
 
     def exchange_region(self):
         """(device address, bytes, packed flag) of what one collective has to move for this job."""
@@ -277,11 +279,21 @@ class Engine:
     def packed_layout(self, kinds):
         """{kind: {table: (offset, nbytes)}} of the packed exchange tables, plus what decoding needs."""
         sp = self._spec
+        mode = self.exchange_region()[2]
         out = {'n_windows': sp.n_windows, 'qs': [sp.q[i] for i in range(sp.n_q)], 'u16': sp.metric == _ffi.METRIC_FB,
-               'sum64': self.exchange_region()[2] == 2, 'kinds': {}}
+               'sum64': mode == 2, 'compact': mode == 3, 'kinds': {}, 'cell_begin': {}}
+        begin = 0
+        for name, kid in (('pod', 0), ('gpu', 1), ('node', 2)):      # global cell numbering: kinds of the job, in this order
+            if sp.key_mask & (1 << kid):
+                out['cell_begin'][name] = begin
+                begin += self._n_keys[name] * sp.n_windows
+        if mode == 3:
+            off, nb = C.c_size_t(), C.c_size_t()
+            self._ck(self._lib.kgs_packed_offset(self._h, KIND_ID[kinds[0]], 6, C.byref(off), C.byref(nb)))
+            out['escape'] = (off.value, nb.value)
         for k in kinds:
             t = {}
-            for name, which in (('count', 0), ('sum', 1), ('max', 2), ('rank', 4)):
+            for name, which in (('count', 0), ('sum', 1), ('max', 2), ('rank', 4)) + ((('sum_hi', 5),) if mode == 3 else ()):
                 off, nb = C.c_size_t(), C.c_size_t()
                 self._ck(self._lib.kgs_packed_offset(self._h, KIND_ID[k], which, C.byref(off), C.byref(nb)))
                 t[name] = (off.value, nb.value)

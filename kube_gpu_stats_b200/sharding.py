@@ -287,9 +287,26 @@ def decode_packed(buf, layout):
         def arr(name, dt):
             off, nb = t[name]
             return buf[off:off + nb].view(dt)
-        count = arr('count', np.uint32).astype(np.uint64)
-        total = arr('sum', np.uint64 if layout['sum64'] else np.uint32).astype(np.uint64)
-        vmax = arr('max', np.uint16).astype(np.uint32)
+        if layout.get('compact'):
+            count = arr('count', np.uint16).astype(np.uint64)
+            total = arr('sum', np.uint16).astype(np.uint64) | (arr('sum_hi', np.uint8).astype(np.uint64) << np.uint64(16))
+            vmax = arr('max', np.uint8).astype(np.uint32)
+            off, nb = layout['escape']                      # cells above 65 534 samples: full numbers from the list
+            n_esc = int(buf[off:off + 4].view(np.uint32)[0])
+            cap = (nb - 16) // 16
+            if n_esc > cap:
+                raise ValueError('compact exchange tables: %d cells on an escape list of %d (sender should use the '
+                                 'packed format for windows this long)' % (n_esc, cap))
+            if n_esc:
+                ent = buf[off + 16:off + 16 + 16 * n_esc].view(np.uint32).reshape(n_esc, 4)
+                cell = ent[:, 0].astype(np.int64) - layout['cell_begin'][kind]
+                mine = (cell >= 0) & (cell < n)
+                count[cell[mine]] = ent[mine, 1].astype(np.uint64)
+                total[cell[mine]] = ent[mine, 2].astype(np.uint64) | (ent[mine, 3].astype(np.uint64) << np.uint64(32))
+        else:
+            count = arr('count', np.uint32).astype(np.uint64)
+            total = arr('sum', np.uint64 if layout['sum64'] else np.uint32).astype(np.uint64)
+            vmax = arr('max', np.uint16).astype(np.uint32)
         cf = count.astype(np.float64)
         mean = np.divide(total.astype(np.float64), cf, out=np.zeros(n), where=count > 0)
         qs = layout['qs']

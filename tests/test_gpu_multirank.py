@@ -48,7 +48,7 @@ def _worker(rank, world, port, out_dir):
         (tr.ts, tr.gpu_gid, tr.pid, tr.util), tr.keys, tr.pod_ids, tr.pod_node, (a, b), 8)
     pods_max = max(int(np.count_nonzero((tr.pod_node >= x) & (tr.pod_node < y))) for x, y in ranges)
     eng = Engine(rank)
-    eng.set_packed_exchange(True)
+    eng.set_packed_exchange('compact')
     eng.build_join(keys, pods, pods_max)
     eng.ingest(ts, gid, pid, util)
     spec = eng.make_spec(kinds=KINDS, metric='sm', gpus_per_node=8, t0=tr.t0, step=STEP, n_windows=N_WINDOWS,

@@ -183,14 +183,17 @@ def test_fetch_all_single_copy_equals_per_table_fetch(engine, cfg1):
             assert_stats_equal(engine.fetch(k), oracle(tr, k, 'mem', tr.t0, 60, 60, 60, QS), what='mem ' + k)
 
 
-@pytest.mark.parametrize('metric,step,width', [('sm', 60, 60), ('mem', 10, 50), ('fb', 300, 300)])
-def test_packed_exchange_tables_decode_to_the_full_tables(engine, cfg1, metric, step, width):
-    """What a peer GPU receives (10 + 2*n_q bytes per cell) must rebuild the sender's tables bit for bit."""
+@pytest.mark.parametrize('mode', [1, 2])
+@pytest.mark.parametrize('metric,step,width', [('sm', 60, 60), ('mem', 10, 50), ('fb', 300, 300), ('sm', 1800, 1800)])
+def test_packed_exchange_tables_decode_to_the_full_tables(engine, cfg1, metric, step, width, mode):
+    """What a peer GPU receives (packed: 10 + 2*n_q bytes per cell; compact: 6 + 2*n_q, with the cells
+    above 65 534 samples - the node cells of the half-hour windows here - on the escape list) must
+    rebuild the sender's tables bit for bit."""
     import torch
     from kube_gpu_stats_b200 import sharding
     tr = cfg1
     kinds = ('pod', 'gpu', 'node')
-    engine.set_packed_exchange(True)
+    engine.set_packed_exchange(mode)
     engine.set_run_log_capacity(2 * 3 * (tr.n + 8 * 4096))
     engine.build_join(tr.keys, tr.pod_ids, tr.n_pods)
     engine.ingest(tr.ts, tr.gpu_gid, tr.pid, tr.util)
@@ -199,7 +202,10 @@ def test_packed_exchange_tables_decode_to_the_full_tables(engine, cfg1, metric, 
     engine.window_stats_device(spec)
     full = {k: engine.fetch(k) for k in kinds}
     ptr, nbytes, packed = engine.exchange_region()
-    assert packed == (2 if metric == 'fb' else 1) and nbytes < engine.result_region()[1]   # fb sums may pass 2^32: u64
+    # fb sums may pass 2^32: u64; the compact tables are for the 8-bit metrics, an fb job falls back to packed
+    assert packed == (2 if metric == 'fb' else (3 if mode == 2 else 1)) and nbytes < engine.result_region()[1]
+    if step == 1800:
+        assert int(full['node']['count'].max()) > 65534
     src = torch.as_tensor(sharding._DeviceBytes(ptr, nbytes), device='cuda:0')
     got = sharding.decode_packed(src.cpu().numpy(), engine.packed_layout(kinds))
     for k in kinds:

@@ -75,16 +75,26 @@ else:
                          n_gpus=n_gpus, n_nodes=n_nodes, qs=qs, total_samples_hint=n)
 ap_exchange = os.environ.get('KGS_EXCHANGE', 'peer')
 gather = None
-if world > 1:
-    eng.set_packed_exchange(True)
-    gather = sharding.PeerTableGather(eng, kinds, world) if ap_exchange == 'peer' else sharding.TableGather(eng, kinds, world)
-    if rank == 0:
-        print('exchange: %s' % type(gather).__name__, flush=True)
 stream = torch.cuda.ExternalStream(eng.stream('compute'), device=torch.device('cuda', local))
 with torch.cuda.stream(stream):
+    if world > 1:
+        eng.set_packed_exchange('compact')
     eng.window_stats_device(spec)                 # warm-up (allocates the arena)
-    if gather:
-        gather.all_gather()
+    eng.sync()
+    if world > 1:
+        # the library's own exchange (kgs_exchange_push / kgs_exchange_nccl); not overlapped here: one pass, then its exchange
+        slot = eng.exchange_region()[1]
+        if ap_exchange == 'peer':
+            gather = sharding.PeerExchange(eng, world, rank, slot)
+        else:
+            ids = [eng.nccl_unique_id() if rank == 0 else None]
+            dist.broadcast_object_list(ids, src=0)
+            eng.nccl_init(ids[0], world, rank)
+            gather = sharding.NcclExchange(eng, world, slot)
+        if rank == 0:
+            print('exchange: %s, %.1f MB per rank and pass' % (type(gather).__name__, slot / 1e6), flush=True)
+        gather.push()
+        eng.exchange_join()
     eng.sync(); torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
@@ -94,7 +104,8 @@ with torch.cuda.stream(stream):
     for _ in range(args.steps):
         eng.window_stats_device(spec)
         if gather:
-            gather.all_gather()
+            gather.push()
+            eng.exchange_join()
     e1.record(stream)
     eng.sync(); torch.cuda.synchronize()
 ms = torch.tensor([e0.elapsed_time(e1) / args.steps], device='cuda', dtype=torch.float64)
@@ -106,7 +117,7 @@ if rank == 0:
           % (world, float(ms), n * world / 1e9, n * world / float(ms) / 1e6, n * 16 / float(ms) / 1e6))
     print('  kernels per pass (ms): ' + ', '.join('%s %.3f' % (k, v[0] / args.steps) for k, v in kt.items() if v[1]))
 
-if args.check:
+if args.check and rank == 0:
     tables = eng.fetch_all(kinds)
     n_win = spec.n_windows
     if not args.sliding:
@@ -133,6 +144,8 @@ if args.check:
         assert np.array_equal(np.ascontiguousarray(tables[kind]['pct'][:, :m]).view(np.uint64), want['pct'].view(np.uint64)), kind
     if rank == 0:
         print('parity ok on rank 0: totals, node = sum of its GPUs, and the base replica bit-identical to the oracle')
+if world > 1:
+    dist.barrier()
 eng.close()
 if world > 1:
     dist.destroy_process_group()
