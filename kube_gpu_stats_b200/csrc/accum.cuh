@@ -72,7 +72,7 @@ struct AccumParams {
 
 __device__ __forceinline__ uint64_t policy_evict_last() {
     uint64_t pol;
-    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+    asm("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));   // no side effect: the compiler may hoist it out of the tile loop
     return pol;
 }
 __device__ __forceinline__ void st_keep_v2(void* p, uint32_t a, uint32_t b, uint64_t pol) {
@@ -260,6 +260,7 @@ __device__ __forceinline__ uint4 lds_v4(uint32_t a) {
 template <bool PCT, bool TMA>
 __global__ void __launch_bounds__(kAccumWarps * 32) k_accum(const __grid_constant__ AccumParams P) {
     extern __shared__ __align__(128) unsigned char tma_smem[];   // TMA only: [warp][stage] tile buffers, then barriers
+    cudaTriggerProgrammaticLaunchCompletion();   // the finalize kernel behind this one may be scheduled while the last CTAs drain
     __shared__ RunQueue queues[kAccumWarps];
     __shared__ AggTable table;
     constexpr uint32_t kAll = 0xFFFFFFFFu;
@@ -488,8 +489,11 @@ __global__ void __launch_bounds__(kAccumWarps * 32) k_accum(const __grid_constan
         // lanes with two or more boundaries: the pieces between the first and the last are retired
         // directly (rare in collector order; every lane in shuffled input, then 32 wide)
         const bool many = (bm & (bm - 1)) != 0;
-        const uint32_t many_mask = dense ? 0u : __ballot_sync(kAll, many);
-        if (P.agg_on && __popc(many_mask) >= 16) agg = &table;
+        uint32_t many_mask = 0;
+        if (!dense) {                                  // warp-uniform
+            many_mask = __ballot_sync(kAll, many);
+            if (P.agg_on && __popc(many_mask) >= 16) agg = &table;
+        }
         if (many_mask) {
             uint32_t nr = 0;
             if (many) {

@@ -362,6 +362,8 @@ __device__ __forceinline__ void defer_cell(const FinParams& P, bool wide, bool b
 __global__ void __launch_bounds__(CellLayout::NT, 8) k_finalize_cells(const __grid_constant__ FinParams P) {
     using L = CellLayout;
     __shared__ uint32_t hist[L::WORDS * L::NT];
+    cudaGridDependencySynchronize();                 // a programmatic dependent of the kernel before it (no-op otherwise)
+    cudaTriggerProgrammaticLaunchCompletion();
     const uint32_t tid = threadIdx.x;
     const uint32_t base = (uint32_t)__cvta_generic_to_shared(hist) + tid * 4;
     const uint32_t n_blocks = (P.total_cells + L::NT - 1) / L::NT;
@@ -532,6 +534,7 @@ __device__ __forceinline__ void finalize_big_part(const FinParams& P, uint32_t c
 
 // Both rare lists in one launch (each is almost always empty; two launches cost 6 % of a step).
 __global__ void __launch_bounds__(WideLayout::NT) k_finalize_rare(const __grid_constant__ FinParams P) {
+    cudaGridDependencySynchronize();                 // a programmatic dependent of k_finalize_cells / k_finalize_slide
     if (blockIdx.x < P.rare_wide_ctas) finalize_wide_part(P, blockIdx.x, P.rare_wide_ctas);
     else finalize_big_part(P, blockIdx.x - P.rare_wide_ctas, gridDim.x - P.rare_wide_ctas);
 }

@@ -113,6 +113,8 @@ __device__ __forceinline__ void load_values(const FinParams& P, uint32_t start, 
 template <int GS>
 __global__ void __launch_bounds__(kGroupThreads, 8) k_finalize_groups(const __grid_constant__ FinParams P) {
     constexpr uint32_t kAll = 0xFFFFFFFFu;
+    cudaGridDependencySynchronize();                 // launched as a programmatic dependent of k_accum (no-op otherwise)
+    cudaTriggerProgrammaticLaunchCompletion();       // k_finalize_cells may be scheduled as this grid drains
     if (P.ctl[1]) return;                            // overflowed run log: lists are incomplete, the host reports it
     constexpr uint32_t gs = GS;                      // lanes per (node, window) group = 1 << P.g_gs_log2
     const uint32_t lane = lane_id();

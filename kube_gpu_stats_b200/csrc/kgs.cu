@@ -97,6 +97,8 @@ struct kgs_ctx {
     uint8_t* done = nullptr;       // per window cell: finished by k_finalize_groups in finalize pass done_gen
     uint32_t done_gen = 0;
     size_t done_bytes = 0;
+    bool last_was_accum = false;   // the last work queued on the compute stream is k_accum
+    bool pdl = true;               // finalize kernels launched as programmatic dependents (not while profiling per kernel)
     bool groups_path = true;       // k_finalize_groups for tumbling-window jobs that include the per-GPU table
     uint32_t thread_cell_max = 256;   // cells above this many samples are counted by a warp, not by a thread
     size_t result_off = 0, result_bytes = 0, exchange_bytes = 0;
@@ -222,6 +224,26 @@ int drain_timed(kgs_handle h) {
     return KGS_OK;
 }
 
+// Launch with programmatic dependent launch (PDL): the kernel may be scheduled while its predecessor on
+// the stream is still draining; it waits in cudaGridDependencySynchronize() (first statement of the
+// kernels launched this way) until the predecessor has completed and its writes are visible.  The
+// predecessors call cudaTriggerProgrammaticLaunchCompletion() when they start, so what is overlapped is
+// the successor's launch and ramp-up with the predecessor's tail.
+template <class P>
+cudaError_t launch_after(void (*kern)(P), unsigned grid, unsigned block, cudaStream_t st, bool pdl, const P& params) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(block);
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kern, params);
+}
+
 inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
 // Does this batch interleave several series - a collector that reports all processes of a GPU (or all
@@ -315,6 +337,7 @@ int kgs_create(int device, kgs_handle* out) {
     if (const char* e = getenv("KGS_ACCUM_TMA")) h->accum_tma = atoi(e) != 0;
     if (const char* e = getenv("KGS_FINALIZE_GROUPS")) h->groups_path = atoi(e) != 0;
     if (const char* e = getenv("KGS_AUTO_REORDER")) h->auto_reorder = atoi(e) != 0;
+    if (const char* e = getenv("KGS_PDL")) h->pdl = atoi(e) != 0;
     if (const char* e = getenv("KGS_THREAD_CELL_MAX")) { const int v = atoi(e); if (v >= 1 && v <= 65535) h->thread_cell_max = (uint32_t)v; }
     if (h->accum_tma) {
         h->accum_ctas_per_sm = 2;   // 64 KB of tile buffers + 42 KB static per CTA
@@ -872,6 +895,7 @@ int kgs_stats_begin(kgs_handle h, const kgs_window_spec* sp) {
         h->desc_cap = 0;
     }
     KGS_CUDA(h, cudaMemsetAsync(h->arena.p, 0, clear_bytes, h->compute));
+    if (h->packed_compact) KGS_CUDA(h, cudaMemsetAsync(h->esc_hdr, 0, 16, h->compute));   // escape list of this job's region: empty
     h->spec = *sp;
     h->W = W;
     h->n_panes = (uint32_t)n_panes;
@@ -983,6 +1007,7 @@ int kgs_stats_accumulate(kgs_handle h) {
     KGS_CUDA(h, cudaEventRecord(B.consumed, st));
     if (pct) h->vals_used = align_up(h->vals_used + B.n, 16);
     h->accumulated += B.n;
+    h->last_was_accum = true;
     return KGS_OK;
 }
 
@@ -1039,10 +1064,13 @@ int kgs_stats_finalize(kgs_handle h) {
                                                  std::to_string(h->accumulated) + " samples: give a larger hint");
     }
     cudaStream_t st = h->compute;
-    if (h->packed_compact) KGS_CUDA(h, cudaMemsetAsync(h->esc_hdr, 0, 16, st));   // escape list: no entries yet
+    if (h->packed_compact && h->job_final) KGS_CUDA(h, cudaMemsetAsync(h->esc_hdr, 0, 16, st));   // finalized again: the escape list starts empty
     // A job may be finalized more than once (more batches in between): the lists of cells left to
     // k_finalize_rare start empty each time.
     if (sp.n_q && h->job_final) KGS_CUDA(h, cudaMemsetAsync(h->ctl + 2, 0, 8, st));
+    // PDL only where the predecessor on the stream is the library's own kernel and no per-kernel events sit in between
+    const bool pdl = h->pdl && !h->prof && h->last_was_accum && !h->job_final;
+    h->last_was_accum = false;
     // k_finalize_groups: tumbling (or sampled) windows of an 8-bit metric, per-GPU table part of the job
     const int slot_of[3] = {(sp.key_mask & 1u) ? 0 : -1, (sp.key_mask & 2u) ? (int)__builtin_popcount(sp.key_mask & 1u) : -1,
                             (sp.key_mask & 4u) ? (int)__builtin_popcount(sp.key_mask & 3u) : -1};
@@ -1072,12 +1100,12 @@ int kgs_stats_finalize(kgs_handle h) {
             P.done_gen = h->done_gen;
             launch(h, KGS_K_FINALIZE_GROUPS, st, [&] {
                 switch (gs_log2) {
-                    case 0: k_finalize_groups<1><<<(unsigned)grid, kGroupThreads, 0, st>>>(P); break;
-                    case 1: k_finalize_groups<2><<<(unsigned)grid, kGroupThreads, 0, st>>>(P); break;
-                    case 2: k_finalize_groups<4><<<(unsigned)grid, kGroupThreads, 0, st>>>(P); break;
-                    case 3: k_finalize_groups<8><<<(unsigned)grid, kGroupThreads, 0, st>>>(P); break;
-                    case 4: k_finalize_groups<16><<<(unsigned)grid, kGroupThreads, 0, st>>>(P); break;
-                    default: k_finalize_groups<32><<<(unsigned)grid, kGroupThreads, 0, st>>>(P); break;
+                    case 0: launch_after(k_finalize_groups<1>, (unsigned)grid, kGroupThreads, st, pdl, P); break;
+                    case 1: launch_after(k_finalize_groups<2>, (unsigned)grid, kGroupThreads, st, pdl, P); break;
+                    case 2: launch_after(k_finalize_groups<4>, (unsigned)grid, kGroupThreads, st, pdl, P); break;
+                    case 3: launch_after(k_finalize_groups<8>, (unsigned)grid, kGroupThreads, st, pdl, P); break;
+                    case 4: launch_after(k_finalize_groups<16>, (unsigned)grid, kGroupThreads, st, pdl, P); break;
+                    default: launch_after(k_finalize_groups<32>, (unsigned)grid, kGroupThreads, st, pdl, P); break;
                 }
             });
         }
@@ -1096,7 +1124,7 @@ int kgs_stats_finalize(kgs_handle h) {
             }
         } else {
             launch(h, KGS_K_FINALIZE, st, [&] {   // at most one wave of CTAs (8 per SM), each walking blocks of cells
-                k_finalize_cells<<<grid_for(cells, CellLayout::NT, 148 * 8), CellLayout::NT, 0, st>>>(P);
+                launch_after(k_finalize_cells, (unsigned)grid_for(cells, CellLayout::NT, 148 * 8), CellLayout::NT, st, pdl, P);
             });
         }
         if (sp.n_q && sp.metric == KGS_METRIC_FB) {   // 16-bit values: two-digit radix select, warp per cell
@@ -1105,7 +1133,7 @@ int kgs_stats_finalize(kgs_handle h) {
             const int wide_grid = grid_for(cells, WideLayout::NT, 148 * 6);
             const int big_grid = h->accumulated * h->W > h->thread_cell_max ? 148 * 4 : 0;
             P.rare_wide_ctas = (uint32_t)wide_grid;
-            launch(h, KGS_K_FINALIZE_WIDE, st, [&] { k_finalize_rare<<<wide_grid + big_grid, WideLayout::NT, 0, st>>>(P); });
+            launch(h, KGS_K_FINALIZE_WIDE, st, [&] { launch_after(k_finalize_rare, (unsigned)(wide_grid + big_grid), WideLayout::NT, st, pdl, P); });
         }
     }
     KGS_CUDA(h, cudaGetLastError());
