@@ -367,7 +367,15 @@ __global__ void __launch_bounds__(CellLayout::NT, 8) k_finalize_cells(const __gr
     const uint32_t tid = threadIdx.x;
     const uint32_t base = (uint32_t)__cvta_generic_to_shared(hist) + tid * 4;
     const uint32_t n_blocks = (P.total_cells + L::NT - 1) / L::NT;
-    // a CTA walks blocks of 128 cells; after k_finalize_groups most blocks have nothing left to do
+    // a CTA walks blocks of 128 cells, gridDim.x apart (node cells, the heaviest, are spread over all CTAs)
+    if (P.done) {   // after k_finalize_groups the usual CTA has nothing left to do: one look at its cells' flags
+        bool all = true;
+        for (uint32_t blk = blockIdx.x; blk < n_blocks; blk += gridDim.x) {
+            const uint32_t i = blk * L::NT + tid;
+            if (i < P.total_cells) all = all && P.done[P.total_cells - 1 - i] == (uint8_t)P.done_gen;
+        }
+        if (__syncthreads_and(all)) return;
+    }
     for (uint32_t blk = blockIdx.x; blk < n_blocks; blk += gridDim.x) {
         const uint32_t idx = blk * L::NT + tid;
         bool live = idx < P.total_cells;

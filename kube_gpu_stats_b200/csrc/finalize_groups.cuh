@@ -244,6 +244,18 @@ __global__ void __launch_bounds__(kGroupThreads, 8) k_finalize_groups(const __gr
             }
         }
     }
+    // ---- (pod, window) cells without a sample (a pod that did not exist yet, or no more): no thread above
+    // ever gets to them; finishing them here leaves k_finalize_cells nothing to do in the usual job -------------
+    if (P.g_pod >= 0) {
+        const FinKind& K = P.kind[P.g_pod];
+        const uint64_t n_pod_cells = (uint64_t)K.n_keys * P.n_windows, n_threads = (uint64_t)gridDim.x * kGroupThreads;
+        for (uint64_t pc = t; pc < n_pod_cells; pc += n_threads) {
+            if (K.cnt[pc] == 0) {
+                store_basics(P, K, (uint32_t)pc, 0, 0, 0);
+                P.done[K.cell_begin + (uint32_t)pc] = (uint8_t)P.done_gen;
+            }
+        }
+    }
     // ---- a window in which the tenant changed: every pod's cell is a sub-range (or two) of the bytes this
     // lane has just used; they are read again (L1) with the other runs masked out ----------------------------
     if (P.g_pod < 0 || !__any_sync(kAll, split)) return;
