@@ -243,7 +243,7 @@ def run_b200(args):
         # before the closing barrier
         eng.window_stats_device(spec)
         if gather is not None:
-            gather.push()
+            gather.push(want_view=False)
 
     def barrier():
         if gather is not None:

@@ -240,10 +240,13 @@ class PeerExchange:
         self._base = bases[rank]
         dist.barrier(group=self.group)          # nobody pushes before every rank's flag words are zero
 
-    def push(self):
+    def push(self, want_view=True):
         """Queue the exchange of the finalized job; returns the [world, bytes] view of the gathered
-        tables (filled when the exchange stream has passed the push: exchange_join / exchange_sync)."""
+        tables (filled when the exchange stream has passed the push: exchange_join / exchange_sync).
+        want_view=False skips building that view: one C call per step and nothing else on the host."""
         ptr, nbytes = self.eng.exchange_push()
+        if not want_view:
+            return None
         half = (ptr - self._base) // (self.world * self.slot)
         a = half * self.world * self.slot
         return self.local[a:a + self.world * self.slot].view(self.world, self.slot)[:, :nbytes]
@@ -268,11 +271,11 @@ class NcclExchange:
         backend = dist.distributed_c10d._get_default_group()._get_backend(torch.device('cuda', device))
         return int(backend._comm_ptr())
 
-    def push(self):
+    def push(self, want_view=True):
         buf = self.recv[self._i]
         self._i ^= 1
         n = self.eng.exchange_nccl(buf.data_ptr(), buf.numel(), self.comm)
-        return buf[:self.world * n].view(self.world, n)
+        return buf[:self.world * n].view(self.world, n) if want_view else None
 
 
 def decode_packed(buf, layout):
