@@ -221,9 +221,13 @@ def run_b200(args):
         try:
             if os.environ.get('KGS_EXCHANGE', 'peer') != 'peer':
                 raise RuntimeError('KGS_EXCHANGE asks for NCCL')
-            gather = sharding.PeerExchange(eng, world, rank, slot_bytes)
-            exchange = ('kgs_exchange_push: copy-engine pushes of the packed tables into every peer over NVLink '
+            gather = sharding.PeerExchange(eng, world, rank, slot_bytes,
+                                           multicast=os.environ.get('KGS_EXCHANGE_MULTICAST', '0') == '1')
+            exchange = ('kgs_exchange_push: copy-engine pushes of the compact tables into every peer over NVLink '
                         '(peer-mapped symmetric memory) + one barrier kernel, overlapped with the next step')
+            if gather.multicast:
+                exchange = ('kgs_exchange_push: ONE copy-engine push of the compact tables to the NVSwitch multicast address '
+                            '(replicated into every rank\'s buffer) + one barrier kernel, overlapped with the next step')
         except Exception as exc:                 # noqa: BLE001
             sys.stderr.write('rank %d: peer exchange not available (%s); using the NCCL all_gather\n' % (rank, exc))
             ok = torch.tensor([0], device='cuda')

@@ -249,6 +249,11 @@ int kgs_fetch_region(kgs_handle h, void* host_dst, size_t nbytes);
  *   collective).  libnccl is looked up with dlopen at the first call; KGS_ERR_STATE if absent. */
 int kgs_exchange_setup(kgs_handle h, int n_ranks, int my_rank, void* const* gathered, void* const* flags,
                        size_t slot_bytes);
+/* Optional, after setup: mc_gathered = ONE address behind which the NVSwitch replicates every write into
+ * the gathered buffers of all ranks (an NVLS multicast mapping of the same allocation, e.g.
+ * cuMulticastBindMem or a symmetric-memory allocator's multicast pointer).  push then issues one copy
+ * instead of n_ranks: the tables are read from this GPU's memory once and leave it once.  NULL = off. */
+int kgs_exchange_set_multicast(kgs_handle h, void* mc_gathered);
 int kgs_exchange_push(kgs_handle h, void** d_gathered, size_t* bytes_per_rank);
 int kgs_exchange_join(kgs_handle h);
 int kgs_exchange_sync(kgs_handle h);

@@ -125,6 +125,7 @@ struct kgs_ctx {
     int region_half = 0;                       // half the open job writes
     int px_n = 0, px_me = 0;                   // peer exchange: ranks, my rank
     char* px_gathered[kMaxRanks] = {nullptr};  // rank r's gathered buffer as mapped on this device
+    char* px_multicast = nullptr;              // the gathered buffers of ALL ranks behind one multicast address (optional)
     PeerFlags px_flags{};
     size_t px_slot = 0;
     uint32_t px_seq = 0;
@@ -1320,6 +1321,16 @@ int kgs_exchange_setup(kgs_handle h, int n_ranks, int my_rank, void* const* gath
     h->px_me = my_rank;
     h->px_slot = slot_bytes;
     h->px_seq = 0;
+    h->px_multicast = nullptr;
+    return KGS_OK;
+}
+
+int kgs_exchange_set_multicast(kgs_handle h, void* mc_gathered) {
+    if (!h) return KGS_ERR_ARG;
+    if (h->px_n == 0) return fail(h, KGS_ERR_STATE, "kgs_exchange_set_multicast: call kgs_exchange_setup first");
+    KGS_CUDA(h, cudaSetDevice(h->device));
+    KGS_CUDA(h, cudaStreamSynchronize(h->xchg));
+    h->px_multicast = static_cast<char*>(mc_gathered);
     return KGS_OK;
 }
 
@@ -1339,14 +1350,21 @@ int kgs_exchange_push(kgs_handle h, void** d_gathered, size_t* bytes_per_rank) {
     const int half = (int)(seq & 1u);
     KGS_CUDA(h, cudaEventRecord(h->fin_done, h->compute));
     KGS_CUDA(h, cudaStreamWaitEvent(h->xchg, h->fin_done, 0));
-    for (int k = 0; k < n; ++k) {   // the neighbour first: spreads the links
+    static const int dbg = getenv("KGS_XCHG_DEBUG") ? atoi(getenv("KGS_XCHG_DEBUG")) : 0;   // experiments only: 1 no self copy, 2 no barrier, 4 no peer copies
+    if (h->px_multicast) {   // ONE copy: the NVSwitch replicates the writes into every rank's buffer (this one included)
+        char* dst = h->px_multicast + ((size_t)half * n + me) * h->px_slot;
+        KGS_CUDA(h, cudaMemcpyAsync(dst, src, nbytes, cudaMemcpyDeviceToDevice, h->xchg));
+    }
+    for (int k = 0; k < n && !h->px_multicast; ++k) {   // the neighbour first: spreads the links
         const int r = (me + 1 + k) % n;
+        if ((r == me && (dbg & 1)) || (r != me && (dbg & 4))) continue;
         char* dst = h->px_gathered[r] + ((size_t)half * n + me) * h->px_slot;
         KGS_CUDA(h, cudaMemcpyAsync(dst, src, nbytes, cudaMemcpyDeviceToDevice, h->xchg));
     }
-    launch(h, KGS_K_EXCHANGE, h->xchg, [&] {
-        k_peer_barrier<<<1, 32, 0, h->xchg>>>(h->px_flags, n, me, half, seq, 10ull * 1000 * 1000 * 1000, h->px_timeout);
-    });
+    if (!(dbg & 2))
+        launch(h, KGS_K_EXCHANGE, h->xchg, [&] {
+            k_peer_barrier<<<1, 32, 0, h->xchg>>>(h->px_flags, n, me, half, seq, 10ull * 1000 * 1000 * 1000, h->px_timeout);
+        });
     KGS_CUDA(h, cudaGetLastError());
     KGS_CUDA(h, cudaEventRecord(h->region_free[h->region_half], h->xchg));
     h->region_busy[h->region_half] = true;

@@ -309,6 +309,10 @@ class Engine:
         self._ck(self._lib.kgs_exchange_setup(self._h, int(n_ranks), int(my_rank), arr(*[int(p) for p in gathered_ptrs]),
                                               arr(*[int(p) for p in flag_ptrs]), int(slot_bytes)))
 
+    def exchange_set_multicast(self, mc_ptr):
+        """One multicast address for all ranks' gathered buffers (kgs_exchange_set_multicast); 0/None = off."""
+        self._ck(self._lib.kgs_exchange_set_multicast(self._h, int(mc_ptr) if mc_ptr else None))
+
     def exchange_push(self):
         """Push the finalized job's tables into every rank's gathered buffer (asynchronous, exchange
         stream).  Returns (device address of this job's gathered half on this device, bytes per rank)."""

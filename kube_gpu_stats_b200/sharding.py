@@ -219,11 +219,12 @@ class PeerExchange:
 
     FLAG_BYTES = 4096
 
-    def __init__(self, engine, world, rank, slot_bytes, group=None):
+    def __init__(self, engine, world, rank, slot_bytes, group=None, multicast=False):
         import torch
         import torch.distributed as dist
         import torch.distributed._symmetric_memory as symm
         self.eng, self.world, self.rank = engine, world, rank
+        self.multicast = False
         self.group = group if group is not None else dist.group.WORLD
         self.slot = (int(slot_bytes) + 255) // 256 * 256
         dev = torch.device('cuda', engine.device)
@@ -238,6 +239,13 @@ class PeerExchange:
         flags = [p + 2 * world * self.slot for p in bases]
         engine.exchange_setup(world, rank, bases, flags, self.slot)
         self._base = bases[rank]
+        if multicast:                           # one push through the switch's multicast address, if every rank has one
+            mc = int(getattr(self.hdl, 'multicast_ptr', 0) or 0)
+            have = torch.tensor([1 if mc else 0], dtype=torch.int64, device=dev)
+            dist.all_reduce(have, op=dist.ReduceOp.MIN, group=self.group)
+            if int(have):
+                engine.exchange_set_multicast(mc)
+                self.multicast = True
         dist.barrier(group=self.group)          # nobody pushes before every rank's flag words are zero
 
     def push(self, want_view=True):

@@ -75,6 +75,13 @@ def _worker(rank, world, port, out_dir):
             view = px.push()
         eng.exchange_sync()
         results['c_peer'] = view.cpu().numpy()
+        if os.environ.get('KGS_TEST_MULTICAST') == '1':     # one copy through the NVSwitch multicast address
+            mx = sharding.PeerExchange(eng, world, rank, nbytes, multicast=True)
+            for i in range(3):
+                eng.window_stats_device(spec)
+                view = mx.push()
+            eng.exchange_sync()
+            results['c_multicast' if mx.multicast else 'c_peer2'] = view.cpu().numpy()
         ids = [eng.nccl_unique_id() if rank == 0 else None]
         dist.broadcast_object_list(ids, src=0)
         eng.nccl_init(ids[0], world, rank)
@@ -91,8 +98,10 @@ def _worker(rank, world, port, out_dir):
         eng.exchange_sync()
         results['c_nccl_torch'] = view.cpu().numpy()
     layout = eng.packed_layout(KINDS)
-    for name in ('nccl', 'c_peer', 'c_nccl_own', 'c_nccl_torch'):
+    for name in results:
         np.testing.assert_array_equal(results['peer'], results[name], err_msg=name)
+    if rank == 0:
+        print('transports with identical bytes:', sorted(results))
     if rank == 0:
         per_rank = [sharding.decode_packed(results['peer'][r], layout) for r in range(world)]
         np.savez(os.path.join(out_dir, 'tables.npz'),
