@@ -221,7 +221,7 @@ def run_b200(args):
         try:
             if os.environ.get('KGS_EXCHANGE', 'peer') != 'peer':
                 raise RuntimeError('KGS_EXCHANGE asks for NCCL')
-            gather = sharding.PeerExchange(eng, world, rank, slot_bytes,
+            gather = sharding.PeerExchange(eng, world, rank, slot_bytes, self_copy=False,   # own tables stay in the result region
                                            multicast=os.environ.get('KGS_EXCHANGE_MULTICAST', '0') == '1')
             exchange = ('kgs_exchange_push: copy-engine pushes of the compact tables into every peer over NVLink '
                         '(peer-mapped symmetric memory) + one barrier kernel, overlapped with the next step')

@@ -254,6 +254,10 @@ int kgs_exchange_setup(kgs_handle h, int n_ranks, int my_rank, void* const* gath
  * cuMulticastBindMem or a symmetric-memory allocator's multicast pointer).  push then issues one copy
  * instead of n_ranks: the tables are read from this GPU's memory once and leave it once.  NULL = off. */
 int kgs_exchange_set_multicast(kgs_handle h, void* mc_gathered);
+/* on = 0: push leaves slot my_rank of this rank's OWN gathered buffer alone - its tables are in its result
+ * region anyway (kgs_exchange_region), with the same lifetime; saves a device-local copy per push.  Default 1
+ * (the gathered buffer is complete, like the result of an all-gather). */
+int kgs_exchange_set_self_copy(kgs_handle h, int on);
 int kgs_exchange_push(kgs_handle h, void** d_gathered, size_t* bytes_per_rank);
 int kgs_exchange_join(kgs_handle h);
 int kgs_exchange_sync(kgs_handle h);

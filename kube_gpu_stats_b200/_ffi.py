@@ -80,6 +80,7 @@ def load(path=LIB_PATH):
         'kgs_fetch_region': [H, vp, C.c_size_t],
         'kgs_exchange_setup': [H, C.c_int, C.c_int, vp, vp, C.c_size_t],
         'kgs_exchange_set_multicast': [H, vp],
+        'kgs_exchange_set_self_copy': [H, C.c_int],
         'kgs_exchange_push': [H, C.POINTER(vp), C.POINTER(C.c_size_t)],
         'kgs_exchange_join': [H],
         'kgs_exchange_sync': [H],

@@ -125,6 +125,7 @@ struct kgs_ctx {
     int region_half = 0;                       // half the open job writes
     int px_n = 0, px_me = 0;                   // peer exchange: ranks, my rank
     char* px_gathered[kMaxRanks] = {nullptr};  // rank r's gathered buffer as mapped on this device
+    bool px_self_copy = true;                  // also copy this rank's tables into its own gathered buffer
     char* px_multicast = nullptr;              // the gathered buffers of ALL ranks behind one multicast address (optional)
     PeerFlags px_flags{};
     size_t px_slot = 0;
@@ -1325,6 +1326,12 @@ int kgs_exchange_setup(kgs_handle h, int n_ranks, int my_rank, void* const* gath
     return KGS_OK;
 }
 
+int kgs_exchange_set_self_copy(kgs_handle h, int on) {
+    if (!h) return KGS_ERR_ARG;
+    h->px_self_copy = on != 0;
+    return KGS_OK;
+}
+
 int kgs_exchange_set_multicast(kgs_handle h, void* mc_gathered) {
     if (!h) return KGS_ERR_ARG;
     if (h->px_n == 0) return fail(h, KGS_ERR_STATE, "kgs_exchange_set_multicast: call kgs_exchange_setup first");
@@ -1357,7 +1364,7 @@ int kgs_exchange_push(kgs_handle h, void** d_gathered, size_t* bytes_per_rank) {
     }
     for (int k = 0; k < n && !h->px_multicast; ++k) {   // the neighbour first: spreads the links
         const int r = (me + 1 + k) % n;
-        if ((r == me && (dbg & 1)) || (r != me && (dbg & 4))) continue;
+        if ((r == me && ((dbg & 1) || !h->px_self_copy)) || (r != me && (dbg & 4))) continue;
         char* dst = h->px_gathered[r] + ((size_t)half * n + me) * h->px_slot;
         KGS_CUDA(h, cudaMemcpyAsync(dst, src, nbytes, cudaMemcpyDeviceToDevice, h->xchg));
     }

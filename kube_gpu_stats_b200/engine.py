@@ -313,6 +313,9 @@ class Engine:
         """One multicast address for all ranks' gathered buffers (kgs_exchange_set_multicast); 0/None = off."""
         self._ck(self._lib.kgs_exchange_set_multicast(self._h, int(mc_ptr) if mc_ptr else None))
 
+    def exchange_set_self_copy(self, on):
+        self._ck(self._lib.kgs_exchange_set_self_copy(self._h, 1 if on else 0))
+
     def exchange_push(self):
         """Push the finalized job's tables into every rank's gathered buffer (asynchronous, exchange
         stream).  Returns (device address of this job's gathered half on this device, bytes per rank)."""

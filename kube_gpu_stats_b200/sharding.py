@@ -219,7 +219,7 @@ class PeerExchange:
 
     FLAG_BYTES = 4096
 
-    def __init__(self, engine, world, rank, slot_bytes, group=None, multicast=False):
+    def __init__(self, engine, world, rank, slot_bytes, group=None, multicast=False, self_copy=True):
         import torch
         import torch.distributed as dist
         import torch.distributed._symmetric_memory as symm
@@ -239,6 +239,7 @@ class PeerExchange:
         flags = [p + 2 * world * self.slot for p in bases]
         engine.exchange_setup(world, rank, bases, flags, self.slot)
         self._base = bases[rank]
+        engine.exchange_set_self_copy(self_copy)   # False: this rank reads its own tables from its result region
         if multicast:                           # one push through the switch's multicast address, if every rank has one
             mc = int(getattr(self.hdl, 'multicast_ptr', 0) or 0)
             have = torch.tensor([1 if mc else 0], dtype=torch.int64, device=dev)

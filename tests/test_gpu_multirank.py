@@ -75,6 +75,18 @@ def _worker(rank, world, port, out_dir):
             view = px.push()
         eng.exchange_sync()
         results['c_peer'] = view.cpu().numpy()
+        # without the device-local copy: the peers' rows arrive as before, the own row is left to the result region
+        nx = sharding.PeerExchange(eng, world, rank, nbytes, self_copy=False)
+        eng.window_stats_device(spec)
+        view = nx.push()
+        eng.exchange_sync()
+        got = view.cpu().numpy()
+        others = [r for r in range(world) if r != rank]
+        np.testing.assert_array_equal(got[others], results['peer'][others])
+        assert not got[rank].any(), 'the own slot must stay untouched'
+        own = torch.as_tensor(sharding._DeviceBytes(eng.exchange_region()[0], nbytes), device='cuda:%d' % rank).cpu().numpy()
+        np.testing.assert_array_equal(own, results['peer'][rank])
+        eng.exchange_set_self_copy(True)
         if os.environ.get('KGS_TEST_MULTICAST') == '1':     # one copy through the NVSwitch multicast address
             mx = sharding.PeerExchange(eng, world, rank, nbytes, multicast=True)
             for i in range(3):
