@@ -101,12 +101,13 @@ int kgs_batch_append(kgs_handle h, const uint32_t* ts, const uint32_t* gpu_gid, 
  * its own run.  No reference counterpart (ingestion, north_star subsystem 1).  Queued on the compute
  * stream; needs a second copy of the batch in device memory. */
 int kgs_reorder_batch(kgs_handle h);
-/* kgs_ingest and the first kgs_batch_append look at a few hundred samples of the host columns: a batch
- * that interleaves several series with a short period (all processes of a GPU, or all GPUs of a node,
- * reported second by second) is marked, and kgs_stats_accumulate then reads a series-major copy of it
- * (the same sort, into the other batch slot) instead.  The resident batch itself stays as ingested:
- * kgs_probe and kgs_fetch_batch answer in the caller's order.  On by default; 0 switches it off
- * (also KGS_AUTO_REORDER=0).  Columns adopted from device memory are never looked at. */
+/* kgs_ingest and the first kgs_batch_append look at a few hundred samples of the host columns.  A batch that
+ * interleaves several series with a short period (all processes of a GPU, or the GPUs of a small box, reported
+ * second by second) is accumulated from a series-major copy (the same sort, into the other batch slot); so is
+ * any other disordered batch (a time-major feed of many GPUs, a random stream) when the job has percentiles -
+ * without percentiles the per-CTA accumulator cache handles a random stream faster than a sort would.  The
+ * resident batch itself stays as ingested: kgs_probe and kgs_fetch_batch answer in the caller's order.  On by
+ * default; 0 switches it off (also KGS_AUTO_REORDER=0).  Columns adopted from device memory are never looked at. */
 int kgs_set_auto_reorder(kgs_handle h, int on);
 /* Copy the resident batch's columns back to host arrays of n entries (any pointer may be NULL). Blocking. */
 int kgs_fetch_batch(kgs_handle h, uint32_t* ts, uint32_t* gpu_gid, uint32_t* pid, uint32_t* util);

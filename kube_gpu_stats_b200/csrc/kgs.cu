@@ -36,7 +36,7 @@ struct Batch {
     const uint32_t* ptr[4] = {nullptr, nullptr, nullptr, nullptr};
     uint64_t n = 0;
     cudaEvent_t ready = nullptr, consumed = nullptr;
-    bool interleaved = false;   // host columns looked like a feed that interleaves several series (looks_interleaved)
+    int order_class = 0;        // what the host columns looked like at ingest (input_order_class): 0 long runs, 1 disordered, 2 interleaved series
 };
 
 struct KindState {
@@ -248,34 +248,38 @@ cudaError_t launch_after(void (*kern)(P), unsigned grid, unsigned block, cudaStr
 
 inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
-// Does this batch interleave several series - a collector that reports all processes of a GPU (or all
-// GPUs of a node) second by second?  Then nearly every sample starts a new run and the statistics
-// kernels crawl (they stay exact).  Three windows of up to 512 samples are looked at on the host:
-// a window votes yes when at least a quarter of its neighbours differ in (gpu, pid) AND the keys
-// repeat with some period of 2..64 samples.  Collector order fails the first test after a few
-// hundred compares; a random stream (configs[2]) fails the second, and is left to the accumulator
-// cache, which is the faster way for it.
-bool looks_interleaved(const uint32_t* gid, const uint32_t* pid, uint64_t n) {
-    if (n < 128) return false;
+// What order is this batch in?  Three windows of up to 512 samples are looked at on the host.
+//   0  long runs: fewer than a quarter of the neighbours differ in (gpu, pid) - collector order; decided after a
+//      few hundred compares;
+//   2  interleaved series: most neighbours differ AND the keys repeat with a period of 2..64 samples - a collector
+//      that reports all processes of a GPU (or the GPUs of a small box) second by second;
+//   1  disordered otherwise - a time-major feed of many GPUs, a random stream (configs[2]).
+// In classes 1 and 2 nearly every sample starts a new run: the kernels stay exact but crawl, and a percentile job
+// pays a 16-byte run descriptor per sample and key kind.  kgs_stats_accumulate therefore reads a series-major copy
+// of a class-2 batch always, and of a class-1 batch when the job has percentiles (without them the per-CTA
+// accumulator cache is the faster way for a random stream).
+int input_order_class(const uint32_t* gid, const uint32_t* pid, uint64_t n) {
+    if (n < 128) return 0;
     const uint64_t win = n < 512 ? n : 512;
     const uint64_t at[3] = {0, (n - win) / 2, n - win};
-    int yes = 0;
+    int disordered = 0, periodic = 0;
     for (int w = 0; w < 3; ++w) {
         const uint32_t* g = gid + at[w];
         const uint32_t* p = pid + at[w];
         uint64_t changes = 0;
         for (uint64_t i = 0; i + 1 < win; ++i) changes += (g[i] != g[i + 1]) | (p[i] != p[i + 1]);
         if (changes * 4 < win) continue;
+        ++disordered;
         for (uint64_t period = 2; period <= 64 && period * 2 < win; ++period) {
             uint64_t same = 0;
             for (uint64_t i = 0; i + period < win; ++i) same += (g[i] == g[i + period]) & (p[i] == p[i + period]);
             if (same * 4 >= 3 * (win - period)) {
-                ++yes;
+                ++periodic;
                 break;
             }
         }
     }
-    return yes >= 2;
+    return periodic >= 2 ? 2 : (disordered >= 2 ? 1 : 0);
 }
 
 int grid_for(uint64_t work_items, int per_block, int max_blocks) {
@@ -441,7 +445,7 @@ int kgs_ingest(kgs_handle h, const uint32_t* ts, const uint32_t* gpu_gid, const 
         if (n) KGS_CUDA(h, cudaMemcpyAsync(B.col[c].p, src[c], n * 4, cudaMemcpyHostToDevice, h->copy));
     }
     B.n = n;
-    B.interleaved = h->auto_reorder && looks_interleaved(gpu_gid, pid, n);
+    B.order_class = h->auto_reorder ? input_order_class(gpu_gid, pid, n) : 0;
     KGS_CUDA(h, cudaEventRecord(B.ready, h->copy));
     h->cur = b;
     h->shadow_valid = false;
@@ -462,7 +466,7 @@ int kgs_batch_reserve(kgs_handle h, uint64_t capacity) {
         B.ptr[c] = static_cast<const uint32_t*>(B.col[c].p);
     }
     B.n = 0;
-    B.interleaved = false;
+    B.order_class = 0;
     KGS_CUDA(h, cudaEventRecord(B.ready, h->copy));
     h->cur = b;
     h->shadow_valid = false;
@@ -483,7 +487,7 @@ int kgs_batch_append(kgs_handle h, const uint32_t* ts, const uint32_t* gpu_gid, 
     // kernels queued on the compute stream may be reading the part already there; appending does not touch it
     for (int c = 0; c < 4; ++c)
         if (n) KGS_CUDA(h, cudaMemcpyAsync(static_cast<uint32_t*>(B.col[c].p) + B.n, src[c], n * 4, cudaMemcpyHostToDevice, h->copy));
-    if (B.n == 0 && n) B.interleaved = h->auto_reorder && looks_interleaved(gpu_gid, pid, n);
+    if (B.n == 0 && n) B.order_class = h->auto_reorder ? input_order_class(gpu_gid, pid, n) : 0;
     B.n += n;
     h->shadow_valid = false;
     KGS_CUDA(h, cudaEventRecord(B.ready, h->copy));
@@ -553,7 +557,7 @@ static int reorder_impl(kgs_handle h, bool switch_cur) {
     KGS_CUDA(h, cudaEventRecord(src.consumed, st));
     for (int c = 0; c < 4; ++c) dst.ptr[c] = slot_cols[c];
     dst.n = n;
-    dst.interleaved = false;
+    dst.order_class = 0;
     KGS_CUDA(h, cudaEventRecord(dst.ready, st));
     if (switch_cur) {
         h->cur = (h->cur + 1) & 1;
@@ -600,7 +604,7 @@ int kgs_adopt_device_batch(kgs_handle h, const uint32_t* d_ts, const uint32_t* d
     Batch& B = h->batch[b];
     B.ptr[0] = d_ts; B.ptr[1] = d_gpu_gid; B.ptr[2] = d_pid; B.ptr[3] = d_util;
     B.n = n;
-    B.interleaved = false;   // device columns: the host cannot look; the caller may call kgs_reorder_batch
+    B.order_class = 0;   // device columns: the host cannot look; the caller may call kgs_reorder_batch
     KGS_CUDA(h, cudaEventRecord(B.ready, h->copy));
     h->cur = b;
     h->shadow_valid = false;
@@ -914,12 +918,15 @@ int kgs_stats_accumulate(kgs_handle h) {
     if (h->cur < 0) return fail(h, KGS_ERR_STATE, "kgs_stats_accumulate: no resident batch (call kgs_ingest)");
     KGS_CUDA(h, cudaSetDevice(h->device));
     if (h->batch[h->cur].n == 0) return KGS_OK;
-    // a batch that interleaves its series is accumulated from a series-major copy (same tables, long runs)
-    if (h->auto_reorder && h->batch[h->cur].interleaved && !h->shadow_valid && h->batch[h->cur].n >= 2) {
+    // a batch that interleaves its series - or, for a percentile job, any disordered batch - is accumulated from a
+    // series-major copy (same tables, long runs)
+    const int oc = h->batch[h->cur].order_class;
+    const bool want_sorted = h->auto_reorder && (oc == 2 || (oc == 1 && h->spec.n_q > 0));
+    if (want_sorted && !h->shadow_valid && h->batch[h->cur].n >= 2) {
         int rc0 = reorder_impl(h, false);
         if (rc0) return rc0;
     }
-    const bool from_shadow = h->shadow_valid && h->batch[h->cur].interleaved;
+    const bool from_shadow = h->shadow_valid && want_sorted;
     Batch& B = h->batch[from_shadow ? ((h->cur + 1) & 1) : h->cur];
     const kgs_window_spec& sp = h->spec;
     const bool pct = sp.n_q > 0;

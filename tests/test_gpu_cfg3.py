@@ -20,6 +20,7 @@ def test_cfg3_scaled_all_kinds_p95(engine):
     10 minutes, p95 (every cell far beyond a thread's histogram: the warp-per-cell path)."""
     tr = synth.config(3, scale=0.02)
     kinds = ('pod', 'gpu', 'node')
+    engine.set_auto_reorder(False)          # the stream as it comes: one run per sample, accumulator cache, run log retry
     engine.build_join(tr.keys, tr.pod_ids, tr.n_pods)
     engine.ingest(tr.ts, tr.gpu_gid, tr.pid, tr.util)
     np.testing.assert_array_equal(engine.probe(8), ws.probe_np(tr.keys, tr.pod_ids, tr.gpu_gid, tr.pid, 8))
@@ -31,6 +32,15 @@ def test_cfg3_scaled_all_kinds_p95(engine):
         want = ws.window_stats_np(tr.ts, tr.gpu_gid, tr.pid, tr.util, tr.keys, tr.pod_ids, key_kind=KINDS[k], metric=0,
                                   gpus_per_node=8, t0=tr.t0, step=600, width=600, n_windows=6, n_keys=nk, qs=(0.95,))
         assert_stats_equal(got[k], want, what='cfg3 x0.02 ' + k)
+    # the default: a disordered batch of a percentile job is accumulated from a series-major copy - same tables
+    engine.set_auto_reorder(True)
+    engine.set_profiling(True)
+    engine.ingest(tr.ts, tr.gpu_gid, tr.pid, tr.util)
+    again = engine.window_stats(kinds=kinds, metric='sm', gpus_per_node=8, t0=tr.t0, step=600, n_windows=6,
+                                n_gpus=tr.n_gpus, n_nodes=tr.n_nodes, qs=(0.95,))
+    assert engine.kernel_times()['reorder'][1] > 0, 'the sorted copy was not made'
+    for k in kinds:
+        assert_stats_equal(again[k], got[k], what='cfg3 x0.02 sorted copy ' + k)
 
 
 def test_cfg3_scaled_no_percentiles_uses_the_cache(engine):

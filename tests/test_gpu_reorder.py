@@ -93,3 +93,40 @@ def test_interleaved_feed_is_accumulated_from_a_sorted_copy(engine, shape):
         np.testing.assert_array_equal(engine.probe(8), ws.probe_np(tr.keys, tr.pod_ids, live.gpu_gid, live.pid, 8))
         for g, w in zip(engine.fetch_batch(), cols):
             np.testing.assert_array_equal(g, w)
+
+
+def test_full_size_time_major_feed(engine):
+    """BASELINE configs[1] delivered second by second (all 8 000 GPUs of a second together, 28.8 M samples):
+    the shape at which an out-of-bounds access was once seen during the reorder work, and a feed whose period
+    (8 000) is far beyond what the interleave test looks for - it is classed as disordered and, the job having
+    a percentile, accumulated from a sorted copy.  Size-independent properties on the whole result and the
+    exact oracle on the first 10 nodes; an explicit kgs_reorder_batch of the same batch gives the same tables."""
+    tr = synth.config(2)
+    o = np.argsort(tr.ts, kind='stable')
+    ts, gid, pid, util = tr.ts[o], tr.gpu_gid[o], tr.pid[o], tr.util[o]
+    kw = dict(kinds=('pod', 'gpu', 'node'), metric='sm', gpus_per_node=8, t0=tr.t0, step=60, n_windows=60,
+              n_gpus=tr.n_gpus, n_nodes=tr.n_nodes, qs=(0.95,))
+    engine.build_join(tr.keys, tr.pod_ids, tr.n_pods)
+    engine.set_profiling(True)
+    engine.ingest(ts, gid, pid, util)
+    got = engine.window_stats(**kw)
+    assert engine.kernel_times()['reorder'][1] > 0
+    for k in kw['kinds']:
+        assert int(got[k]['count'].sum()) == tr.n, k
+    assert int(got['pod']['sum'].sum()) == int((tr.util & 0xFF).astype(np.uint64).sum())
+    g = np.asarray(got['gpu']['count']).reshape(tr.n_nodes, 8, 60)
+    np.testing.assert_array_equal(g.sum(axis=1).reshape(-1), got['node']['count'])
+    nodes = 10
+    m = nodes * 8 * 3600
+    pods = int(np.searchsorted(tr.pod_node, nodes))
+    for kind, kid, nk in (('pod', ws.KEY_POD, pods), ('gpu', ws.KEY_GPU, nodes * 8), ('node', ws.KEY_NODE, nodes)):
+        want = ws.window_stats_np(tr.ts[:m], tr.gpu_gid[:m], tr.pid[:m], tr.util[:m], tr.keys, tr.pod_ids, key_kind=kid,
+                                  metric=0, gpus_per_node=8, t0=tr.t0, step=60, width=60, n_windows=60, n_keys=nk, qs=(0.95,))
+        head = {f: (np.asarray(v)[:, :nk * 60] if f == 'pct' else np.asarray(v)[:nk * 60]) for f, v in got[kind].items()}
+        assert_stats_equal(head, want, what='time-major full size ' + kind)
+    engine.set_auto_reorder(False)
+    engine.ingest(ts, gid, pid, util)
+    engine.reorder()
+    again = engine.window_stats(**kw)
+    for k in kw['kinds']:
+        assert_stats_equal(again[k], got[k], what='explicit reorder ' + k)
