@@ -3,7 +3,9 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <atomic>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/kgs.h"
@@ -88,6 +90,10 @@ struct kgs_ctx {
         mx_long, mx_out, mx_ctl;
     uint64_t mx_n_series = 0, mx_n_samples = 0, mx_n_long = 0;
     std::vector<cudaEvent_t> mx_arrived;   // one event per piece of text on the copy stream
+    void* mx_stage[3] = {nullptr, nullptr, nullptr};          // pinned pieces a pageable answer is staged through
+    cudaEvent_t mx_stage_free[3] = {nullptr, nullptr, nullptr};
+    size_t mx_stage_bytes = 0;
+    int mx_stage_threads = 0;              // host threads copying into a pinned piece (0 = half the cores, at most 8)
     uint32_t mx_piece_bytes = 32u << 20;
     bool mx_valid = false;
     size_t clear_bytes = 0;
@@ -282,6 +288,70 @@ int input_order_class(const uint32_t* gid, const uint32_t* pid, uint64_t n) {
     return periodic >= 2 ? 2 : (disordered >= 2 ? 1 : 0);
 }
 
+// A pageable answer (the `bytes` object an HTTP client hands over) on its way to the device.  cudaMemcpyAsync from
+// pageable memory goes through the driver's own small staging buffer, synchronously: 10 GB/s.  Here a thread of the
+// library copies piece after piece into three pinned buffers with several host threads and queues the pinned piece on
+// the copy stream, so the host copy of piece i+1 runs beside the DMA of piece i and the decode of piece i-1.
+struct TextStager {
+    kgs_ctx* h = nullptr;
+    const char* text = nullptr;
+    char* dtext = nullptr;
+    uint64_t nbytes = 0;
+    size_t padded = 0, piece_bytes = 0;
+    uint32_t n_pieces = 0;
+    int n_threads = 1;
+    std::atomic<uint32_t> issued{0};       // pieces whose copy and arrival event have been queued
+    std::atomic<int> cuda_error{0};
+    std::atomic<bool> stop{false};
+    std::thread worker;
+
+    static void host_copy(char* dst, const char* src, size_t len, int n_threads) {
+        if (n_threads <= 1 || len < (4u << 20)) {
+            memcpy(dst, src, len);
+            return;
+        }
+        std::vector<std::thread> helpers;
+        const size_t share = (len / n_threads + 4095) & ~(size_t)4095;
+        for (int t = 1; t < n_threads; ++t) {
+            const size_t a = std::min(len, (size_t)t * share), b = std::min(len, a + share);
+            if (b > a) helpers.emplace_back([=] { memcpy(dst + a, src + a, b - a); });
+        }
+        memcpy(dst, src, std::min(len, share));
+        for (auto& t : helpers) t.join();
+    }
+
+    void run() {
+        cudaError_t e = cudaSetDevice(h->device);
+        for (uint32_t i = 0; i < n_pieces && e == cudaSuccess && !stop.load(); ++i) {
+            const int slot = (int)(i % 3);
+            const size_t off = (size_t)i * piece_bytes;
+            const size_t len = off < nbytes ? std::min<size_t>(nbytes - off, piece_bytes) : 0;
+            if (i >= 3) e = cudaEventSynchronize(h->mx_stage_free[slot]);      // the DMA that last read this buffer
+            if (e == cudaSuccess && len) {
+                host_copy(static_cast<char*>(h->mx_stage[slot]), text + off, len, n_threads);
+                e = cudaMemcpyAsync(dtext + off, h->mx_stage[slot], len, cudaMemcpyHostToDevice, h->copy);
+            }
+            if (e == cudaSuccess && i + 1 == n_pieces) e = cudaMemsetAsync(dtext + nbytes, 0, padded - nbytes, h->copy);
+            if (e == cudaSuccess) e = cudaEventRecord(h->mx_arrived[i], h->copy);
+            if (e == cudaSuccess) e = cudaEventRecord(h->mx_stage_free[slot], h->copy);
+            if (e == cudaSuccess) issued.store(i + 1, std::memory_order_release);
+        }
+        if (e != cudaSuccess) cuda_error.store((int)e);
+    }
+    // true once piece k - 1 has been queued (false: the worker failed)
+    bool wait_issued(uint32_t k) {
+        while (issued.load(std::memory_order_acquire) < k) {
+            if (cuda_error.load()) return false;
+            std::this_thread::yield();
+        }
+        return true;
+    }
+    ~TextStager() {
+        stop.store(true);
+        if (worker.joinable()) worker.join();
+    }
+};
+
 int grid_for(uint64_t work_items, int per_block, int max_blocks) {
     uint64_t b = (work_items + per_block - 1) / per_block;
     if (b < 1) b = 1;
@@ -344,6 +414,7 @@ int kgs_create(int device, kgs_handle* out) {
     if (const char* e = getenv("KGS_FINALIZE_GROUPS")) h->groups_path = atoi(e) != 0;
     if (const char* e = getenv("KGS_AUTO_REORDER")) h->auto_reorder = atoi(e) != 0;
     if (const char* e = getenv("KGS_PDL")) h->pdl = atoi(e) != 0;
+    if (const char* e = getenv("KGS_STAGE_THREADS")) { const int v = atoi(e); if (v >= 0 && v <= 64) h->mx_stage_threads = v; }
     if (const char* e = getenv("KGS_THREAD_CELL_MAX")) { const int v = atoi(e); if (v >= 1 && v <= 65535) h->thread_cell_max = (uint32_t)v; }
     if (h->accum_tma) {
         h->accum_ctas_per_sm = 2;   // 64 KB of tile buffers + 42 KB static per CTA
@@ -391,6 +462,10 @@ int kgs_destroy(kgs_handle h) {
     for (DevBuf& b : h->sortbuf)
         if (b.p) cudaFree(b.p);
     for (auto e : h->mx_arrived) cudaEventDestroy(e);
+    for (int i = 0; i < 3; ++i) {
+        if (h->mx_stage[i]) cudaFreeHost(h->mx_stage[i]);
+        if (h->mx_stage_free[i]) cudaEventDestroy(h->mx_stage_free[i]);
+    }
     cudaStreamDestroy(h->copy);
     cudaStreamDestroy(h->compute);
     delete h;
@@ -1575,12 +1650,44 @@ int kgs_matrix_parse(kgs_handle h, const char* text, uint64_t nbytes, int result
         cudaStream_t s;
         ~DrainCopies() { cudaStreamSynchronize(s); }
     } drain{h->copy};
+    // pageable text is staged through pinned pieces by a thread of its own (TextStager); pinned text is queued directly
+    bool staged = false;
+    if (nbytes >= (8u << 20)) {
+        cudaPointerAttributes pa{};
+        const cudaError_t pe = cudaPointerGetAttributes(&pa, text);
+        if (pe != cudaSuccess) cudaGetLastError();
+        staged = pe != cudaSuccess || pa.type == cudaMemoryTypeUnregistered;
+    }
+    TextStager stager;   // declared after `drain`: joined first, then the copy stream is drained
+    if (staged) {
+        const size_t piece_bytes = (size_t)piece_ctas * kMxTile;
+        if (h->mx_stage_bytes < piece_bytes) {
+            for (int i = 0; i < 3; ++i) {
+                if (h->mx_stage[i]) KGS_CUDA(h, cudaFreeHost(h->mx_stage[i]));
+                h->mx_stage[i] = nullptr;
+                KGS_CUDA(h, cudaHostAlloc(&h->mx_stage[i], piece_bytes, cudaHostAllocDefault));
+                if (!h->mx_stage_free[i]) KGS_CUDA(h, cudaEventCreateWithFlags(&h->mx_stage_free[i], cudaEventDisableTiming));
+            }
+            h->mx_stage_bytes = piece_bytes;
+        }
+        int nt = h->mx_stage_threads;
+        if (nt <= 0) nt = std::max(1, std::min(8, (int)std::thread::hardware_concurrency() / 2));
+        stager.h = h; stager.text = text; stager.dtext = dtext; stager.nbytes = nbytes; stager.padded = padded;
+        stager.piece_bytes = piece_bytes; stager.n_pieces = n_pieces; stager.n_threads = nt;
+        stager.worker = std::thread([&stager] { stager.run(); });
+    }
+    auto piece_queued = [&](uint32_t k) -> int {   // the arrival event of piece k has been recorded (a wait on an unrecorded event is no wait)
+        if (staged && !stager.wait_issued(k + 1))
+            return fail(h, KGS_ERR_CUDA, std::string("staging the answer: ") + cudaGetErrorString((cudaError_t)stager.cuda_error.load()));
+        return KGS_OK;
+    };
     unsigned long long head[8];
     uint64_t k_done = 0, s_done = 0;
     uint32_t sent = 0;
     for (uint32_t i = 0; i < n_pieces; ++i) {
-        while (sent < n_pieces && sent <= i + 2)
+        while (!staged && sent < n_pieces && sent <= i + 2)
             if ((rc = send_piece(sent++))) return rc;
+        if ((rc = piece_queued(i))) return rc;
         KGS_CUDA(h, cudaStreamWaitEvent(st, h->mx_arrived[i], 0));
         P.cta_first = i * piece_ctas;
         P.cta_count = std::min(piece_ctas, n_ctas - P.cta_first);
@@ -1617,7 +1724,10 @@ int kgs_matrix_parse(kgs_handle h, const char* text, uint64_t nbytes, int result
         P.k_end = (uint32_t)ns;
         launch(h, KGS_K_PARSE, st, [&] { k_mx_emit<<<grid, kMxThreads, 0, st>>>(P); });
         // a pair that starts in the last bytes of this piece is read on into the next one
-        if (!P.last_piece) KGS_CUDA(h, cudaStreamWaitEvent(st, h->mx_arrived[i + 1], 0));
+        if (!P.last_piece) {
+            if ((rc = piece_queued(i + 1))) return rc;
+            KGS_CUDA(h, cudaStreamWaitEvent(st, h->mx_arrived[i + 1], 0));
+        }
         if (ns > k_done)
             launch(h, KGS_K_PARSE, st, [&] { k_mx_parse<<<(unsigned)((ns - k_done + 127) / 128), 128, 0, st>>>(P); });
         KGS_CUDA(h, cudaGetLastError());
