@@ -287,7 +287,7 @@ int kgs_segmented_mean_f64(kgs_handle h, const double* values, const uint64_t* o
  * `text` is a host pointer, nbytes < 4 GiB; it is copied in 32 MB pieces on the copy stream and a
  * piece is decoded while the next ones are in flight.  Pinned text is queued as it is; pageable text (the
  * bytes object an HTTP client returns) is staged by a thread of the library through three pinned pieces,
- * copied by several host threads (KGS_STAGE_THREADS, default half the cores, at most 8), so that the host
+ * copied by several host threads (KGS_STAGE_THREADS, default three quarters of the cores, at most 12), so that the host
  * copy, the DMA and the decode of consecutive pieces overlap.
  * Errors: KGS_ERR_PARSE if the text ends inside a string / with open brackets, or a sample is not
  * `[number, "text"]` with text that float() accepts (kgs_last_error names the byte); an escape

@@ -93,7 +93,7 @@ struct kgs_ctx {
     void* mx_stage[3] = {nullptr, nullptr, nullptr};          // pinned pieces a pageable answer is staged through
     cudaEvent_t mx_stage_free[3] = {nullptr, nullptr, nullptr};
     size_t mx_stage_bytes = 0;
-    int mx_stage_threads = 0;              // host threads copying into a pinned piece (0 = half the cores, at most 8)
+    int mx_stage_threads = 0;              // host threads copying into a pinned piece (0 = three quarters of the cores, at most 12)
     uint32_t mx_piece_bytes = 32u << 20;
     bool mx_valid = false;
     size_t clear_bytes = 0;
@@ -305,30 +305,54 @@ struct TextStager {
     std::atomic<bool> stop{false};
     std::thread worker;
 
-    static void host_copy(char* dst, const char* src, size_t len, int n_threads) {
-        if (n_threads <= 1 || len < (4u << 20)) {
+    // helper threads live for one answer and share every piece: job counter up = a new piece to copy
+    std::vector<std::thread> helpers;
+    std::atomic<uint64_t> job{0};
+    std::atomic<int> pending{0};
+    std::atomic<bool> helpers_stop{false};
+    char* job_dst = nullptr;
+    const char* job_src = nullptr;
+    size_t job_len = 0, job_share = 0;
+
+    void copy_share(int t) {
+        const size_t a = std::min(job_len, (size_t)t * job_share), b = std::min(job_len, a + job_share);
+        if (b > a) memcpy(job_dst + a, job_src + a, b - a);
+    }
+    void helper_loop(int t) {
+        uint64_t seen = 0;
+        for (;;) {
+            while (job.load(std::memory_order_acquire) == seen) {
+                if (helpers_stop.load(std::memory_order_relaxed)) return;
+                __builtin_ia32_pause();
+            }
+            seen = job.load(std::memory_order_acquire);
+            copy_share(t);
+            pending.fetch_sub(1, std::memory_order_release);
+        }
+    }
+    void host_copy(char* dst, const char* src, size_t len) {
+        if (helpers.empty() || len < (4u << 20)) {
             memcpy(dst, src, len);
             return;
         }
-        std::vector<std::thread> helpers;
-        const size_t share = (len / n_threads + 4095) & ~(size_t)4095;
-        for (int t = 1; t < n_threads; ++t) {
-            const size_t a = std::min(len, (size_t)t * share), b = std::min(len, a + share);
-            if (b > a) helpers.emplace_back([=] { memcpy(dst + a, src + a, b - a); });
-        }
-        memcpy(dst, src, std::min(len, share));
-        for (auto& t : helpers) t.join();
+        job_dst = dst; job_src = src; job_len = len;
+        job_share = (len / n_threads + 4095) & ~(size_t)4095;
+        pending.store((int)helpers.size(), std::memory_order_relaxed);
+        job.fetch_add(1, std::memory_order_release);
+        copy_share(0);
+        while (pending.load(std::memory_order_acquire)) __builtin_ia32_pause();
     }
 
     void run() {
         cudaError_t e = cudaSetDevice(h->device);
+        for (int t = 1; t < n_threads; ++t) helpers.emplace_back([this, t] { helper_loop(t); });
         for (uint32_t i = 0; i < n_pieces && e == cudaSuccess && !stop.load(); ++i) {
             const int slot = (int)(i % 3);
             const size_t off = (size_t)i * piece_bytes;
             const size_t len = off < nbytes ? std::min<size_t>(nbytes - off, piece_bytes) : 0;
             if (i >= 3) e = cudaEventSynchronize(h->mx_stage_free[slot]);      // the DMA that last read this buffer
             if (e == cudaSuccess && len) {
-                host_copy(static_cast<char*>(h->mx_stage[slot]), text + off, len, n_threads);
+                host_copy(static_cast<char*>(h->mx_stage[slot]), text + off, len);
                 e = cudaMemcpyAsync(dtext + off, h->mx_stage[slot], len, cudaMemcpyHostToDevice, h->copy);
             }
             if (e == cudaSuccess && i + 1 == n_pieces) e = cudaMemsetAsync(dtext + nbytes, 0, padded - nbytes, h->copy);
@@ -336,6 +360,9 @@ struct TextStager {
             if (e == cudaSuccess) e = cudaEventRecord(h->mx_stage_free[slot], h->copy);
             if (e == cudaSuccess) issued.store(i + 1, std::memory_order_release);
         }
+        helpers_stop.store(true);
+        for (auto& t : helpers) t.join();
+        helpers.clear();
         if (e != cudaSuccess) cuda_error.store((int)e);
     }
     // true once piece k - 1 has been queued (false: the worker failed)
@@ -1671,7 +1698,7 @@ int kgs_matrix_parse(kgs_handle h, const char* text, uint64_t nbytes, int result
             h->mx_stage_bytes = piece_bytes;
         }
         int nt = h->mx_stage_threads;
-        if (nt <= 0) nt = std::max(1, std::min(8, (int)std::thread::hardware_concurrency() / 2));
+        if (nt <= 0) nt = std::max(1, std::min(12, (int)std::thread::hardware_concurrency() * 3 / 4));
         stager.h = h; stager.text = text; stager.dtext = dtext; stager.nbytes = nbytes; stager.padded = padded;
         stager.piece_bytes = piece_bytes; stager.n_pieces = n_pieces; stager.n_threads = nt;
         stager.worker = std::thread([&stager] { stager.run(); });

@@ -63,11 +63,14 @@ def measure(series=8000, points=3600, cpu_series=256, reps=5):
         wall = (time.perf_counter() - t0) / reps
         launches = (eng.launch_count() - launches0) // reps
         assert (ns, nv) == (series, n_samples)
-        # pageable bytes object instead of the pinned buffer (what requests hands over)
-        t0 = time.perf_counter()
+        # pageable bytes object instead of the pinned buffer (what requests hands over); the first call pins the
+        # library's three staging pieces (once per handle), so it is not the one that is timed
         eng.matrix_parse(text)
-        eng.matrix_mean()
-        wall_pageable = time.perf_counter() - t0
+        t0 = time.perf_counter()
+        for _ in range(2):
+            eng.matrix_parse(text)
+            eng.matrix_mean()
+        wall_pageable = (time.perf_counter() - t0) / 2
     small = answer_text(cpu_series, points)
     t0 = time.perf_counter()
     ref = reference_decode(small)
