@@ -238,6 +238,10 @@ int kgs_fetch_region(kgs_handle h, void* host_dst, size_t nbytes);
  *   push: copies this rank's region into slot my_rank of the current half of EVERY rank's buffer
  *     (one cudaMemcpyAsync per rank, copy engines over NVLink), then one small kernel tells every
  *     peer "complete" and waits for every peer's word (10 s limit, reported by kgs_exchange_sync).
+ *     The copies are QUEUED when the next job's accumulate kernel has been launched (they then run
+ *     beside the finalize kernels, which are not bound by HBM, instead of beside the one kernel that
+ *     is); kgs_exchange_join / kgs_exchange_sync / kgs_sync / the next push queue them at once.
+ *     KGS_PUSH_DEFER=0: always at once.
  *     Every rank must push the same number of times.  *d_gathered = where rank r's tables of THIS
  *     job will be on this device: (char*)*d_gathered + r * slot_bytes, valid once the exchange stream
  *     has passed the push, until the next-but-one push.  Readers of a half must be ordered (same

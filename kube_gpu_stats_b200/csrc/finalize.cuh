@@ -67,7 +67,8 @@ struct FinParams {
     uint32_t g_gpn, g_nodes;             // gpus per node; nodes covered by the groups
     uint32_t packed_sum64;               // packed sums are u64 (a cell's sum may not fit 32 bits)
     uint32_t packed_compact;             // compact packed tables: count u16, sum 24 bits, max u8 (8-bit metrics)
-    uint32_t* esc_hdr;                   // compact: [0] = cells on the escape list, which follows at esc
+    uint32_t* esc_count;                 // compact: device counter of escape-list entries (in the job's control words)
+    uint32_t* esc_hdr;                   // compact: [0] = cells on the escape list (written once the finalize kernels are done), list follows at esc
     uint4* esc;                          //   {global cell, count, sum low, sum high} of a cell above 65 534 samples
     uint32_t esc_cap;
     uint32_t slide_chunk;                // windows per thread of k_finalize_slide
@@ -119,7 +120,7 @@ __device__ __forceinline__ void store_basics(const FinParams& P, const FinKind& 
         K.p_sum_hi[c] = (uint8_t)(total >> 16);
         static_cast<uint8_t*>(K.p_max)[c] = (uint8_t)vmax;
         if (esc) {   // rare: the full numbers go on a list the receiver patches in (overflow is reported by the host)
-            const uint32_t at = atomicAdd(P.esc_hdr, 1u);
+            const uint32_t at = atomicAdd(P.esc_count, 1u);
             if (at < P.esc_cap) P.esc[at] = make_uint4(K.cell_begin + c, (uint32_t)count, (uint32_t)total, (uint32_t)(total >> 32));
         }
     } else if (K.p_count) {
@@ -543,6 +544,8 @@ __device__ __forceinline__ void finalize_big_part(const FinParams& P, uint32_t c
 // Both rare lists in one launch (each is almost always empty; two launches cost 6 % of a step).
 __global__ void __launch_bounds__(WideLayout::NT) k_finalize_rare(const __grid_constant__ FinParams P) {
     cudaGridDependencySynchronize();                 // a programmatic dependent of k_finalize_cells / k_finalize_slide
+    if (P.esc_hdr && blockIdx.x == 0 && threadIdx.x < 4)   // every store_basics has run: publish the escape list's length
+        P.esc_hdr[threadIdx.x] = threadIdx.x == 0 ? *P.esc_count : 0u;
     if (blockIdx.x < P.rare_wide_ctas) finalize_wide_part(P, blockIdx.x, P.rare_wide_ctas);
     else finalize_big_part(P, blockIdx.x - P.rare_wide_ctas, gridDim.x - P.rare_wide_ctas);
 }

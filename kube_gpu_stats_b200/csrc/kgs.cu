@@ -136,6 +136,8 @@ struct kgs_ctx {
     PeerFlags px_flags{};
     size_t px_slot = 0;
     uint32_t px_seq = 0;
+    bool px_defer = true;                      // queue a push's copies behind the NEXT job's accumulate kernel (see kgs_exchange_push)
+    struct { bool on = false; char* src = nullptr; size_t nbytes = 0; int half = 0, region_half = 0; uint32_t seq = 0; } px_pending;
     uint32_t* px_timeout = nullptr;            // device word raised by k_peer_barrier when a peer never arrived
     void* nccl_comm = nullptr;                 // own communicator (kgs_nccl_init)
     // measurement
@@ -379,6 +381,38 @@ struct TextStager {
     }
 };
 
+// Queue the copies and the barrier of the pending push on the exchange stream, behind whatever the compute stream
+// holds at this moment.
+int flush_pending_push(kgs_handle h) {
+    if (!h->px_pending.on) return KGS_OK;
+    h->px_pending.on = false;
+    const int n = h->px_n, me = h->px_me, half = h->px_pending.half;
+    const uint32_t seq = h->px_pending.seq;
+    char* src = h->px_pending.src;
+    const size_t nbytes = h->px_pending.nbytes;
+    KGS_CUDA(h, cudaEventRecord(h->fin_done, h->compute));
+    KGS_CUDA(h, cudaStreamWaitEvent(h->xchg, h->fin_done, 0));
+    static const int dbg = getenv("KGS_XCHG_DEBUG") ? atoi(getenv("KGS_XCHG_DEBUG")) : 0;   // experiments only: 1 no self copy, 2 no barrier, 4 no peer copies
+    if (h->px_multicast) {   // ONE copy: the NVSwitch replicates the writes into every rank's buffer (this one included)
+        char* dst = h->px_multicast + ((size_t)half * n + me) * h->px_slot;
+        KGS_CUDA(h, cudaMemcpyAsync(dst, src, nbytes, cudaMemcpyDeviceToDevice, h->xchg));
+    }
+    for (int k = 0; k < n && !h->px_multicast; ++k) {   // the neighbour first: spreads the links
+        const int r = (me + 1 + k) % n;
+        if ((r == me && ((dbg & 1) || !h->px_self_copy)) || (r != me && (dbg & 4))) continue;
+        char* dst = h->px_gathered[r] + ((size_t)half * n + me) * h->px_slot;
+        KGS_CUDA(h, cudaMemcpyAsync(dst, src, nbytes, cudaMemcpyDeviceToDevice, h->xchg));
+    }
+    if (!(dbg & 2))
+        launch(h, KGS_K_EXCHANGE, h->xchg, [&] {
+            k_peer_barrier<<<1, 32, 0, h->xchg>>>(h->px_flags, n, me, half, seq, 10ull * 1000 * 1000 * 1000, h->px_timeout);
+        });
+    KGS_CUDA(h, cudaGetLastError());
+    KGS_CUDA(h, cudaEventRecord(h->region_free[h->px_pending.region_half], h->xchg));
+    h->region_busy[h->px_pending.region_half] = true;
+    return KGS_OK;
+}
+
 int grid_for(uint64_t work_items, int per_block, int max_blocks) {
     uint64_t b = (work_items + per_block - 1) / per_block;
     if (b < 1) b = 1;
@@ -441,6 +475,7 @@ int kgs_create(int device, kgs_handle* out) {
     if (const char* e = getenv("KGS_FINALIZE_GROUPS")) h->groups_path = atoi(e) != 0;
     if (const char* e = getenv("KGS_AUTO_REORDER")) h->auto_reorder = atoi(e) != 0;
     if (const char* e = getenv("KGS_PDL")) h->pdl = atoi(e) != 0;
+    if (const char* e = getenv("KGS_PUSH_DEFER")) h->px_defer = atoi(e) != 0;
     if (const char* e = getenv("KGS_STAGE_THREADS")) { const int v = atoi(e); if (v >= 0 && v <= 64) h->mx_stage_threads = v; }
     if (const char* e = getenv("KGS_THREAD_CELL_MAX")) { const int v = atoi(e); if (v >= 1 && v <= 65535) h->thread_cell_max = (uint32_t)v; }
     if (h->accum_tma) {
@@ -459,6 +494,7 @@ int kgs_create(int device, kgs_handle* out) {
 int kgs_destroy(kgs_handle h) {
     if (!h) return KGS_OK;
     cudaSetDevice(h->device);
+    h->px_pending.on = false;   // a push nobody waited for is dropped with the handle
     cudaStreamSynchronize(h->copy);
     cudaStreamSynchronize(h->compute);
     if (h->xchg) cudaStreamSynchronize(h->xchg);
@@ -502,6 +538,8 @@ int kgs_destroy(kgs_handle h) {
 int kgs_sync(kgs_handle h) {
     if (!h) return KGS_ERR_ARG;
     KGS_CUDA(h, cudaSetDevice(h->device));
+    int rc0 = flush_pending_push(h);
+    if (rc0) return rc0;
     KGS_CUDA(h, cudaStreamSynchronize(h->copy));
     KGS_CUDA(h, cudaStreamSynchronize(h->compute));
     KGS_CUDA(h, cudaStreamSynchronize(h->xchg));
@@ -924,11 +962,7 @@ int kgs_stats_begin(kgs_handle h, const kgs_window_spec* sp) {
     off += result_area;
     const int half = (int)(h->job_seq++ & 1);
     const size_t slot_shift = half ? result_area : 0;
-    h->region_half = half;
-    if (h->region_busy[half]) {   // the exchange of the job two back read this half: its kernels come first
-        KGS_CUDA(h, cudaStreamWaitEvent(h->compute, h->region_free[half], 0));
-        h->region_busy[half] = false;
-    }
+    h->region_half = half;   // (kgs_stats_finalize waits for the exchange of the job two back, which read this half)
     // the rare list has one entry per window cell (a cell is listed at most once), so it cannot overflow
     if (window_cells >= (1ull << 32)) return fail(h, KGS_ERR_ARG, "too many window cells");
     const uint64_t rare_cap = pct ? window_cells : 0;
@@ -1003,7 +1037,6 @@ int kgs_stats_begin(kgs_handle h, const kgs_window_spec* sp) {
         h->desc_cap = 0;
     }
     KGS_CUDA(h, cudaMemsetAsync(h->arena.p, 0, clear_bytes, h->compute));
-    if (h->packed_compact) KGS_CUDA(h, cudaMemsetAsync(h->esc_hdr, 0, 16, h->compute));   // escape list of this job's region: empty
     h->spec = *sp;
     h->W = W;
     h->n_panes = (uint32_t)n_panes;
@@ -1119,6 +1152,10 @@ int kgs_stats_accumulate(kgs_handle h) {
     if (pct) h->vals_used = align_up(h->vals_used + B.n, 16);
     h->accumulated += B.n;
     h->last_was_accum = true;
+    {   // the previous job's tables start travelling now, behind this kernel (kgs_exchange_push)
+        int rc3 = flush_pending_push(h);
+        if (rc3) return rc3;
+    }
     return KGS_OK;
 }
 
@@ -1175,10 +1212,19 @@ int kgs_stats_finalize(kgs_handle h) {
                                                  std::to_string(h->accumulated) + " samples: give a larger hint");
     }
     cudaStream_t st = h->compute;
-    if (h->packed_compact && h->job_final) KGS_CUDA(h, cudaMemsetAsync(h->esc_hdr, 0, 16, st));   // finalized again: the escape list starts empty
+    P.esc_count = h->ctl + 5;
     // A job may be finalized more than once (more batches in between): the lists of cells left to
     // k_finalize_rare start empty each time.
-    if (sp.n_q && h->job_final) KGS_CUDA(h, cudaMemsetAsync(h->ctl + 2, 0, 8, st));
+    if (h->job_final) KGS_CUDA(h, cudaMemsetAsync(h->ctl + 2, 0, 16, st));   // ctl[2..5]: rare-list lengths, spare, escape count
+    // This job's result region was last read by the exchange of the job two back: that comes first.  (Nothing before
+    // the finalize kernels writes the region, so the wait sits here and not at begin: the exchange of job i may run
+    // beside the accumulate kernel of job i+2.)
+    int rc_push = flush_pending_push(h);
+    if (rc_push) return rc_push;
+    if (h->region_busy[h->region_half]) {
+        KGS_CUDA(h, cudaStreamWaitEvent(h->compute, h->region_free[h->region_half], 0));
+        h->region_busy[h->region_half] = false;
+    }
     // PDL only where the predecessor on the stream is the library's own kernel and no per-kernel events sit in between
     const bool pdl = h->pdl && !h->prof && h->last_was_accum && !h->job_final;
     h->last_was_accum = false;
@@ -1248,6 +1294,8 @@ int kgs_stats_finalize(kgs_handle h) {
         }
     }
     KGS_CUDA(h, cudaGetLastError());
+    if (h->packed_compact && !(cells && sp.n_q && sp.metric != KGS_METRIC_FB))   // k_finalize_rare was not there to do it
+        KGS_CUDA(h, cudaMemcpyAsync(h->esc_hdr, h->ctl + 5, 4, cudaMemcpyDeviceToDevice, st));
     h->job_final = true;
     return KGS_OK;
 }
@@ -1260,13 +1308,11 @@ int kgs_window_stats(kgs_handle h, const kgs_window_spec* spec) {
 }
 
 static int check_job_flags(kgs_handle h) {
-    uint32_t ctl[4] = {0, 0, 0, 0};
+    uint32_t ctl[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     KGS_CUDA(h, cudaMemcpyAsync(ctl, h->ctl, sizeof(ctl), cudaMemcpyDeviceToHost, h->compute));
     KGS_CUDA(h, cudaStreamSynchronize(h->compute));
     if (h->packed_compact && h->job_final) {
-        uint32_t n_esc = 0;
-        KGS_CUDA(h, cudaMemcpyAsync(&n_esc, h->esc_hdr, 4, cudaMemcpyDeviceToHost, h->compute));
-        KGS_CUDA(h, cudaStreamSynchronize(h->compute));
+        const uint32_t n_esc = ctl[5];
         if (n_esc > h->esc_cap)
             return fail(h, KGS_ERR_CAPACITY, "compact exchange tables: " + std::to_string(n_esc) + " cells above 65 534 samples, the escape list holds " +
                                                  std::to_string(h->esc_cap) + " (use kgs_set_packed_exchange(h, 1) for windows this long)");
@@ -1421,6 +1467,7 @@ int kgs_exchange_setup(kgs_handle h, int n_ranks, int my_rank, void* const* gath
         return fail(h, KGS_ERR_ARG, "kgs_exchange_setup: 1 <= n_ranks <= 16 and 0 <= my_rank < n_ranks");
     if (slot_bytes == 0 || (slot_bytes & 15)) return fail(h, KGS_ERR_ARG, "kgs_exchange_setup: slot_bytes must be a positive multiple of 16");
     KGS_CUDA(h, cudaSetDevice(h->device));
+    h->px_pending.on = false;
     KGS_CUDA(h, cudaStreamSynchronize(h->xchg));
     for (int r = 0; r < n_ranks; ++r) {
         if (!gathered[r] || !flags[r]) return fail(h, KGS_ERR_ARG, "kgs_exchange_setup: null buffer");
@@ -1461,29 +1508,21 @@ int kgs_exchange_push(kgs_handle h, void** d_gathered, size_t* bytes_per_rank) {
         return fail(h, KGS_ERR_CAPACITY, "kgs_exchange_push: the job's tables (" + std::to_string(nbytes) + " bytes) exceed slot_bytes (" +
                                              std::to_string(h->px_slot) + ")");
     KGS_CUDA(h, cudaSetDevice(h->device));
+    if ((rc = flush_pending_push(h))) return rc;   // an earlier push nobody has started yet
     const int n = h->px_n, me = h->px_me;
     const uint32_t seq = ++h->px_seq;
     const int half = (int)(seq & 1u);
-    KGS_CUDA(h, cudaEventRecord(h->fin_done, h->compute));
-    KGS_CUDA(h, cudaStreamWaitEvent(h->xchg, h->fin_done, 0));
-    static const int dbg = getenv("KGS_XCHG_DEBUG") ? atoi(getenv("KGS_XCHG_DEBUG")) : 0;   // experiments only: 1 no self copy, 2 no barrier, 4 no peer copies
-    if (h->px_multicast) {   // ONE copy: the NVSwitch replicates the writes into every rank's buffer (this one included)
-        char* dst = h->px_multicast + ((size_t)half * n + me) * h->px_slot;
-        KGS_CUDA(h, cudaMemcpyAsync(dst, src, nbytes, cudaMemcpyDeviceToDevice, h->xchg));
-    }
-    for (int k = 0; k < n && !h->px_multicast; ++k) {   // the neighbour first: spreads the links
-        const int r = (me + 1 + k) % n;
-        if ((r == me && ((dbg & 1) || !h->px_self_copy)) || (r != me && (dbg & 4))) continue;
-        char* dst = h->px_gathered[r] + ((size_t)half * n + me) * h->px_slot;
-        KGS_CUDA(h, cudaMemcpyAsync(dst, src, nbytes, cudaMemcpyDeviceToDevice, h->xchg));
-    }
-    if (!(dbg & 2))
-        launch(h, KGS_K_EXCHANGE, h->xchg, [&] {
-            k_peer_barrier<<<1, 32, 0, h->xchg>>>(h->px_flags, n, me, half, seq, 10ull * 1000 * 1000 * 1000, h->px_timeout);
-        });
-    KGS_CUDA(h, cudaGetLastError());
-    KGS_CUDA(h, cudaEventRecord(h->region_free[h->region_half], h->xchg));
-    h->region_busy[h->region_half] = true;
+    h->px_pending.on = true;
+    h->px_pending.src = src;
+    h->px_pending.nbytes = nbytes;
+    h->px_pending.half = half;
+    h->px_pending.seq = seq;
+    h->px_pending.region_half = h->region_half;
+    // The copies read this job's tables from HBM and write the peers' tables into it - beside the next job's
+    // accumulate kernel, which is the one kernel of a step that is bound by HBM, that costs the most.  So they are
+    // queued when that kernel has been launched (kgs_stats_accumulate) and run beside the finalize kernels, which
+    // are bound by instruction issue; join / sync / the next push start them at once if no job follows.
+    if (!h->px_defer && (rc = flush_pending_push(h))) return rc;
     if (d_gathered) *d_gathered = h->px_gathered[me] + (size_t)half * n * h->px_slot;
     if (bytes_per_rank) *bytes_per_rank = nbytes;
     return KGS_OK;
@@ -1492,6 +1531,8 @@ int kgs_exchange_push(kgs_handle h, void** d_gathered, size_t* bytes_per_rank) {
 int kgs_exchange_join(kgs_handle h) {
     if (!h) return KGS_ERR_ARG;
     KGS_CUDA(h, cudaSetDevice(h->device));
+    int rc0 = flush_pending_push(h);
+    if (rc0) return rc0;
     for (int b = 0; b < 2; ++b)
         if (h->region_busy[b]) KGS_CUDA(h, cudaStreamWaitEvent(h->compute, h->region_free[b], 0));
     return KGS_OK;
@@ -1500,6 +1541,8 @@ int kgs_exchange_join(kgs_handle h) {
 int kgs_exchange_sync(kgs_handle h) {
     if (!h) return KGS_ERR_ARG;
     KGS_CUDA(h, cudaSetDevice(h->device));
+    int rc0 = flush_pending_push(h);
+    if (rc0) return rc0;
     KGS_CUDA(h, cudaStreamSynchronize(h->xchg));
     uint32_t flag = 0;
     KGS_CUDA(h, cudaMemcpy(&flag, h->px_timeout, 4, cudaMemcpyDeviceToHost));
