@@ -8,7 +8,7 @@ import os
 import re
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, 'libkgs.so')
+LIB_PATH = os.environ.get('KGS_LIB_PATH') or os.path.join(HERE, 'libkgs.so')   # KGS_LIB_PATH: experiments with another build
 HEADER_PATH = os.path.join(HERE, '..', 'include', 'kgs.h')
 
 KGS_OK, KGS_ERR_ARG, KGS_ERR_CUDA, KGS_ERR_STATE, KGS_ERR_CAPACITY, KGS_ERR_NOMEM, KGS_ERR_PARSE = range(7)

@@ -329,12 +329,11 @@ KGS_HD inline bool parse_float(const char* s, uint32_t len, double* out) {
         unsigned long long w = 0;
         uint32_t nd = 0;
         long long e10 = 0;
-        bool trunc = false, seen = false, point = false, prev_digit = false;
+        bool trunc = false, seen = false, point = false;
         for (; i < end; ++i) {
             const char c = s[i];
             if (is_digit(c)) {
                 seen = true;
-                prev_digit = true;
                 const uint32_t dg = (uint32_t)(c - '0');
                 if (nd == 0 && dg == 0) {
                     if (point) --e10;
@@ -348,7 +347,6 @@ KGS_HD inline bool parse_float(const char* s, uint32_t len, double* out) {
                 }
             } else if (c == '.' && !point) {
                 point = true;
-                prev_digit = false;
             } else {
                 break;
             }
@@ -364,12 +362,10 @@ KGS_HD inline bool parse_float(const char* s, uint32_t len, double* out) {
                 ++i;
             }
             bool eseen = false;
-            prev_digit = false;
             for (; i < end; ++i) {
                 const char c = s[i];
                 if (is_digit(c)) {
                     eseen = true;
-                    prev_digit = true;
                     if (e < 100000000) e = e * 10 + (c - '0');
                 } else {
                     break;
