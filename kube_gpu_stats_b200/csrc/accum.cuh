@@ -68,6 +68,7 @@ struct AccumParams {
     uint32_t* ctl;                 // ctl[0] pool cursor, ctl[1] overflow flag, ctl[4] CTAs that used the accumulator cache
     uint32_t agg_on;               // every cell index < 2^30: the per-CTA accumulator cache may be used
     uint32_t dense_ok;             // step >= 8 and no sampled windows: the dense-tile shortcut applies
+    uint32_t dense16_ok;           // step >= 16, an 8-bit metric: two tiles at once, 16 consecutive samples per lane
 };
 
 __device__ __forceinline__ uint64_t policy_evict_last() {
@@ -219,6 +220,159 @@ __device__ __forceinline__ void load_oct(const AccumParams& P, uint32_t i0, bool
     }
 }
 
+// What the chain machinery needs to know about one lane's consecutive samples.
+struct LaneRuns {
+    uint32_t g0, p0, pane0;        // key of the lane's first sample
+    uint32_t g1, p1, pane1;        // key of its last sample
+    uint32_t fc, fs, fm, fstart;   // forward piece (the whole lane when single, else its last piece): count, sum, max, offset
+    uint32_t ac, as, am;           // first piece of a lane with a boundary inside
+    bool single;                   // no boundary inside the lane
+};
+
+// Chains: a chain starts at a lane's LAST piece, runs over the following single-piece lanes with the same key and
+// absorbs the first piece of the lane that ends it.  One segmented shuffle reduction sums every chain of the tile;
+// chains (and stand-alone first pieces) become records of the warp's queue, a record that continues the queued tail
+// is merged into it.  LS = samples per lane (8: the general tile; 16: two tiles at once, dense input only).
+template <int LS>
+__device__ __forceinline__ void append_chains(RunQueue& Q, uint32_t& queued, const LaneRuns& L, uint32_t start0, uint32_t lane) {
+    constexpr uint32_t kAll = 0xFFFFFFFFu;
+    const bool single = L.single;
+    // does my first piece continue the previous lane's last piece?
+    const uint32_t pg = __shfl_up_sync(kAll, L.g1, 1);
+    const uint32_t pp = __shfl_up_sync(kAll, L.p1, 1);
+    const uint32_t ppn = __shfl_up_sync(kAll, L.pane1, 1);
+    const bool cont = lane > 0 && pg == L.g0 && pp == L.p0 && ppn == L.pane0;
+    // a chain starts at every lane with a boundary inside (its last piece) and at every single
+    // lane that does not continue its predecessor
+    const bool head = !single || !cont;
+    const uint32_t heads = __ballot_sync(kAll, head);
+    const uint32_t rest = (lane == 31) ? 0u : (heads & (0xFFFFFFFEu << lane));
+    const uint32_t seg_end = rest ? (uint32_t)(__ffs(rest) - 2) : 31u;
+    uint32_t fs = L.fs, fm = L.fm;
+    // chain totals: sum and max by a segmented shuffle reduction, count is implied
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t s2 = __shfl_down_sync(kAll, fs, d);
+        const uint32_t m2 = __shfl_down_sync(kAll, fm, d);
+        if (lane + d <= seg_end) {
+            fs += s2;
+            fm = max(fm, m2);
+        }
+    }
+    uint32_t cc = L.fc + (uint32_t)LS * (seg_end - lane);
+    {   // absorb the first piece of the split lane that ends the chain, if it has the chain's key
+        const uint32_t j = min(seg_end + 1, 31u);
+        const bool joins = !single && cont;
+        const uint32_t jj = __shfl_sync(kAll, (uint32_t)joins, j);
+        const uint32_t jc = __shfl_sync(kAll, L.ac, j);
+        const uint32_t js = __shfl_sync(kAll, L.as, j);
+        const uint32_t jm = __shfl_sync(kAll, L.am, j);
+        if (seg_end < 31 && jj) {
+            cc += jc;
+            fs += js;
+            fm = max(fm, jm);
+        }
+    }
+    // records this lane appends: its chain (head lanes, valid key) and a stand-alone first piece
+    const bool rec_chain = head && L.pane1 != kInvalid;
+    const bool rec_first = !single && !cont && L.pane0 != kInvalid;
+    // the record that starts exactly at the tile's first sample may continue the queued tail
+    bool merged = false;
+    if (lane == 0 && queued && (single ? rec_chain : rec_first)) {
+        const uint32_t r = queued - 1;
+        const uint32_t mc = single ? cc : L.ac, ms = single ? fs : L.as, mm = single ? fm : L.am;
+        if (Q.gid[r] == L.g0 && Q.pid[r] == L.p0 && Q.pane[r] == L.pane0 && Q.start[r] + Q.cnt[r] == start0 &&
+            Q.cnt[r] + mc <= kMergeMax) {
+            Q.cnt[r] += mc;
+            Q.sum[r] += ms;
+            Q.mx[r] = max(Q.mx[r], mm);
+            merged = true;
+        }
+    }
+    merged = __shfl_sync(kAll, (uint32_t)merged, 0) != 0;
+    const uint32_t m_first = __ballot_sync(kAll, rec_first);
+    const uint32_t m_chain = __ballot_sync(kAll, rec_chain);
+    const uint32_t below = (1u << lane) - 1u;
+    // slot order = sample order: a lane's first piece precedes its chain
+    uint32_t slot = queued + __popc(m_first & below) + __popc(m_chain & below) - ((merged && lane > 0) ? 1u : 0u);
+    if (rec_first) {
+        if (!(lane == 0 && merged)) {
+            Q.gid[slot] = L.g0; Q.pid[slot] = L.p0; Q.pane[slot] = L.pane0;
+            Q.cnt[slot] = L.ac; Q.sum[slot] = L.as; Q.mx[slot] = L.am; Q.start[slot] = start0;
+        }
+        slot += (lane == 0 && merged) ? 0u : 1u;
+    }
+    if (rec_chain && !(lane == 0 && merged && single)) {
+        Q.gid[slot] = L.g1; Q.pid[slot] = L.p1; Q.pane[slot] = L.pane1;
+        Q.cnt[slot] = cc; Q.sum[slot] = fs; Q.mx[slot] = fm; Q.start[slot] = start0 + L.fstart;
+    }
+    queued += __popc(m_first) + __popc(m_chain) - (merged ? 1u : 0u);
+}
+
+// Two tiles at once for dense input: a lane takes SIXTEEN consecutive samples (two 256-bit loads per column).
+// If every lane of the warp holds 16 consecutive seconds of one (gpu, pid) - the normal case in collector order -
+// the lane's values are packed into four words (they go to the value log as they are), its pane boundary, if any,
+// follows from one division, the piece sums come from dp4a on the masked words, and ONE pass of the chain
+// machinery serves 512 samples instead of 256.  Returns false (nothing done) for any other tile pair; the caller
+// then takes the general 8-samples-per-lane path.  Needs step >= 16 (at most one boundary per lane).
+template <bool PCT>
+__device__ __forceinline__ bool dense16_tiles(const AccumParams& P, RunQueue& Q, uint32_t& queued, uint32_t tile, uint32_t lane) {
+    constexpr uint32_t kAll = 0xFFFFFFFFu;
+    const uint32_t i0 = tile * kTileSamples + 16 * lane;
+    uint32_t w[4], t0, g0, p0, acc = 0;
+    {
+        Oct o;
+        load_oct(P, i0, true, o);
+        t0 = o.t[0]; g0 = o.g[0]; p0 = o.p[0];
+#pragma unroll
+        for (int j = 1; j < 8; ++j) acc |= ((o.t[j] - t0) ^ (uint32_t)j) | (o.g[j] ^ g0) | (o.p[j] ^ p0);
+        uint32_t v[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] = (o.u[j] >> P.mshift) & 0xFFu;
+        w[0] = v[0] | (v[1] << 8) | (v[2] << 16) | (v[3] << 24);
+        w[1] = v[4] | (v[5] << 8) | (v[6] << 16) | (v[7] << 24);
+    }
+    {
+        Oct o;
+        load_oct(P, i0 + 8, true, o);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc |= ((o.t[j] - t0) ^ (uint32_t)(8 + j)) | (o.g[j] ^ g0) | (o.p[j] ^ p0);
+        uint32_t v[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] = (o.u[j] >> P.mshift) & 0xFFu;
+        w[2] = v[0] | (v[1] << 8) | (v[2] << 16) | (v[3] << 24);
+        w[3] = v[4] | (v[5] << 8) | (v[6] << 16) | (v[7] << 24);
+    }
+    if (!__all_sync(kAll, acc == 0 && t0 >= P.t0 && t0 < 0xFFFFFF00u)) return false;
+    if (PCT) st_keep_v4(P.vals + P.vals_base + i0, make_uint4(w[0], w[1], w[2], w[3]), policy_evict_last());
+    const uint32_t x0 = t0 - P.t0;
+    const uint32_t pn0 = fdiv(x0, P.dstep);
+    const uint32_t left = P.step - (x0 - pn0 * P.step);          // samples from t0 to the end of pane pn0
+    const uint32_t p_a = pn0 < P.n_panes ? pn0 : kInvalid;
+    const uint32_t p_b = pn0 + 1 < P.n_panes ? pn0 + 1 : kInvalid;
+    const bool split = left < 16 && p_a != p_b;
+    const uint32_t k = split ? left : 0u;                        // first piece = samples [0, k), forward piece = [k, 16)
+    uint32_t tot = 0, as = 0, am = 0, fm = 0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int below = min(max((int)k - 4 * i, 0), 4);       // bytes of word i that belong to the first piece
+        const uint32_t m = (uint32_t)(~(0xFFFFFFFFFFFFFFFFull << (8 * below)));
+        const uint32_t aw = w[i] & m, fw = w[i] & ~m;
+        tot = __dp4a(w[i], 0x01010101u, tot);
+        as = __dp4a(aw, 0x01010101u, as);
+        am = max(am, max(max(aw & 0xFFu, (aw >> 8) & 0xFFu), max((aw >> 16) & 0xFFu, aw >> 24)));
+        fm = max(fm, max(max(fw & 0xFFu, (fw >> 8) & 0xFFu), max((fw >> 16) & 0xFFu, fw >> 24)));
+    }
+    LaneRuns L;
+    L.single = !split;
+    L.g0 = g0; L.p0 = p0; L.pane0 = p_a;
+    L.g1 = g0; L.p1 = p0; L.pane1 = (left < 16) ? p_b : p_a;
+    L.fc = 16 - k; L.fs = tot - as; L.fm = fm; L.fstart = k;
+    L.ac = k; L.as = as; L.am = am;
+    append_chains<16>(Q, queued, L, (uint32_t)P.vals_base + i0, lane);
+    return true;
+}
+
 // ---- TMA staging (TMA = true) ----------------------------------------------------------------------
 // Each warp owns a ring of kStages tile buffers in shared memory (4 columns x 1 KB) and one mbarrier
 // per buffer.  Lane 0 arms the barrier with the 4 KB it expects and issues four 1-D bulk copies
@@ -258,7 +412,7 @@ __device__ __forceinline__ uint4 lds_v4(uint32_t a) {
 }
 
 template <bool PCT, bool TMA>
-__global__ void __launch_bounds__(kAccumWarps * 32) k_accum(const __grid_constant__ AccumParams P) {
+__global__ void __launch_bounds__(kAccumWarps * 32, 4) k_accum(const __grid_constant__ AccumParams P) {
     extern __shared__ __align__(128) unsigned char tma_smem[];   // TMA only: [warp][stage] tile buffers, then barriers
     cudaTriggerProgrammaticLaunchCompletion();   // the finalize kernel behind this one may be scheduled while the last CTAs drain
     __shared__ RunQueue queues[kAccumWarps];
@@ -312,7 +466,35 @@ __global__ void __launch_bounds__(kAccumWarps * 32) k_accum(const __grid_constan
                 if (tile_begin + st < tile_end && tile_begin + st < full_tiles) tma_issue(st, tile_begin + st);
         }
     }
+    uint32_t skip16 = 0, penalty16 = 8;   // after a pair of tiles that was not dense: no further attempt for a while
+    auto drain = [&]() {   // retire all but the newest record (it may still grow)
+        __syncwarp();
+        if (queued > 32) {
+            flush_queue<PCT>(P, agg, lc, Q, queued - 1, nk);
+            __syncwarp();
+            if (lane == 0) {
+                const uint32_t r = queued - 1;
+                Q.gid[0] = Q.gid[r]; Q.pid[0] = Q.pid[r]; Q.pane[0] = Q.pane[r];
+                Q.cnt[0] = Q.cnt[r]; Q.sum[0] = Q.sum[r]; Q.mx[0] = Q.mx[r]; Q.start[0] = Q.start[r];
+            }
+            queued = 1;
+            __syncwarp();
+        }
+    };
     for (uint32_t tile = tile_begin; tile < tile_end; ++tile) {
+        if (!TMA && P.dense16_ok && tile + 1 < tile_end && tile + 1 < full_tiles) {   // warp-uniform
+            if (skip16) {
+                --skip16;
+            } else if (dense16_tiles<PCT>(P, Q, queued, tile, lane)) {
+                penalty16 = 8;
+                drain();
+                ++tile;
+                continue;
+            } else {
+                skip16 = penalty16;
+                penalty16 = min(penalty16 * 2, 1024u);
+            }
+        }
         const uint32_t i0 = tile * kTileSamples + 8 * lane;
         const bool full = tile < full_tiles;
         if (TMA && full) {
@@ -396,96 +578,29 @@ __global__ void __launch_bounds__(kAccumWarps * 32) k_accum(const __grid_constan
                     if (i0 + j < P.n) dst[j] = (uint8_t)v[j];
             }
         }
-        const bool single = bm == 0;
-        // does my first piece continue the previous lane's last piece?
-        const uint32_t pg = __shfl_up_sync(kAll, cur.g[7], 1);
-        const uint32_t pp = __shfl_up_sync(kAll, cur.p[7], 1);
-        const uint32_t ppn = __shfl_up_sync(kAll, pane[7], 1);
-        const bool cont = lane > 0 && pg == cur.g[0] && pp == cur.p[0] && ppn == pane[0];
-        // a chain starts at every lane with a boundary inside (its last piece) and at every single
-        // lane that does not continue its predecessor
-        const bool head = !single || !cont;
-        const uint32_t heads = __ballot_sync(kAll, head);
-        const uint32_t rest = (lane == 31) ? 0u : (heads & (0xFFFFFFFEu << lane));
-        const uint32_t seg_end = rest ? (uint32_t)(__ffs(rest) - 2) : 31u;
-        // forward piece of this lane (whole lane when single) and, for split lanes, the first piece
-        uint32_t fc = 8, fs, fm, fstart = 0;          // forward: count, sum, max, offset of its first sample
-        uint32_t ac = 0, as = 0, am = 0;              // first piece of a split lane
-        if (single) {
-            fs = ((v[0] + v[1]) + (v[2] + v[3])) + ((v[4] + v[5]) + (v[6] + v[7]));
-            fm = max(max(max(v[0], v[1]), max(v[2], v[3])), max(max(v[4], v[5]), max(v[6], v[7])));
+        LaneRuns L;
+        L.single = bm == 0;
+        L.g0 = cur.g[0]; L.p0 = cur.p[0]; L.pane0 = pane[0];
+        L.g1 = cur.g[7]; L.p1 = cur.p[7]; L.pane1 = pane[7];
+        L.fc = 8; L.fstart = 0; L.ac = 0; L.as = 0; L.am = 0;
+        if (L.single) {
+            L.fs = ((v[0] + v[1]) + (v[2] + v[3])) + ((v[4] + v[5]) + (v[6] + v[7]));
+            L.fm = max(max(max(v[0], v[1]), max(v[2], v[3])), max(max(v[4], v[5]), max(v[6], v[7])));
         } else {
             const uint32_t first_end = __ffs(bm) - 1;             // first piece = samples [0, first_end)
             const uint32_t last_begin = 31 - __clz(bm);           // last piece  = samples [last_begin, 8)
-            fs = 0; fm = 0;
+            L.fs = 0; L.fm = 0;
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
-                if ((uint32_t)j < first_end) { as += v[j]; am = max(am, v[j]); }
-                if ((uint32_t)j >= last_begin) { fs += v[j]; fm = max(fm, v[j]); }
+                if ((uint32_t)j < first_end) { L.as += v[j]; L.am = max(L.am, v[j]); }
+                if ((uint32_t)j >= last_begin) { L.fs += v[j]; L.fm = max(L.fm, v[j]); }
             }
-            ac = first_end;
-            fc = 8 - last_begin;
-            fstart = last_begin;
+            L.ac = first_end;
+            L.fc = 8 - last_begin;
+            L.fstart = last_begin;
         }
-        // chain totals: sum and max by a segmented shuffle reduction, count is implied
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            const uint32_t s2 = __shfl_down_sync(kAll, fs, d);
-            const uint32_t m2 = __shfl_down_sync(kAll, fm, d);
-            if (lane + d <= seg_end) {
-                fs += s2;
-                fm = max(fm, m2);
-            }
-        }
-        uint32_t cc = fc + 8 * (seg_end - lane);
-        {   // absorb the first piece of the split lane that ends the chain, if it has the chain's key
-            const uint32_t j = min(seg_end + 1, 31u);
-            const bool joins = !single && cont;
-            const uint32_t jj = __shfl_sync(kAll, (uint32_t)joins, j);
-            const uint32_t jc = __shfl_sync(kAll, ac, j);
-            const uint32_t js = __shfl_sync(kAll, as, j);
-            const uint32_t jm = __shfl_sync(kAll, am, j);
-            if (seg_end < 31 && jj) {
-                cc += jc;
-                fs += js;
-                fm = max(fm, jm);
-            }
-        }
-        // records this lane appends: its chain (head lanes, valid key) and a stand-alone first piece
-        const bool rec_chain = head && pane[7] != kInvalid;
-        const bool rec_first = !single && !cont && pane[0] != kInvalid;
         const uint32_t start0 = (uint32_t)P.vals_base + i0;
-        // the record that starts exactly at the tile's first sample may continue the queued tail
-        bool merged = false;
-        if (lane == 0 && queued && (single ? rec_chain : rec_first)) {
-            const uint32_t r = queued - 1;
-            const uint32_t mc = single ? cc : ac, ms = single ? fs : as, mm = single ? fm : am;
-            if (Q.gid[r] == cur.g[0] && Q.pid[r] == cur.p[0] && Q.pane[r] == pane[0] && Q.start[r] + Q.cnt[r] == start0 &&
-                Q.cnt[r] + mc <= kMergeMax) {
-                Q.cnt[r] += mc;
-                Q.sum[r] += ms;
-                Q.mx[r] = max(Q.mx[r], mm);
-                merged = true;
-            }
-        }
-        merged = __shfl_sync(kAll, (uint32_t)merged, 0) != 0;
-        const uint32_t m_first = __ballot_sync(kAll, rec_first);
-        const uint32_t m_chain = __ballot_sync(kAll, rec_chain);
-        const uint32_t below = (1u << lane) - 1u;
-        // slot order = sample order: a lane's first piece precedes its chain
-        uint32_t slot = queued + __popc(m_first & below) + __popc(m_chain & below) - ((merged && lane > 0) ? 1u : 0u);
-        if (rec_first) {
-            if (!(lane == 0 && merged)) {
-                Q.gid[slot] = cur.g[0]; Q.pid[slot] = cur.p[0]; Q.pane[slot] = pane[0];
-                Q.cnt[slot] = ac; Q.sum[slot] = as; Q.mx[slot] = am; Q.start[slot] = start0;
-            }
-            slot += (lane == 0 && merged) ? 0u : 1u;
-        }
-        if (rec_chain && !(lane == 0 && merged && single)) {
-            Q.gid[slot] = cur.g[7]; Q.pid[slot] = cur.p[7]; Q.pane[slot] = pane[7];
-            Q.cnt[slot] = cc; Q.sum[slot] = fs; Q.mx[slot] = fm; Q.start[slot] = start0 + fstart;
-        }
-        queued += __popc(m_first) + __popc(m_chain) - (merged ? 1u : 0u);
+        append_chains<kLaneSamples>(Q, queued, L, start0, lane);
         // lanes with two or more boundaries: the pieces between the first and the last are retired
         // directly (rare in collector order; every lane in shuffled input, then 32 wide)
         const bool many = (bm & (bm - 1)) != 0;
@@ -539,18 +654,7 @@ __global__ void __launch_bounds__(kAccumWarps * 32) k_accum(const __grid_constan
                 }
             }
         }
-        __syncwarp();
-        if (queued > 32) {   // retire all but the newest record (it may still grow)
-            flush_queue<PCT>(P, agg, lc, Q, queued - 1, nk);
-            __syncwarp();
-            if (lane == 0) {
-                const uint32_t r = queued - 1;
-                Q.gid[0] = Q.gid[r]; Q.pid[0] = Q.pid[r]; Q.pane[0] = Q.pane[r];
-                Q.cnt[0] = Q.cnt[r]; Q.sum[0] = Q.sum[r]; Q.mx[0] = Q.mx[r]; Q.start[0] = Q.start[r];
-            }
-            queued = 1;
-            __syncwarp();
-        }
+        drain();
         if (TMA && full) {   // this tile's samples have all been consumed: refill its buffer with the tile kStages ahead
             const uint32_t next = tile + kStages;
             __syncwarp();

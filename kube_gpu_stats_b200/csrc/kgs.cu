@@ -121,6 +121,7 @@ struct kgs_ctx {
     uint32_t slide_chunk = 8;      // measured best on B200 (4: 3.0 ms, 8: 1.9, 16: 2.1, 64: 5.0 for the cfg5-shaped test)
     int accum_waves = 2;           // CTAs per resident slot: > 1 keeps the tail short when another kernel (a collective) shares the SMs
     bool dense_path = true;
+    bool dense16_path = true;      // k_accum: two tiles at once (16 samples per lane) where the input is dense
     bool accum_tma = false;        // stage tiles through shared memory with cp.async.bulk + mbarrier
     int accum_ctas_per_sm = 4;     // resident CTAs of 8 warps per SM at 64 registers
     // table exchange (exchange.cuh)
@@ -470,6 +471,7 @@ int kgs_create(int device, kgs_handle* out) {
     if (const char* e = getenv("KGS_SLIDE_CHUNK")) { const int v = atoi(e); if (v >= 1 && v <= 4096) h->slide_chunk = (uint32_t)v; }
     if (const char* e = getenv("KGS_ACCUM_WAVES")) { const int v = atoi(e); if (v >= 1 && v <= 16) h->accum_waves = v; }
     if (const char* e = getenv("KGS_DENSE")) h->dense_path = atoi(e) != 0;
+    if (const char* e = getenv("KGS_DENSE16")) h->dense16_path = atoi(e) != 0;
     if (const char* e = getenv("KGS_PARSE_PIECE_KB")) { const int v = atoi(e); if (v >= 16 && v <= (1 << 21)) h->mx_piece_bytes = (uint32_t)v << 10; }
     if (const char* e = getenv("KGS_ACCUM_TMA")) h->accum_tma = atoi(e) != 0;
     if (const char* e = getenv("KGS_FINALIZE_GROUPS")) h->groups_path = atoi(e) != 0;
@@ -1104,6 +1106,7 @@ int kgs_stats_accumulate(kgs_handle h) {
     P.ctl = h->ctl;
     P.agg_on = 1;
     P.dense_ok = (sp.step >= 8 && sp.width >= sp.step && h->dense_path) ? 1u : 0u;
+    P.dense16_ok = (P.dense_ok && sp.step >= 16 && sp.metric != KGS_METRIC_FB && h->dense16_path) ? 1u : 0u;
     for (int k = 0; k < 3; ++k)
         if ((uint64_t)h->kind[k].n_keys * h->n_panes >= (1ull << 30)) P.agg_on = 0;
     cudaStream_t st = h->compute;
