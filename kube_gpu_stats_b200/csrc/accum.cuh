@@ -309,42 +309,69 @@ __device__ __forceinline__ void append_chains(RunQueue& Q, uint32_t& queued, con
     queued += __popc(m_first) + __popc(m_chain) - (merged ? 1u : 0u);
 }
 
-// Two tiles at once for dense input: a lane takes SIXTEEN consecutive samples (two 256-bit loads per column).
-// If every lane of the warp holds 16 consecutive seconds of one (gpu, pid) - the normal case in collector order -
-// the lane's values are packed into four words (they go to the value log as they are), its pane boundary, if any,
-// follows from one division, the piece sums come from dp4a on the masked words, and ONE pass of the chain
-// machinery serves 512 samples instead of 256.  Returns false (nothing done) for any other tile pair; the caller
-// then takes the general 8-samples-per-lane path.  Needs step >= 16 (at most one boundary per lane).
+// Two tiles at once for dense input.  Each tile is loaded the usual way (a lane reads 8 consecutive samples per
+// column with one 256-bit load, a warp instruction covers 1 KB without gaps) and reduced to a lane summary: the
+// 8 values packed into two words (they go to the value log as they are), the first sample's key and time, and
+// whether the lane is 8 consecutive seconds of one (gpu, pid).  If that holds for all lanes of both tiles and every
+// odd lane continues its even neighbour, the summaries of lanes (2l, 2l+1) are brought together by shuffles: lane l
+// then stands for SIXTEEN consecutive samples, its pane boundary, if any, follows from one division, the piece sums
+// come from dp4a on the masked words, and ONE pass of the chain machinery serves 512 samples instead of 256.
+// Returns false (nothing done, nothing written) for any other pair of tiles; the caller then takes the general
+// 8-samples-per-lane path for them.  Needs step >= 16 (at most one boundary in 16 seconds).
+struct LaneSummary {
+    uint32_t w0, w1, t0, g0, p0;
+    bool ok;                     // dense lane, and (odd lanes) the continuation of the lane before
+};
+
+__device__ __forceinline__ LaneSummary summarize_lane(const AccumParams& P, uint32_t i0, uint32_t lane) {
+    constexpr uint32_t kAll = 0xFFFFFFFFu;
+    Oct o;
+    load_oct(P, i0, true, o);
+    LaneSummary S;
+    S.t0 = o.t[0]; S.g0 = o.g[0]; S.p0 = o.p[0];
+    uint32_t acc = 0;
+#pragma unroll
+    for (int j = 1; j < 8; ++j) acc |= ((o.t[j] - S.t0) ^ (uint32_t)j) | (o.g[j] ^ S.g0) | (o.p[j] ^ S.p0);
+    uint32_t v[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] = (o.u[j] >> P.mshift) & 0xFFu;
+    S.w0 = v[0] | (v[1] << 8) | (v[2] << 16) | (v[3] << 24);
+    S.w1 = v[4] | (v[5] << 8) | (v[6] << 16) | (v[7] << 24);
+    // an odd lane must continue its even neighbour: 8 seconds later, same gpu and process
+    const uint32_t pt = __shfl_up_sync(kAll, S.t0, 1), pg = __shfl_up_sync(kAll, S.g0, 1), pp = __shfl_up_sync(kAll, S.p0, 1);
+    const bool pair = !(lane & 1u) || (S.t0 == pt + 8u && S.g0 == pg && S.p0 == pp);
+    S.ok = acc == 0 && pair && S.t0 >= P.t0 && S.t0 < 0xFFFFFF00u;
+    return S;
+}
+
 template <bool PCT>
 __device__ __forceinline__ bool dense16_tiles(const AccumParams& P, RunQueue& Q, uint32_t& queued, uint32_t tile, uint32_t lane) {
     constexpr uint32_t kAll = 0xFFFFFFFFu;
-    const uint32_t i0 = tile * kTileSamples + 16 * lane;
-    uint32_t w[4], t0, g0, p0, acc = 0;
-    {
-        Oct o;
-        load_oct(P, i0, true, o);
-        t0 = o.t[0]; g0 = o.g[0]; p0 = o.p[0];
-#pragma unroll
-        for (int j = 1; j < 8; ++j) acc |= ((o.t[j] - t0) ^ (uint32_t)j) | (o.g[j] ^ g0) | (o.p[j] ^ p0);
-        uint32_t v[8];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) v[j] = (o.u[j] >> P.mshift) & 0xFFu;
-        w[0] = v[0] | (v[1] << 8) | (v[2] << 16) | (v[3] << 24);
-        w[1] = v[4] | (v[5] << 8) | (v[6] << 16) | (v[7] << 24);
+    const uint32_t base = tile * kTileSamples;
+    const LaneSummary A = summarize_lane(P, base + 8 * lane, lane);
+    if (!__all_sync(kAll, A.ok)) return false;
+    const LaneSummary B = summarize_lane(P, base + kTileSamples + 8 * lane, lane);
+    if (!__all_sync(kAll, B.ok)) return false;
+    if (PCT) {
+        st_keep_v2(P.vals + P.vals_base + base + 8 * lane, A.w0, A.w1, policy_evict_last());
+        st_keep_v2(P.vals + P.vals_base + base + kTileSamples + 8 * lane, B.w0, B.w1, policy_evict_last());
     }
+    // lane l now stands for samples [16 l, 16 l + 16) of the pair: summaries 2l, 2l+1 of tile A (l < 16) or B
+    const uint32_t even = (2u * lane) & 31u, odd = even + 1u;
+    const bool from_a = lane < 16;
+    uint32_t w[4];
     {
-        Oct o;
-        load_oct(P, i0 + 8, true, o);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) acc |= ((o.t[j] - t0) ^ (uint32_t)(8 + j)) | (o.g[j] ^ g0) | (o.p[j] ^ p0);
-        uint32_t v[8];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) v[j] = (o.u[j] >> P.mshift) & 0xFFu;
-        w[2] = v[0] | (v[1] << 8) | (v[2] << 16) | (v[3] << 24);
-        w[3] = v[4] | (v[5] << 8) | (v[6] << 16) | (v[7] << 24);
+        const uint32_t a0 = __shfl_sync(kAll, A.w0, even), b0 = __shfl_sync(kAll, B.w0, even);
+        const uint32_t a1 = __shfl_sync(kAll, A.w1, even), b1 = __shfl_sync(kAll, B.w1, even);
+        const uint32_t a2 = __shfl_sync(kAll, A.w0, odd), b2 = __shfl_sync(kAll, B.w0, odd);
+        const uint32_t a3 = __shfl_sync(kAll, A.w1, odd), b3 = __shfl_sync(kAll, B.w1, odd);
+        w[0] = from_a ? a0 : b0; w[1] = from_a ? a1 : b1; w[2] = from_a ? a2 : b2; w[3] = from_a ? a3 : b3;
     }
-    if (!__all_sync(kAll, acc == 0 && t0 >= P.t0 && t0 < 0xFFFFFF00u)) return false;
-    if (PCT) st_keep_v4(P.vals + P.vals_base + i0, make_uint4(w[0], w[1], w[2], w[3]), policy_evict_last());
+    const uint32_t ta = __shfl_sync(kAll, A.t0, even), tb = __shfl_sync(kAll, B.t0, even);
+    const uint32_t ga = __shfl_sync(kAll, A.g0, even), gb = __shfl_sync(kAll, B.g0, even);
+    const uint32_t pa = __shfl_sync(kAll, A.p0, even), pb = __shfl_sync(kAll, B.p0, even);
+    const uint32_t t0 = from_a ? ta : tb, g0 = from_a ? ga : gb, p0 = from_a ? pa : pb;
+    const uint32_t i0 = base + 16 * lane;
     const uint32_t x0 = t0 - P.t0;
     const uint32_t pn0 = fdiv(x0, P.dstep);
     const uint32_t left = P.step - (x0 - pn0 * P.step);          // samples from t0 to the end of pane pn0
