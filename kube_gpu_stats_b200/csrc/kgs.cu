@@ -121,7 +121,7 @@ struct kgs_ctx {
     uint32_t slide_chunk = 8;      // measured best on B200 (4: 3.0 ms, 8: 1.9, 16: 2.1, 64: 5.0 for the cfg5-shaped test)
     int accum_waves = 2;           // CTAs per resident slot: > 1 keeps the tail short when another kernel (a collective) shares the SMs
     bool dense_path = true;
-    bool dense16_path = true;      // k_accum: two tiles at once (16 samples per lane) where the input is dense
+    bool dense16_path = false;     // k_accum: two tiles at once (16 samples per lane) where the input is dense; measured slower, KGS_DENSE16=1
     bool accum_tma = false;        // stage tiles through shared memory with cp.async.bulk + mbarrier
     int accum_ctas_per_sm = 4;     // resident CTAs of 8 warps per SM at 64 registers
     // table exchange (exchange.cuh)

@@ -267,6 +267,20 @@ def test_tma_staged_accumulate_gives_the_same_tables(built_lib, cfg1, monkeypatc
         check(eng, cfg1, ('pod', 'gpu', 'node'), 'mem', cfg1.t0 + 3, 7, 21, 90, (0.5,))
 
 
+def test_sixteen_samples_per_lane_accumulate_gives_the_same_tables(built_lib, cfg1, monkeypatch):
+    """k_accum's optional two-tiles-at-once path (KGS_DENSE16=1: lane summaries paired by shuffles, one pass of the
+    chain machinery per 512 samples) against the oracle: dense input with tenancy changes, a step that is not a
+    multiple of 16, sliding windows, and input where it never applies."""
+    from kube_gpu_stats_b200.engine import Engine
+    monkeypatch.setenv('KGS_DENSE16', '1')
+    tr = synth.config(2, scale=0.03)
+    with Engine(0) as eng:
+        check(eng, tr, ('pod', 'gpu', 'node'), 'sm', tr.t0, 60, 60, 60, QS)
+        check(eng, tr, ('pod', 'gpu', 'node'), 'mem', tr.t0 + 5, 17, 17, 200, (0.5,), ingest=False)
+        check(eng, tr, ('gpu', 'node'), 'sm', tr.t0, 20, 100, 170, (0.95,), ingest=False)
+        check(eng, cfg1, ('pod', 'gpu', 'node'), 'sm', cfg1.t0, 60, 60, 60, (0.5,))
+
+
 def test_cfg2_full_size_properties_and_exact_slice(engine):
     """BASELINE configs[1] at FULL size (1 000 nodes, 28.8 M samples, 10 000 pods): size-independent
     properties on the whole result and an exact oracle comparison on the first 20 nodes."""
