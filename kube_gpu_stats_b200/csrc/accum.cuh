@@ -401,13 +401,13 @@ __device__ __forceinline__ bool dense16_tiles(const AccumParams& P, RunQueue& Q,
 }
 
 // ---- TMA staging (TMA = true) ----------------------------------------------------------------------
-// Each warp owns a ring of kStages tile buffers in shared memory (4 columns x 1 KB) and one mbarrier
+// Each warp owns kStages tile buffers in shared memory (4 columns x 1 KB) and one mbarrier
 // per buffer.  Lane 0 arms the barrier with the 4 KB it expects and issues four 1-D bulk copies
 // (cp.async.bulk -> UBLKCP): the copy engine moves the next tiles while the warp works on the current
 // one, with no registers held for data in flight and no load instructions to issue.  The warp waits
 // on the barrier's phase bit, reads its 8 samples per column with two LDS.128, and re-arms the
 // buffer with the tile kStages ahead.  Warps never wait for each other.
-constexpr int kStages = 2;
+constexpr int kStages = 1;   // one buffer per warp: it is refilled as soon as the warp has its tile in registers (32 KB per CTA: 4 CTAs per SM)
 constexpr uint32_t kTileBytes = 4 * kTileSamples * 4;   // four u32 columns
 constexpr uint32_t kTmaSmemBytes = kAccumWarps * kStages * (kTileBytes + 8);
 
@@ -440,12 +440,14 @@ __device__ __forceinline__ uint4 lds_v4(uint32_t a) {
 
 template <bool PCT, bool TMA>
 __global__ void __launch_bounds__(kAccumWarps * 32, 4) k_accum(const __grid_constant__ AccumParams P) {
-    extern __shared__ __align__(128) unsigned char tma_smem[];   // TMA only: [warp][stage] tile buffers, then barriers
+    // dynamic shared memory: with TMA the warps' tile buffers and their barriers, else the accumulator cache
+    // (the two are never needed together: the cache is for input far from collector order, the staging for dense input)
+    extern __shared__ __align__(128) unsigned char tma_smem[];
     cudaTriggerProgrammaticLaunchCompletion();   // the finalize kernel behind this one may be scheduled while the last CTAs drain
     __shared__ RunQueue queues[kAccumWarps];
-    __shared__ AggTable table;
+    AggTable& table = *reinterpret_cast<AggTable*>(tma_smem);
     constexpr uint32_t kAll = 0xFFFFFFFFu;
-    if (P.agg_on) {
+    if (!TMA && P.agg_on) {
         for (uint32_t i = threadIdx.x; i < kAggSlots; i += blockDim.x) {
             table.tag[i] = 0; table.cnt[i] = 0; table.mx[i] = 0; table.sum[i] = 0;
         }
@@ -539,6 +541,14 @@ __global__ void __launch_bounds__(kAccumWarps * 32, 4) k_accum(const __grid_cons
             cur.p[0] = a.x; cur.p[1] = a.y; cur.p[2] = a.z; cur.p[3] = a.w; cur.p[4] = b.x; cur.p[5] = b.y; cur.p[6] = b.z; cur.p[7] = b.w;
             a = lds_v4(src + 3 * kTileSamples * 4); b = lds_v4(src + 3 * kTileSamples * 4 + 16);
             cur.u[0] = a.x; cur.u[1] = a.y; cur.u[2] = a.z; cur.u[3] = a.w; cur.u[4] = b.x; cur.u[5] = b.y; cur.u[6] = b.z; cur.u[7] = b.w;
+            // The tile is in registers: refill the buffer with the next tile NOW, so that the copy runs while this
+            // tile is processed.  Every lane's eight shared-memory loads must have returned before the copy engine
+            // may overwrite the buffer: the vote below cannot complete before each lane has used one word of each.
+            const uint32_t touch = cur.t[0] ^ cur.t[4] ^ cur.g[0] ^ cur.g[4] ^ cur.p[0] ^ cur.p[4] ^ cur.u[0] ^ cur.u[4];
+            const uint32_t voted = __ballot_sync(kAll, touch == 0x5A5A5A5Au);   // only its completion matters
+            asm volatile("" ::"r"(voted) : "memory");
+            const uint32_t next = tile + 1;
+            if (lane == 0 && next < tile_end && next < full_tiles) tma_issue(0u, next);
         } else {
             load_oct(P, i0, full, cur);
         }
@@ -634,7 +644,7 @@ __global__ void __launch_bounds__(kAccumWarps * 32, 4) k_accum(const __grid_cons
         uint32_t many_mask = 0;
         if (!dense) {                                  // warp-uniform
             many_mask = __ballot_sync(kAll, many);
-            if (P.agg_on && __popc(many_mask) >= 16) agg = &table;
+            if (!TMA && P.agg_on && __popc(many_mask) >= 16) agg = &table;
         }
         if (many_mask) {
             uint32_t nr = 0;
@@ -682,14 +692,9 @@ __global__ void __launch_bounds__(kAccumWarps * 32, 4) k_accum(const __grid_cons
             }
         }
         drain();
-        if (TMA && full) {   // this tile's samples have all been consumed: refill its buffer with the tile kStages ahead
-            const uint32_t next = tile + kStages;
-            __syncwarp();
-            if (lane == 0 && next < tile_end && next < full_tiles) tma_issue((tile - tile_begin) % kStages, next);
-        }
     }
     flush_queue<PCT>(P, agg, lc, Q, queued, nk);
-    if (P.agg_on) {   // write the CTA's accumulator cache out: one RED per occupied slot and statistic
+    if (!TMA && P.agg_on) {   // write the CTA's accumulator cache out: one RED per occupied slot and statistic
         __syncthreads();
         bool used = false;
         for (uint32_t i = threadIdx.x; i < kAggSlots; i += blockDim.x) {

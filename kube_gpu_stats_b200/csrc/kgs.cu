@@ -480,10 +480,12 @@ int kgs_create(int device, kgs_handle* out) {
     if (const char* e = getenv("KGS_PUSH_DEFER")) h->px_defer = atoi(e) != 0;
     if (const char* e = getenv("KGS_STAGE_THREADS")) { const int v = atoi(e); if (v >= 0 && v <= 64) h->mx_stage_threads = v; }
     if (const char* e = getenv("KGS_THREAD_CELL_MAX")) { const int v = atoi(e); if (v >= 1 && v <= 65535) h->thread_cell_max = (uint32_t)v; }
-    if (h->accum_tma) {
-        h->accum_ctas_per_sm = 2;   // 64 KB of tile buffers + 42 KB static per CTA
-        cudaFuncSetAttribute(k_accum<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTmaSmemBytes);
-        cudaFuncSetAttribute(k_accum<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTmaSmemBytes);
+    {   // dynamic shared memory of k_accum: the warps' tile buffers (TMA) or the accumulator cache, beside 21.5 KB of run queues
+        const int dyn = (int)std::max<size_t>(kTmaSmemBytes, sizeof(AggTable));
+        cudaFuncSetAttribute(k_accum<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn);
+        cudaFuncSetAttribute(k_accum<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn);
+        cudaFuncSetAttribute(k_accum<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn);
+        cudaFuncSetAttribute(k_accum<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn);
     }
     if (const char* e = getenv("KGS_ACCUM_CTAS_PER_SM")) {   // tuning knob for experiments
         const int v = atoi(e);
@@ -1109,6 +1111,9 @@ int kgs_stats_accumulate(kgs_handle h) {
     P.dense16_ok = (P.dense_ok && sp.step >= 16 && sp.metric != KGS_METRIC_FB && h->dense16_path) ? 1u : 0u;
     for (int k = 0; k < 3; ++k)
         if ((uint64_t)h->kind[k].n_keys * h->n_panes >= (1ull << 30)) P.agg_on = 0;
+    // tile staging through shared memory (cp.async.bulk): forced by KGS_ACCUM_TMA=1; it replaces the accumulator cache
+    const bool use_tma = h->accum_tma;
+    if (use_tma) P.agg_on = 0;
     cudaStream_t st = h->compute;
     KGS_CUDA(h, cudaStreamWaitEvent(st, B.ready, 0));
     // every warp owns a contiguous chunk of 256-sample tiles; ctas_per_sm resident CTAs of 8 warps
@@ -1142,12 +1147,12 @@ int kgs_stats_accumulate(kgs_handle h) {
         h->desc_priv_next += (uint32_t)(per_warp * warps);
     }
     launch(h, KGS_K_ACCUM, st, [&] {
-        if (h->accum_tma) {
+        if (use_tma) {
             if (pct) k_accum<true, true><<<grid, 256, kTmaSmemBytes, st>>>(P);
             else k_accum<false, true><<<grid, 256, kTmaSmemBytes, st>>>(P);
         } else {
-            if (pct) k_accum<true, false><<<grid, 256, 0, st>>>(P);
-            else k_accum<false, false><<<grid, 256, 0, st>>>(P);
+            if (pct) k_accum<true, false><<<grid, 256, sizeof(AggTable), st>>>(P);
+            else k_accum<false, false><<<grid, 256, sizeof(AggTable), st>>>(P);
         }
     });
     KGS_CUDA(h, cudaGetLastError());
