@@ -174,8 +174,10 @@ int kgs_set_run_log_capacity(kgs_handle h, uint64_t entries);
  * KGS_JC_POOL_ENTRIES   run-log entries taken from the shared overflow pool (0 in collector order);
  * KGS_JC_CACHE_CTAS     accumulate CTAs that folded runs in their shared-memory accumulator cache
  *                       first (input far from collector order: the flat random stream of configs[2]);
- * KGS_JC_BIG_CELLS      window cells of the last finalize counted by a whole warp (many samples);
- * KGS_JC_WIDE_CELLS     window cells of the last finalize with a value >= 104 (or the 16-bit metric).
+ * KGS_JC_BIG_CELLS      window cells of the last finalize counted by a whole warp (more than 256 samples, or
+ *                       a value >= 104);
+ * KGS_JC_WIDE_CELLS     window cells of the last finalize left to the 16-bit select, or (sliding windows) to
+ *                       the second kernel.
  * No reference counterpart (the reference has one code path). */
 enum { KGS_JC_POOL_ENTRIES = 0, KGS_JC_CACHE_CTAS = 1, KGS_JC_BIG_CELLS = 2, KGS_JC_WIDE_CELLS = 3, KGS_N_JOB_COUNTERS = 4 };
 int kgs_job_counter(kgs_handle h, int which, uint64_t* out);
@@ -205,7 +207,7 @@ int kgs_result_region(kgs_handle h, void** d_ptr, size_t* exchange_bytes, size_t
  *   on = 2, compact (8-bit metrics; fb_mib jobs fall back to packed): count u16, sum 24 bits (a u16 table
  *     and a u8 table), max u8, per percentile u8|u8<<8: 6 + 2*n_q bytes per cell.  A cell above 65 534
  *     samples has count 0xFFFF in the table and its full count and sum on an escape list at the head of
- *     the region ({u32 entries, 3 x u32 zero}, then {u32 global cell, u32 count, u64 sum} each; global
+ *     the region ({u32 entries, 3 x u32 reserved}, then {u32 global cell, u32 count, u64 sum} each; global
  *     cell = cells of the earlier key kinds + key * n_windows + window).  The list has room for 1/64 of
  *     the cells + 1024; beyond that the sender's next fetch fails with KGS_ERR_CAPACITY and the receiver
  *     sees entries > capacity - meant for windows of minutes, not of days.

@@ -355,14 +355,71 @@ __device__ __forceinline__ void defer_cell(const FinParams& P, bool wide, bool b
     }
 }
 
+// One window cell by a whole warp: u32 bins in shared memory (hist = 256 words of the warp's own), every lane
+// reads the same run descriptor and the warp counts the run's bytes together; the ranks are then located with a
+// warp scan over the 256 bins (lane l owns bins 8l .. 8l+7).  For cells with many samples, where one thread
+// walking the values is the long pole, and for cells with values >= 104, which the 104-bin thread histograms
+// cannot take.  count = the cell's sample count (a percentile job holds fewer than 2^32 samples).
+__device__ __forceinline__ void warp_cell_select(const FinParams& P, const FinKind& K, uint32_t c, uint32_t pc0,
+                                                 uint32_t count, uint32_t* hist) {
+    constexpr uint32_t kAll = 0xFFFFFFFFu;
+    const uint32_t lane = lane_id();
+    for (uint32_t b = lane; b < 256; b += 32) hist[b] = 0;
+    __syncwarp();
+    for (uint32_t d = 0; d < P.W; ++d) {
+        uint32_t at = K.head[pc0 + d];
+        while (at) {
+            const uint4 r = __ldg(P.desc + (at - 1));
+            for (uint32_t o = lane; o < r.y; o += 32) atomicAdd(hist + P.vals[(uint64_t)r.x + o], 1u);
+            at = r.z;
+        }
+    }
+    __syncwarp();
+    uint32_t mine[8], incl = 0;
+#pragma unroll
+    for (int b = 0; b < 8; ++b) {
+        mine[b] = hist[8 * lane + b];
+        incl += mine[b];
+    }
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t o = __shfl_up_sync(kAll, incl, d);
+        if (lane >= (uint32_t)d) incl += o;
+    }
+    const uint32_t excl = incl - (mine[0] + mine[1] + mine[2] + mine[3] + mine[4] + mine[5] + mine[6] + mine[7]);
+    auto value_of_rank = [&](uint32_t r) {   // every lane gets the answer
+        uint32_t v = 0;
+        if (excl <= r && r < incl) {
+            uint32_t cum = excl;
+#pragma unroll
+            for (int b = 0; b < 8; ++b) {
+                if (r >= cum && r - cum < mine[b]) v = 8 * lane + b;
+                cum += mine[b];
+            }
+        }
+        const uint32_t owner = __ballot_sync(kAll, excl <= r && r < incl);
+        return __shfl_sync(kAll, v, owner ? __ffs(owner) - 1 : 0);
+    };
+    for (uint32_t iq = 0; iq < P.n_q; ++iq) {
+        uint32_t ilo, ihi;
+        double w;
+        pct_ranks(P.q[iq], count, ilo, ihi, w);
+        const uint32_t vlo = value_of_rank(ilo), vhi = value_of_rank(ihi);
+        if (lane == 0) store_pct(P, K, c, iq, vlo, vhi, w);
+    }
+    __syncwarp();
+}
+
 // Every window cell that k_finalize_groups has not finished: count / sum / max / mean, and the
-// percentiles of cells with up to thread_cell_max samples whose values stay below 104.  Cells are
-// visited from the END of the index space (node cells, the heaviest, are scheduled first).  Cells
-// with more samples go to the big part of the rare list (a warp per cell), other non-empty cells
-// (a value >= 104, the 16-bit metric) to its wide part.
+// percentiles of cells with up to thread_cell_max samples whose values stay below 104 by a thread each
+// (private histogram); cells with more samples or larger values by their whole warp, one after the
+// other, in place (warp_cell_select) - no list, no second kernel.  Cells are visited from the END of
+// the index space (node cells, the heaviest, are spread first).  Cells of the 16-bit metric go on
+// the list k_finalize_u16 works off.
 __global__ void __launch_bounds__(CellLayout::NT, 8) k_finalize_cells(const __grid_constant__ FinParams P) {
     using L = CellLayout;
     __shared__ uint32_t hist[L::WORDS * L::NT];
+    __shared__ uint32_t hist32[L::NT / 32][256];     // warp-per-cell path (warp_cell_select)
     cudaGridDependencySynchronize();                 // a programmatic dependent of the kernel before it (no-op otherwise)
     cudaTriggerProgrammaticLaunchCompletion();
     const uint32_t tid = threadIdx.x;
@@ -401,10 +458,24 @@ __global__ void __launch_bounds__(CellLayout::NT, 8) k_finalize_cells(const __gr
         // a run log that overflowed holds incomplete lists: the host reports the error, skip selection
         if (P.n_q == 0 || P.ctl[1]) continue;
         const FinKind& K = P.kind[ks];
-        const bool big = live && !P.u16 && count > P.thread_cell_max;
-        const bool fast = live && count > 0 && !big && vmax < (uint32_t)L::BINS && !P.u16;
-        const bool wide = live && count > 0 && !fast && !big;
-        defer_cell(P, wide, big, ks, c);
+        // a cell with many samples, or with a value the 104-bin thread histogram cannot take, is counted by its
+        // whole warp right here (8-bit metrics); cells of the 16-bit metric go on the list k_finalize_u16 works off
+        const bool big = live && !P.u16 && count > 0 && (count > P.thread_cell_max || vmax >= (uint32_t)L::BINS);
+        const bool fast = live && count > 0 && !big && !P.u16;
+        const bool wide = live && count > 0 && P.u16;
+        defer_cell(P, wide, false, ks, c);
+        {
+            const uint32_t big_mask = __ballot_sync(0xFFFFFFFFu, big);
+            if (big_mask) {
+                if (lane_id() == 0) atomicAdd(P.ctl + 2, (uint32_t)__popc(big_mask));   // job counter
+                for (uint32_t m = big_mask; m; m &= m - 1) {
+                    const int src = __ffs(m) - 1;
+                    const uint32_t ks_b = __shfl_sync(0xFFFFFFFFu, ks, src), c_b = __shfl_sync(0xFFFFFFFFu, c, src);
+                    const uint32_t pc_b = __shfl_sync(0xFFFFFFFFu, pc0, src), n_b = __shfl_sync(0xFFFFFFFFu, (uint32_t)count, src);
+                    warp_cell_select(P, P.kind[ks_b], c_b, pc_b, n_b, hist32[tid >> 5]);
+                }
+            }
+        }
         // Twin cells.  With one process per GPU a (gpu, window) cell and its (pod, window) cell usually
         // consist of the very same single run, and k_accum wrote that run's descriptors side by side
         // (pod at index i, gpu at i + 1).  The pod cell's thread then selects once and stores the
@@ -480,10 +551,9 @@ __device__ __forceinline__ void finalize_wide_part(const FinParams& P, uint32_t 
 // Every lane reads the same descriptor, the whole warp counts each run's bytes; the ranks are then
 // located with a warp scan over the 256 bins (lane l owns bins 8l .. 8l+7).  The CTAs behind the wide part.
 __device__ __forceinline__ void finalize_big_part(const FinParams& P, uint32_t cta, uint32_t n_ctas) {
-    constexpr uint32_t kAll = 0xFFFFFFFFu;
     constexpr uint32_t kWarps = WideLayout::NT / 32;
     __shared__ uint32_t hist_all[kWarps][256];
-    const uint32_t lane = lane_id(), wib = threadIdx.x >> 5;
+    const uint32_t wib = threadIdx.x >> 5;
     uint32_t* hist = hist_all[wib];
     const uint32_t n_big = P.ctl[1] ? 0u : min(P.ctl[2], P.rare_cap);
     const uint32_t warps = n_ctas * kWarps;
@@ -493,51 +563,7 @@ __device__ __forceinline__ void finalize_big_part(const FinParams& P, uint32_t c
         const uint32_t c = P.rare_list[2 * e + 1];
         const uint32_t key = c / P.n_windows, j = c - key * P.n_windows;
         const uint32_t pc0 = key * P.n_panes + j;
-        for (uint32_t b = lane; b < 256; b += 32) hist[b] = 0;
-        __syncwarp();
-        for (uint32_t d = 0; d < P.W; ++d) {
-            uint32_t at = K.head[pc0 + d];
-            while (at) {
-                const uint4 r = __ldg(P.desc + (at - 1));
-                for (uint32_t o = lane; o < r.y; o += 32) atomicAdd(hist + P.vals[(uint64_t)r.x + o], 1u);
-                at = r.z;
-            }
-        }
-        __syncwarp();
-        const uint32_t count = K.o_count[c];     // a percentile job holds fewer than 2^32 samples, so u32 ranks suffice
-        uint32_t mine[8], incl = 0;
-#pragma unroll
-        for (int b = 0; b < 8; ++b) {
-            mine[b] = hist[8 * lane + b];
-            incl += mine[b];
-        }
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            const uint32_t o = __shfl_up_sync(kAll, incl, d);
-            if (lane >= (uint32_t)d) incl += o;
-        }
-        const uint32_t excl = incl - (mine[0] + mine[1] + mine[2] + mine[3] + mine[4] + mine[5] + mine[6] + mine[7]);
-        auto value_of_rank = [&](uint32_t r) {   // every lane gets the answer
-            uint32_t v = 0;
-            if (excl <= r && r < incl) {
-                uint32_t cum = excl;
-#pragma unroll
-                for (int b = 0; b < 8; ++b) {
-                    if (r >= cum && r - cum < mine[b]) v = 8 * lane + b;
-                    cum += mine[b];
-                }
-            }
-            const uint32_t owner = __ballot_sync(kAll, excl <= r && r < incl);
-            return __shfl_sync(kAll, v, owner ? __ffs(owner) - 1 : 0);
-        };
-        for (uint32_t iq = 0; iq < P.n_q; ++iq) {
-            uint32_t ilo, ihi;
-            double w;
-            pct_ranks(P.q[iq], count, ilo, ihi, w);
-            const uint32_t vlo = value_of_rank(ilo), vhi = value_of_rank(ihi);
-            if (lane == 0) store_pct(P, K, c, iq, vlo, vhi, w);
-        }
-        __syncwarp();
+        warp_cell_select(P, K, c, pc0, K.o_count[c], hist);
     }
 }
 

@@ -1276,6 +1276,7 @@ int kgs_stats_finalize(kgs_handle h) {
         }
     }
     if (!groups) P.done = nullptr;
+    bool rare_launched = false;
     if (cells) {
         if (h->W > 1 && h->slide && sp.metric != KGS_METRIC_FB) {
             // sliding windows: per-cell basics, then one thread per chunk of windows keeps the histogram sliding
@@ -1288,13 +1289,14 @@ int kgs_stats_finalize(kgs_handle h) {
                 if (grid) launch(h, KGS_K_FINALIZE, st, [&] { k_finalize_slide<<<grid, CellLayout::NT, 0, st>>>(P); });
             }
         } else {
-            launch(h, KGS_K_FINALIZE, st, [&] {   // at most one wave of CTAs (8 per SM), each walking blocks of cells
-                launch_after(k_finalize_cells, (unsigned)grid_for(cells, CellLayout::NT, 148 * 8), CellLayout::NT, st, pdl, P);
+            launch(h, KGS_K_FINALIZE, st, [&] {   // at most one wave of CTAs (7 per SM: 30.7 KB of shared memory each), each walking blocks of cells
+                launch_after(k_finalize_cells, (unsigned)grid_for(cells, CellLayout::NT, 148 * 7), CellLayout::NT, st, pdl, P);
             });
         }
         if (sp.n_q && sp.metric == KGS_METRIC_FB) {   // 16-bit values: two-digit radix select, warp per cell
             launch(h, KGS_K_FINALIZE_WIDE, st, [&] { k_finalize_u16<<<148 * 8, 128, 0, st>>>(P); });
-        } else if (sp.n_q) {   // one launch for the cells with values >= 104 and those with many samples
+        } else if (sp.n_q && h->W > 1 && h->slide) {   // sliding windows: one launch for the windows the sliding histograms could not take
+            rare_launched = true;
             const int wide_grid = grid_for(cells, WideLayout::NT, 148 * 6);
             const int big_grid = h->accumulated * h->W > h->thread_cell_max ? 148 * 4 : 0;
             P.rare_wide_ctas = (uint32_t)wide_grid;
@@ -1302,7 +1304,7 @@ int kgs_stats_finalize(kgs_handle h) {
         }
     }
     KGS_CUDA(h, cudaGetLastError());
-    if (h->packed_compact && !(cells && sp.n_q && sp.metric != KGS_METRIC_FB))   // k_finalize_rare was not there to do it
+    if (h->packed_compact && !rare_launched)   // k_finalize_rare was not there to do it
         KGS_CUDA(h, cudaMemcpyAsync(h->esc_hdr, h->ctl + 5, 4, cudaMemcpyDeviceToDevice, st));
     h->job_final = true;
     return KGS_OK;
