@@ -355,6 +355,18 @@ __device__ __forceinline__ void defer_cell(const FinParams& P, bool wide, bool b
     }
 }
 
+// Compact exchange tables: the length of the escape list belongs in the header of the exchanged region, and it is
+// final only when the last store_basics of the job has run.  Every CTA of the last kernel that stores basics calls
+// this once, all its threads together, on its way out; the CTA that arrives last writes the header.
+__device__ __forceinline__ void publish_escapes(const FinParams& P) {
+    if (!P.esc_hdr || threadIdx.x != 0) return;
+    __threadfence();
+    if (atomicAdd(P.ctl + 6, 1u) == gridDim.x - 1) {
+        P.esc_hdr[0] = *reinterpret_cast<volatile uint32_t*>(P.esc_count);
+        P.esc_hdr[1] = 0; P.esc_hdr[2] = 0; P.esc_hdr[3] = 0;
+    }
+}
+
 // One window cell by a whole warp: u32 bins in shared memory (hist = 256 words of the warp's own), every lane
 // reads the same run descriptor and the warp counts the run's bytes together; the ranks are then located with a
 // warp scan over the 256 bins (lane l owns bins 8l .. 8l+7).  For cells with many samples, where one thread
@@ -432,7 +444,10 @@ __global__ void __launch_bounds__(CellLayout::NT, 8) k_finalize_cells(const __gr
             const uint32_t i = blk * L::NT + tid;
             if (i < P.total_cells) all = all && P.done[P.total_cells - 1 - i] == (uint8_t)P.done_gen;
         }
-        if (__syncthreads_and(all)) return;
+        if (__syncthreads_and(all)) {
+            publish_escapes(P);
+            return;
+        }
     }
     for (uint32_t blk = blockIdx.x; blk < n_blocks; blk += gridDim.x) {
         const uint32_t idx = blk * L::NT + tid;
@@ -512,6 +527,8 @@ __global__ void __launch_bounds__(CellLayout::NT, 8) k_finalize_cells(const __gr
         add_cell<L>(base, P, K, pc0, work);   // warp-synchronous: every lane takes part
         if (work) select_store<L>(base, P, K, c, (uint32_t)count, vmax, twin_cell);
     }
+    __syncthreads();   // every store_basics of this CTA (and its escape-list entries) has been issued
+    publish_escapes(P);
 }
 
 // The wide list: values up to 255 (u16 bins, 256 values), at most 65 535 samples per cell.

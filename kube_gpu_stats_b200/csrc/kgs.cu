@@ -1223,7 +1223,7 @@ int kgs_stats_finalize(kgs_handle h) {
     P.esc_count = h->ctl + 5;
     // A job may be finalized more than once (more batches in between): the lists of cells left to
     // k_finalize_rare start empty each time.
-    if (h->job_final) KGS_CUDA(h, cudaMemsetAsync(h->ctl + 2, 0, 16, st));   // ctl[2..5]: rare-list lengths, spare, escape count
+    if (h->job_final) KGS_CUDA(h, cudaMemsetAsync(h->ctl + 2, 0, 20, st));   // ctl[2..6]: rare-list lengths, spare, escape count, CTAs done
     // This job's result region was last read by the exchange of the job two back: that comes first.  (Nothing before
     // the finalize kernels writes the region, so the wait sits here and not at begin: the exchange of job i may run
     // beside the accumulate kernel of job i+2.)
@@ -1276,7 +1276,7 @@ int kgs_stats_finalize(kgs_handle h) {
         }
     }
     if (!groups) P.done = nullptr;
-    bool rare_launched = false;
+    bool rare_launched = false;   // "the escape list's length has a kernel that publishes it" (k_finalize_rare, k_finalize_cells)
     if (cells) {
         if (h->W > 1 && h->slide && sp.metric != KGS_METRIC_FB) {
             // sliding windows: per-cell basics, then one thread per chunk of windows keeps the histogram sliding
@@ -1289,6 +1289,7 @@ int kgs_stats_finalize(kgs_handle h) {
                 if (grid) launch(h, KGS_K_FINALIZE, st, [&] { k_finalize_slide<<<grid, CellLayout::NT, 0, st>>>(P); });
             }
         } else {
+            rare_launched = !(sp.n_q && sp.metric == KGS_METRIC_FB);   // k_finalize_cells publishes the escape list's length itself
             launch(h, KGS_K_FINALIZE, st, [&] {   // at most one wave of CTAs (7 per SM: 30.7 KB of shared memory each), each walking blocks of cells
                 launch_after(k_finalize_cells, (unsigned)grid_for(cells, CellLayout::NT, 148 * 7), CellLayout::NT, st, pdl, P);
             });
