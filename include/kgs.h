@@ -109,6 +109,9 @@ int kgs_reorder_batch(kgs_handle h);
  * resident batch itself stays as ingested: kgs_probe and kgs_fetch_batch answer in the caller's order.  On by
  * default; 0 switches it off (also KGS_AUTO_REORDER=0).  Columns adopted from device memory are never looked at. */
 int kgs_set_auto_reorder(kgs_handle h, int on);
+/* The look itself, for callers that want to know (host arrays, no GPU involved): 0 long runs (collector
+ * order), 1 disordered, 2 several series interleaved with a period of 2..64 samples; -1 for a null array. */
+int kgs_input_order_class(const uint32_t* gpu_gid, const uint32_t* pid, uint64_t n);
 /* Copy the resident batch's columns back to host arrays of n entries (any pointer may be NULL). Blocking. */
 int kgs_fetch_batch(kgs_handle h, uint32_t* ts, uint32_t* gpu_gid, uint32_t* pid, uint32_t* util);
 /* Same, for columns that already live in this device's memory, 32-byte aligned (no copy is made;

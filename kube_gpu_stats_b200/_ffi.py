@@ -59,6 +59,7 @@ def load(path=LIB_PATH):
         'kgs_batch_append': [H, vp, vp, vp, vp, C.c_uint64],
         'kgs_reorder_batch': [H],
         'kgs_set_auto_reorder': [H, C.c_int],
+        'kgs_input_order_class': [vp, vp, C.c_uint64],
         'kgs_fetch_batch': [H, vp, vp, vp, vp],
         'kgs_adopt_device_batch': [H, vp, vp, vp, vp, C.c_uint64],
         'kgs_build_join': [H, vp, vp, C.c_uint64, C.c_uint32],

@@ -718,6 +718,11 @@ int kgs_reorder_batch(kgs_handle h) {
     return reorder_impl(h, true);
 }
 
+int kgs_input_order_class(const uint32_t* gpu_gid, const uint32_t* pid, uint64_t n) {
+    if (n && (!gpu_gid || !pid)) return -1;
+    return input_order_class(gpu_gid, pid, n);
+}
+
 int kgs_set_auto_reorder(kgs_handle h, int on) {
     if (!h) return KGS_ERR_ARG;
     h->auto_reorder = on != 0;
