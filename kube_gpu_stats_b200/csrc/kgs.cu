@@ -97,6 +97,13 @@ struct kgs_ctx {
     uint32_t mx_piece_bytes = 32u << 20;
     bool mx_valid = false;
     size_t clear_bytes = 0;
+    // The accumulators exist twice and alternate between jobs: the half the NEXT job will use is cleared on a stream of
+    // its own while this job's finalize kernels run, so that the 24 MB memset of configs[1] is not on the step's path.
+    cudaStream_t prep = nullptr;
+    cudaEvent_t acc_idle = nullptr, acc_clean[2] = {nullptr, nullptr};
+    struct PreCleared { bool valid = false; void* base = nullptr; size_t bytes = 0, shift = 0; } pre[2];
+    bool preclear_on = true, preclear_pending = false;
+    size_t acc_shift_other = 0;    // where the other half of the accumulators lies in the arena of the open job
     uint32_t* ctl = nullptr;       // [0] run cursor [1] run-log overflow [2] big cells listed [3] wide cells listed
     uint32_t* rare_list = nullptr; // cells left to k_finalize_rare: wide ones from the front, big ones from the back
     uint32_t rare_cap = 0;
@@ -460,6 +467,10 @@ int kgs_create(int device, kgs_handle* out) {
         if ((e = cudaEventCreate(&h->mark[b])) != cudaSuccess) return bail(e, "cudaEventCreate");
     }
     if ((e = cudaStreamCreateWithFlags(&h->xchg, cudaStreamNonBlocking)) != cudaSuccess) return bail(e, "cudaStreamCreate");
+    if ((e = cudaStreamCreateWithFlags(&h->prep, cudaStreamNonBlocking)) != cudaSuccess) return bail(e, "cudaStreamCreate");
+    if ((e = cudaEventCreateWithFlags(&h->acc_idle, cudaEventDisableTiming)) != cudaSuccess) return bail(e, "cudaEventCreate");
+    for (int b = 0; b < 2; ++b)
+        if ((e = cudaEventCreateWithFlags(&h->acc_clean[b], cudaEventDisableTiming)) != cudaSuccess) return bail(e, "cudaEventCreate");
     if ((e = cudaEventCreateWithFlags(&h->fin_done, cudaEventDisableTiming)) != cudaSuccess) return bail(e, "cudaEventCreate");
     for (int b = 0; b < 2; ++b)
         if ((e = cudaEventCreateWithFlags(&h->region_free[b], cudaEventDisableTiming)) != cudaSuccess) return bail(e, "cudaEventCreate");
@@ -478,6 +489,7 @@ int kgs_create(int device, kgs_handle* out) {
     if (const char* e = getenv("KGS_AUTO_REORDER")) h->auto_reorder = atoi(e) != 0;
     if (const char* e = getenv("KGS_PDL")) h->pdl = atoi(e) != 0;
     if (const char* e = getenv("KGS_PUSH_DEFER")) h->px_defer = atoi(e) != 0;
+    if (const char* e = getenv("KGS_PRECLEAR")) h->preclear_on = atoi(e) != 0;
     if (const char* e = getenv("KGS_STAGE_THREADS")) { const int v = atoi(e); if (v >= 0 && v <= 64) h->mx_stage_threads = v; }
     if (const char* e = getenv("KGS_THREAD_CELL_MAX")) { const int v = atoi(e); if (v >= 1 && v <= 65535) h->thread_cell_max = (uint32_t)v; }
     {   // dynamic shared memory of k_accum: the warps' tile buffers (TMA) or the accumulator cache, beside 21.5 KB of run queues
@@ -502,6 +514,10 @@ int kgs_destroy(kgs_handle h) {
     cudaStreamSynchronize(h->copy);
     cudaStreamSynchronize(h->compute);
     if (h->xchg) cudaStreamSynchronize(h->xchg);
+    if (h->prep) { cudaStreamSynchronize(h->prep); cudaStreamDestroy(h->prep); }
+    if (h->acc_idle) cudaEventDestroy(h->acc_idle);
+    for (int b = 0; b < 2; ++b)
+        if (h->acc_clean[b]) cudaEventDestroy(h->acc_clean[b]);
     if (h->nccl_comm && nccl_api().ok) nccl_api().comm_destroy(h->nccl_comm);
     if (h->xchg) cudaStreamDestroy(h->xchg);
     if (h->fin_done) cudaEventDestroy(h->fin_done);
@@ -547,6 +563,7 @@ int kgs_sync(kgs_handle h) {
     KGS_CUDA(h, cudaStreamSynchronize(h->copy));
     KGS_CUDA(h, cudaStreamSynchronize(h->compute));
     KGS_CUDA(h, cudaStreamSynchronize(h->xchg));
+    KGS_CUDA(h, cudaStreamSynchronize(h->prep));
     return KGS_OK;
 }
 
@@ -977,24 +994,31 @@ int kgs_stats_begin(kgs_handle h, const kgs_window_spec* sp) {
     const uint64_t rare_cap = pct ? window_cells : 0;
     const size_t rare_off = off;
     off = align_up(off + (size_t)rare_cap * 8, 256);
+    // the second half of the accumulators (jobs alternate; see kgs_ctx::pre)
+    const size_t acc1_off = off;
+    if (h->preclear_on) off = align_up(off + clear_bytes, 256);
+    const size_t acc_shift = (h->preclear_on && half) ? acc1_off : 0;
+    h->acc_shift_other = (h->preclear_on && !half) ? acc1_off : 0;
     // queued kernels may still use the previous job's arena
     if (off > h->arena.cap) {
         KGS_CUDA(h, cudaStreamSynchronize(h->compute));
         KGS_CUDA(h, cudaStreamSynchronize(h->xchg));
+        KGS_CUDA(h, cudaStreamSynchronize(h->prep));
     }
     int rc;
     if ((rc = reserve(h, h->arena, off))) return rc;
     char* base = static_cast<char*>(h->arena.p);
-    h->ctl = reinterpret_cast<uint32_t*>(base);
+    char* acc = base + acc_shift;   // this job's accumulators, control words and done flags
+    h->ctl = reinterpret_cast<uint32_t*>(acc);
     for (int k = 0; k < 3; ++k) {
         KindState& K = h->kind[k];
         K = KindState();
         if (!(sp->key_mask & (1u << k))) continue;
         K.n_keys = nk_in[k];
-        K.sum = reinterpret_cast<unsigned long long*>(base + lay[k].sum);
-        K.cnt = reinterpret_cast<uint32_t*>(base + lay[k].cnt);
-        K.mx = reinterpret_cast<uint32_t*>(base + lay[k].mx);
-        K.head = pct ? reinterpret_cast<uint32_t*>(base + lay[k].head) : nullptr;
+        K.sum = reinterpret_cast<unsigned long long*>(acc + lay[k].sum);
+        K.cnt = reinterpret_cast<uint32_t*>(acc + lay[k].cnt);
+        K.mx = reinterpret_cast<uint32_t*>(acc + lay[k].mx);
+        K.head = pct ? reinterpret_cast<uint32_t*>(acc + lay[k].head) : nullptr;
         K.o_count = reinterpret_cast<uint32_t*>(base + slot_shift + lay[k].oc);
         K.o_sum = reinterpret_cast<unsigned long long*>(base + slot_shift + lay[k].os);
         K.o_mean = reinterpret_cast<double*>(base + slot_shift + lay[k].omean);
@@ -1020,7 +1044,7 @@ int kgs_stats_begin(kgs_handle h, const kgs_window_spec* sp) {
     h->packed_bytes = packed_end - packed_begin;
     h->rare_list = reinterpret_cast<uint32_t*>(base + rare_off);
     h->rare_cap = (uint32_t)rare_cap;
-    h->done = pct ? reinterpret_cast<uint8_t*>(base + done_off) : nullptr;
+    h->done = pct ? reinterpret_cast<uint8_t*>(acc + done_off) : nullptr;
     h->done_bytes = pct ? (size_t)window_cells : 0;
     h->done_gen = 0;
     h->clear_bytes = clear_bytes;
@@ -1045,7 +1069,16 @@ int kgs_stats_begin(kgs_handle h, const kgs_window_spec* sp) {
         h->vals_cap = 0;
         h->desc_cap = 0;
     }
-    KGS_CUDA(h, cudaMemsetAsync(h->arena.p, 0, clear_bytes, h->compute));
+    {   // this job's half: cleared beside the previous job's finalize kernels if that job had the same layout, else now
+        kgs_ctx::PreCleared& pc = h->pre[half];
+        if (h->preclear_on && pc.valid && pc.base == h->arena.p && pc.bytes == clear_bytes && pc.shift == acc_shift)
+            KGS_CUDA(h, cudaStreamWaitEvent(h->compute, h->acc_clean[half], 0));
+        else
+            KGS_CUDA(h, cudaMemsetAsync(acc, 0, clear_bytes, h->compute));
+        pc.valid = false;
+        h->pre[half ^ 1].valid = false;   // cleared for another job's layout, or in use until this job's kernels have passed it
+        h->preclear_pending = h->preclear_on;
+    }
     h->spec = *sp;
     h->W = W;
     h->n_panes = (uint32_t)n_panes;
@@ -1168,6 +1201,18 @@ int kgs_stats_accumulate(kgs_handle h) {
     {   // the previous job's tables start travelling now, behind this kernel (kgs_exchange_push)
         int rc3 = flush_pending_push(h);
         if (rc3) return rc3;
+    }
+    if (h->preclear_pending) {   // the other half of the accumulators (the previous job's) is cleared for the next job, behind this kernel
+        h->preclear_pending = false;
+        const int other = h->region_half ^ 1;
+        KGS_CUDA(h, cudaEventRecord(h->acc_idle, st));
+        KGS_CUDA(h, cudaStreamWaitEvent(h->prep, h->acc_idle, 0));
+        KGS_CUDA(h, cudaMemsetAsync(static_cast<char*>(h->arena.p) + h->acc_shift_other, 0, h->clear_bytes, h->prep));
+        KGS_CUDA(h, cudaEventRecord(h->acc_clean[other], h->prep));
+        h->pre[other].valid = true;
+        h->pre[other].base = h->arena.p;
+        h->pre[other].bytes = h->clear_bytes;
+        h->pre[other].shift = h->acc_shift_other;
     }
     return KGS_OK;
 }
